@@ -1,0 +1,177 @@
+// oracle/oracle.cpp -- TEST INFRASTRUCTURE ONLY: the CPU oracle for the Sail path-tracing hot path.
+//
+// A scalar FP32 restatement of the reference's GLSL (files cited in oracle/shader_*.h), consuming
+// exactly the reference wire format: objects 18 x n, texParams 16 x tn, lights 18 x ln
+// (src/core/tracer.js:42-90) plus the uniforms of src/core/shader.js:41-49.
+//
+// PARITY UNPINNED: the reference ships no tests, golden vectors or CPU implementation of this path
+// and cannot be executed here (no JS engine, no graphics stack) -- SURVEY.md 4, 8(c).  The oracle's
+// arithmetic model is stated in oracle/glsl.h.
+//
+// Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load
+// this library.  The product (libsail_b200.so) never links or calls it.
+#include <omp.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include <vector>
+
+#ifdef SAIL_COUNT_OPS
+thread_local uint64_t g_sail_ops = 0;
+#endif
+
+#include "shader_trace.h"
+#include "oracle_filters.h"
+
+static std::vector<float> g_objects, g_texparams, g_lights;
+
+extern "C" {
+
+int oracle_set_scene(const float* objs, int n, const float* texparams, int tn, const float* lts, int ln) {
+    if (n < 0 || tn < 0 || ln < 0) return -1;
+    g_objects.assign(objs, objs + (size_t)n * 18);
+    g_texparams.assign(texparams, texparams + (size_t)tn * 16);
+    g_lights.assign(lts, lts + (size_t)ln * 18);
+    U.n = n;
+    U.tn = tn;
+    U.ln = ln;
+    U.objects_ = sampler2D{g_objects.data(), 18, n};
+    U.texParams_ = sampler2D{g_texparams.data(), 16, tn};
+    U.lights_ = sampler2D{g_lights.data(), 18, ln};
+    return 0;
+}
+
+static void set_frame(const float* matrix, const float* eye, float textureWeight, float time, int maxBounces) {
+    for (int i = 0; i < 16; i++) U.matrix.m[i] = real(matrix[i]);
+    U.eye = vec3(eye[0], eye[1], eye[2]);
+    U.textureWeight = real(textureWeight);
+    U.timeSinceStart_ = real(time);
+    U.maxBounces = maxBounces;
+}
+
+// One progressive frame (Tracer.render, src/core/tracer.js:92-101 + fstrace.glsl:6-17).
+// accum: W*H*3 running mean, read as `cache` and overwritten with out_color.  Row 0 = bottom row.
+// normal/position/hitId/depth may be NULL.  Returns the number of counted FP32 ops (0 unless built
+// with SAIL_COUNT_OPS).
+uint64_t oracle_render_frame(int W, int H, const float* matrix, const float* eye, float textureWeight, float time,
+                             int maxBounces, float* accum, float* normal, float* position, int* hitId, float* depth,
+                             int nthreads) {
+    set_frame(matrix, eye, textureWeight, time, maxBounces);
+    FrameRays fr = makeFrameRays();
+    uint64_t ops = 0;
+    if (nthreads <= 0) nthreads = omp_get_max_threads();
+#pragma omp parallel for schedule(dynamic, 4) num_threads(nthreads) reduction(+ : ops)
+    for (int y = 0; y < H; y++) {
+#ifdef SAIL_COUNT_OPS
+        g_sail_ops = 0;
+#endif
+        for (int x = 0; x < W; x++) {
+            size_t i = (size_t)y * W + x;
+            vec3 cache(accum[3 * i], accum[3 * i + 1], accum[3 * i + 2]);
+            PixelOut o = fstrace_main(fr, x, y, W, H, cache, nullptr);
+            accum[3 * i] = o.color.x.v; accum[3 * i + 1] = o.color.y.v; accum[3 * i + 2] = o.color.z.v;
+            if (normal) { normal[3 * i] = o.normal.x.v; normal[3 * i + 1] = o.normal.y.v; normal[3 * i + 2] = o.normal.z.v; }
+            if (position) { position[3 * i] = o.position.x.v; position[3 * i + 1] = o.position.y.v; position[3 * i + 2] = o.position.z.v; }
+            if (hitId) hitId[i] = o.hitId;
+            if (depth) depth[i] = o.depth.v;
+        }
+#ifdef SAIL_COUNT_OPS
+        ops += g_sail_ops;
+#endif
+    }
+    return ops;
+}
+
+// Per-bounce dump of one frame: hitId/t [W*H*maxBounces], rays [W*H*maxBounces*6]; radiance e [W*H*3]
+// (the un-accumulated sample).  Unreached bounces: hitId = -2.
+int oracle_trace_dump(int W, int H, const float* matrix, const float* eye, float time, int maxBounces, int* hitId,
+                      float* t, float* rays, float* radiance) {
+    set_frame(matrix, eye, 0.0f, time, maxBounces);
+    FrameRays fr = makeFrameRays();
+#pragma omp parallel for schedule(dynamic, 4)
+    for (int y = 0; y < H; y++) {
+        for (int x = 0; x < W; x++) {
+            size_t i = (size_t)y * W + x;
+            for (int b = 0; b < maxBounces; b++) {
+                hitId[i * maxBounces + b] = -2;
+                t[i * maxBounces + b] = 0.0f;
+                for (int k = 0; k < 6; k++) rays[(i * maxBounces + b) * 6 + k] = 0.0f;
+            }
+            BounceDump d{hitId + i * maxBounces, t + i * maxBounces, rays + i * maxBounces * 6};
+            PixelOut o = fstrace_main(fr, x, y, W, H, vec3(0.0f, 0.0f, 0.0f), &d);
+            if (radiance) { radiance[3 * i] = o.color.x.v; radiance[3 * i + 1] = o.color.y.v; radiance[3 * i + 2] = o.color.z.v; }
+        }
+    }
+    return 0;
+}
+
+// intersectObjects on arbitrary rays (fuzz / replay tests).  rays: N x 6 (origin, dir).
+// out: id (-1 miss), t, normal N x 3 (after the flip of shader.shape.js:39-40), matCategory.
+int oracle_intersect_rays(int N, const float* rays, int* id, float* t, float* normal, int* matCategory) {
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < N; i++) {
+        Ray r(vec3(rays[6 * i], rays[6 * i + 1], rays[6 * i + 2]), vec3(rays[6 * i + 3], rays[6 * i + 4], rays[6 * i + 5]));
+        Intersect ins = intersectObjects(r);
+        bool miss = ins.d >= real(MAX_DISTANCE);
+        id[i] = miss ? -1 : ins.index;
+        t[i] = ins.d.v;
+        if (normal) { normal[3 * i] = ins.normal.x.v; normal[3 * i + 1] = ins.normal.y.v; normal[3 * i + 2] = ins.normal.z.v; }
+        if (matCategory) matCategory[i] = miss ? 0 : ins.matCategory;
+    }
+    return 0;
+}
+
+// Full hit record for unit KATs: out[24] = d, hit(3), normal(3), dpdu(3), sc(3), emission(3), into, matCategory, index.
+int oracle_intersect_detail(const float* ray, float* out) {
+    Ray r(vec3(ray[0], ray[1], ray[2]), vec3(ray[3], ray[4], ray[5]));
+    Intersect ins = intersectObjects(r);
+    bool miss = ins.d >= real(MAX_DISTANCE);
+    memset(out, 0, 24 * sizeof(float));
+    out[0] = ins.d.v;
+    out[19] = miss ? -1.0f : (float)ins.index;
+    if (miss) return 0;
+    const vec3* v[5] = {&ins.hit, &ins.normal, &ins.dpdu, &ins.sc, &ins.emission};
+    for (int k = 0; k < 5; k++) { out[1 + 3 * k] = v[k]->x.v; out[2 + 3 * k] = v[k]->y.v; out[3 + 3 * k] = v[k]->z.v; }
+    out[16] = ins.into ? 1.0f : 0.0f;
+    out[17] = (float)ins.matCategory;
+    out[18] = ins.matIndex.v;
+    return 0;
+}
+
+// random2(seed) at a pixel (random.glsl:5-10), for RNG KATs.
+void oracle_random2(int x, int y, float seed, float* out) {
+    gl_FragCoord = vec3((float)x + 0.5f, (float)y + 0.5f, 0.5f);
+    vec2 u = random2(real(seed));
+    out[0] = u.x.v;
+    out[1] = u.y.v;
+}
+
+// Elementwise detmath KATs: which = 0 sin,1 cos,2 tan,3 atan,4 acos,5 asin,6 exp,7 log; 8 atan2(a,b); 9 pow(a,b)
+void oracle_detmath(int which, int N, const float* a, const float* b, float* out) {
+    for (int i = 0; i < N; i++) {
+        float x = a[i], y = b ? b[i] : 0.0f, r = 0.0f;
+        switch (which) {
+            case 0: r = dm_sin(x); break;
+            case 1: r = dm_cos(x); break;
+            case 2: r = dm_tan(x); break;
+            case 3: r = dm_atan(x); break;
+            case 4: r = dm_acos(x); break;
+            case 5: r = dm_asin(x); break;
+            case 6: r = dm_exp(x); break;
+            case 7: r = dm_log(x); break;
+            case 8: r = dm_atan2(x, y); break;
+            case 9: r = dm_pow(x, y); break;
+        }
+        out[i] = r;
+    }
+}
+
+int oracle_counts_ops(void) {
+#ifdef SAIL_COUNT_OPS
+    return 1;
+#else
+    return 0;
+#endif
+}
+
+}  // extern "C"

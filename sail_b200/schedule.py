@@ -1,0 +1,56 @@
+"""Deterministic frame schedule.
+
+The reference seeds its shader RNG with wall-clock seconds and jitters the frustum with
+``Math.random()`` (/root/reference/src/core/tracer.js:94-98), so its frames are not reproducible.
+Here both are explicit: frame k has ``timeSinceStart = float32((k+1)/60)`` and jitter
+``((2u1-1)/W, (2u2-1)/H)`` with (u1,u2) the 2k-th and (2k+1)-th outputs of mulberry32(20180120).
+"""
+import numpy as np
+
+DEFAULT_SEED = 20180120
+
+
+def _imul(a, b):
+    return (a * b) & 0xFFFFFFFF
+
+
+class Mulberry32:
+    def __init__(self, seed=DEFAULT_SEED):
+        self.a = seed & 0xFFFFFFFF
+
+    def next(self):
+        self.a = (self.a + 0x6D2B79F5) & 0xFFFFFFFF
+        a = self.a
+        t = _imul(a ^ (a >> 15), 1 | a)
+        t = ((t + _imul(t ^ (t >> 7), 61 | t)) & 0xFFFFFFFF) ^ t
+        return ((t ^ (t >> 14)) & 0xFFFFFFFF) / 4294967296.0
+
+
+class FrameSchedule:
+    """Supplies (jitter_x, jitter_y, timeSinceStart) for frame k; random access."""
+
+    def __init__(self, seed=DEFAULT_SEED):
+        self.seed = seed
+        self._rng = Mulberry32(seed)
+        self._u = []
+
+    def _ensure(self, count):
+        while len(self._u) < count:
+            self._u.append(self._rng.next())
+
+    def jitter_unit(self, k):
+        self._ensure(2 * k + 2)
+        return self._u[2 * k] * 2 - 1, self._u[2 * k + 1] * 2 - 1
+
+    def time(self, k):
+        return float(np.float32((k + 1) / 60.0))
+
+
+def frame_matrix(mvp, jitter_unit, width, height):
+    """tracer.js:94-96: inverse(Translation((jx, jy, 0)) * MVP), double precision, returned as the
+    column-major float32[16] that ``gl.uniformMatrix4fv`` receives (matrix.js:612-622)."""
+    t = np.eye(4, dtype=np.float64)
+    t[0, 3] = jitter_unit[0] / width
+    t[1, 3] = jitter_unit[1] / height
+    inv = np.linalg.inv(t @ np.asarray(mvp, dtype=np.float64))
+    return np.ascontiguousarray(inv.T.reshape(16).astype(np.float32))
