@@ -1,0 +1,180 @@
+/* sail_b200.h -- C ABI of libsail_b200.so: the B200 (sm_100a) path-tracing core behind Sail's
+ * Renderer / Tracer.
+ *
+ * This is the drop-in boundary (DESIGN.md "Boundary").  Each entry point replaces one
+ * step of the reference's WebGL path; the citation is the reference code that the function stands in
+ * for (paths relative to /root/reference).  The host (Node.js through the N-API shim of
+ * INTEGRATION.md, or the Python mirror in sail_b200/) keeps building the same three Float32 tables and
+ * the same per-frame uniforms as src/core/tracer.js does and hands them over unchanged.
+ *
+ * Conventions: plain C types only; every function returns 0 on success or a negative SAIL_ERR_*;
+ * sail_last_error() gives the message of the last failure on that context.  A context is not thread
+ * safe (the reference is driven from one JS event loop).  sail_render*() are asynchronous on the
+ * context's CUDA stream; sail_read_*() / sail_present() synchronise.  Image row 0 is the BOTTOM row
+ * (gl_FragCoord convention); pixels are row-major, interleaved channels.  There is no CPU fallback:
+ * without a usable sm_100 device sail_create() fails with SAIL_ERR_CUDA.
+ */
+#ifndef SAIL_B200_H
+#define SAIL_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SAIL_ABI_VERSION 1
+
+/* Row widths of the wire format (src/core/webgl.js:137-139). */
+#define SAIL_OBJECTS_LENGTH 18
+#define SAIL_TEXPARAMS_LENGTH 16
+#define SAIL_LIGHTS_LENGTH 18
+#define SAIL_MAX_FRAMES_PER_CALL 32
+
+enum {
+    SAIL_OK = 0,
+    SAIL_ERR_CUDA = -1,     /* no device / CUDA runtime failure (reference: alert(), src/core/webgl.js:222-225) */
+    SAIL_ERR_INVALID = -2,  /* bad argument or malformed table (reference: throw "<string>", src/scene/light.js:52) */
+    SAIL_ERR_STATE = -3,    /* call out of order, e.g. render before upload (reference: silent no-op, webgl.js:52) */
+    SAIL_ERR_NOMEM = -4
+};
+
+/* Display filter plugins (src/shader/filter/shader.filter.js:18-30). */
+enum {
+    SAIL_FILTER_COLOR = 0, SAIL_FILTER_GAMMA = 1, SAIL_FILTER_BOX = 2, SAIL_FILTER_GAUSSIAN = 3,
+    SAIL_FILTER_MITCHELL = 4, SAIL_FILTER_SINC = 5, SAIL_FILTER_TRIANGLE = 6, SAIL_FILTER_NORMAL = 7,
+    SAIL_FILTER_POSITION = 8, SAIL_FILTER_WAVELET = 9, SAIL_FILTER_TONEMAPPING = 10
+};
+
+/* Per-pixel outputs.  COLOR/NORMAL/POSITION are the three MRT attachments of
+ * src/shader/main/fstrace.glsl:2-4,14-16; HIT_ID and DEPTH expose Intersect.index / Intersect.d of the
+ * primary ray (src/shader/const/struct.glsl:2,11), which the reference computes but never outputs. */
+enum {
+    SAIL_AOV_COLOR = 0,     /* float32 x3: the progressive accumulation (frameCache[0], src/core/webgl.js:88-92) */
+    SAIL_AOV_NORMAL = 1,    /* float32 x3: n/2 + 0.5 */
+    SAIL_AOV_POSITION = 2,  /* float32 x3: normalize(p) */
+    SAIL_AOV_HIT_ID = 3,    /* int32 x1: object index of the first hit, -1 = miss */
+    SAIL_AOV_DEPTH = 4      /* float32 x1: first-hit distance in units of the un-normalised primary ray */
+};
+
+enum {
+    SAIL_ACCUM_MEAN = 0,  /* out = mix(e, cache, textureWeight)  (fstrace.glsl:13-14) -- the reference's update */
+    SAIL_ACCUM_SUM = 1    /* out = cache + e; textureWeight ignored.  For sample-sharded multi-GPU rendering:
+                             per-GPU sums are reduced and divided by the sample count (DESIGN.md "Multi-GPU") */
+};
+
+enum {
+    SAIL_KERNEL_MEGA = 0,      /* one thread traces a whole path (default) */
+    SAIL_KERNEL_WAVEFRONT = 1  /* per-bounce kernels over compacted ray queues */
+};
+
+typedef struct sail_ctx sail_ctx;
+
+/* new Sail.Renderer(canvas): src/core/renderer.js:9-39 + WebglHelper.initWebgl (src/core/webgl.js:215-227)
+ * + the frameCache allocation (webgl.js:12-28).  The 512x512 canvas becomes an explicit size. */
+typedef struct sail_create_info {
+    int32_t width, height;  /* full image size in pixels */
+    int32_t device;         /* CUDA device ordinal */
+    int32_t row_begin;      /* rows [row_begin, row_end) are rendered by this context (tile sharding); */
+    int32_t row_end;        /* 0,0 = the whole image.  Buffers always cover the full image. */
+    int32_t reserved[3];
+} sail_create_info;
+
+/* scene.tracerConfig() / scene.rendererConfig() lowered to PODs (src/scene/scene.js:70-118; plugin
+ * parameters of src/shader/generator.js:10-24).  The masks are specialisation hints (bit = category id of
+ * src/shader/const/define.glsl:18-44); results never depend on them. */
+typedef struct sail_config {
+    uint32_t shape_mask, material_mask, texture_mask, light_mask;
+    int32_t trace_id;         /* 0 = "path" (src/shader/trace/shader.trace.js:7-9) */
+    int32_t max_bounces;      /* MAXBOUNCES, const/define.glsl:6 (5) */
+    int32_t accum_mode;       /* SAIL_ACCUM_* */
+    int32_t kernel;           /* SAIL_KERNEL_* */
+    int32_t filter_id;        /* SAIL_FILTER_* */
+    float filter_gamma_c;     /* FILTER_GAMMA_C (filter/gamma.glsl:1-8) */
+    float filter_radius[2];   /* FILTER_WINDOW_RADIUS / FILTER_WAVELET_R */
+    float filter_weights[16]; /* windowWeightTable built by filter/{box,gaussian,mitchell,sinc,triangle}.js */
+    int32_t reserved[4];
+} sail_config;
+
+/* One frame's uniforms: Tracer.render(), src/core/tracer.js:92-101 / src/core/shader.js:41-49. */
+typedef struct sail_frame {
+    float matrix[16];     /* uniform mat4 matrix, column-major, already inverted and jittered on the host */
+    float eye[3];         /* uniform vec3 eye */
+    float textureWeight;  /* sampleCount / (sampleCount + 1) */
+    float timeSinceStart; /* seconds; seeds the per-pixel hash RNG (src/shader/trace/path.glsl:21) */
+} sail_frame;
+
+const char* sail_version(void);
+int sail_abi_version(void);
+/* Number of usable sm_100 devices (0 = none; never falls back to the CPU). */
+int sail_device_count(void);
+
+int sail_create(const sail_create_info* info, sail_ctx** out);
+void sail_destroy(sail_ctx* ctx);
+const char* sail_last_error(const sail_ctx* ctx);
+void sail_default_config(sail_config* cfg);
+
+/* setProgram(new TraceShader(scene.tracerConfig())) + setProgram(new RenderShader(scene.rendererConfig())):
+ * src/core/tracer.js:43, src/core/renderer.js:46. */
+int sail_configure(sail_ctx* ctx, const sail_config* cfg);
+
+/* Tracer.update(scene): src/core/tracer.js:42-90.  The library copies the tables (as texImage2D does). */
+int sail_upload_scene(sail_ctx* ctx, const float* objects, int32_t n, const float* texparams, int32_t tn,
+                      const float* lights, int32_t ln);
+/* Tracer.updateObjects(scene): src/core/tracer.js:25-40 (objects table only; n may change). */
+int sail_upload_objects(sail_ctx* ctx, const float* objects, int32_t n);
+
+/* Clears the accumulation and AOV buffers (a fresh frameCache; the reference instead restarts the running
+ * mean with textureWeight = 0 when scene.sampleCount is reset, src/core/renderer.js:57-60). */
+int sail_reset(sail_ctx* ctx);
+
+/* Tracer.render(mvp, eye, sampleCount) -> shader.render('triangle'): src/core/tracer.js:92-101,
+ * src/core/webgl.js:51-93.  One call = 1 sample per pixel over this context's rows. */
+int sail_render(sail_ctx* ctx, const float matrix_colmajor[16], const float eye[3], float textureWeight,
+                float timeSinceStart);
+/* `count` consecutive frames; pixel results equal `count` sail_render() calls, the accumulator stays in
+ * registers between frames.  AOVs are those of the last frame, as they would be after `count` calls. */
+int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count);
+
+int sail_synchronize(sail_ctx* ctx);
+
+/* Read back a full-image buffer (what readPixels on frameCache[0], [2], [3] would give). */
+int sail_read_aov(sail_ctx* ctx, int32_t which, void* out, size_t out_bytes);
+int sail_read_accum(sail_ctx* ctx, float* rgb, size_t out_bytes);
+/* Overwrite the accumulation buffer (resume a saved progressive image / install a reduced multi-GPU sum). */
+int sail_write_accum(sail_ctx* ctx, const float* rgb, size_t in_bytes);
+/* accum *= s (SAIL_ACCUM_SUM: divide the reduced sum by the sample count). */
+int sail_scale_accum(sail_ctx* ctx, float s);
+
+/* renderShader.render('triangle'): src/core/renderer.js:63, src/shader/main/fsrender.glsl:4-6 with the
+ * configured filter plugin.  Either output may be NULL.  rgba_f32: W*H*4 floats; rgba8: W*H*4 bytes
+ * (what the canvas would hold: clamped to [0,1], rounded to 8 bits). */
+int sail_present(sail_ctx* ctx, float* rgba_f32, uint8_t* rgba8);
+
+/* Device-side handles for hosts that combine buffers across GPUs themselves (torch.distributed / NCCL on
+ * the host side): raw device pointers of the full-image buffers and the CUDA stream (cudaStream_t). */
+void* sail_device_ptr(sail_ctx* ctx, int32_t which);
+void* sail_stream(sail_ctx* ctx);
+
+/* Diagnostics / picking: intersectObjects() (src/shader/shape/shader.shape.js:28-51) on caller-supplied
+ * rays.  rays: count x 6 (origin, dir).  Outputs (each may be NULL): hit_id (-1 = miss), t,
+ * normal count x 3 (flipped toward the ray), mat_category. */
+int sail_intersect_rays(sail_ctx* ctx, const float* rays, int32_t count, int32_t* hit_id, float* t, float* normal,
+                        int32_t* mat_category);
+/* One frame with per-bounce records (no accumulation): hit_id/t are W*H*max_bounces (unreached = -2),
+ * rays W*H*max_bounces*6, radiance W*H*3 (the raw sample e).  Each may be NULL. */
+int sail_trace_dump(sail_ctx* ctx, const sail_frame* frame, int32_t* hit_id, float* t, float* rays, float* radiance);
+/* Elementwise evaluation of the device math library: which = 0 sin, 1 cos, 2 tan, 3 atan, 4 acos, 5 asin,
+ * 6 exp, 7 log, 8 atan(a,b), 9 pow(a,b), 10 a/b, 11 sqrt. */
+int sail_eval_math(sail_ctx* ctx, int32_t which, const float* a, const float* b, float* out, int32_t count);
+/* Number of kernels this context has launched since creation. */
+uint64_t sail_launch_count(const sail_ctx* ctx);
+/* Device time of the most recent sail_render() / sail_render_n() call, from CUDA events recorded on the
+ * context's stream around its kernels, in milliseconds (synchronises). */
+int sail_last_render_ms(sail_ctx* ctx, float* ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,292 @@
+"""ctypes binding of ``libsail_b200.so`` (include/sail_b200.h).
+
+This is the Python twin of the N-API shim a Node.js host would use: it only marshals
+pointers and sizes across the C ABI.  There is no fallback -- if the library is missing or no sm_100
+device is present the calls raise.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsail_b200.so")
+
+MAX_FRAMES_PER_CALL = 32
+AOV_COLOR, AOV_NORMAL, AOV_POSITION, AOV_HIT_ID, AOV_DEPTH = range(5)
+ACCUM_MEAN, ACCUM_SUM = 0, 1
+KERNEL_MEGA, KERNEL_WAVEFRONT = 0, 1
+ERR_CUDA, ERR_INVALID, ERR_STATE, ERR_NOMEM = -1, -2, -3, -4
+
+
+class SailError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__("sail_b200 error %d: %s" % (code, message))
+        self.code = code
+
+
+class CreateInfo(ctypes.Structure):
+    _fields_ = [("width", ctypes.c_int32), ("height", ctypes.c_int32), ("device", ctypes.c_int32),
+                ("row_begin", ctypes.c_int32), ("row_end", ctypes.c_int32), ("reserved", ctypes.c_int32 * 3)]
+
+
+class Config(ctypes.Structure):
+    _fields_ = [("shape_mask", ctypes.c_uint32), ("material_mask", ctypes.c_uint32), ("texture_mask", ctypes.c_uint32),
+                ("light_mask", ctypes.c_uint32), ("trace_id", ctypes.c_int32), ("max_bounces", ctypes.c_int32),
+                ("accum_mode", ctypes.c_int32), ("kernel", ctypes.c_int32), ("filter_id", ctypes.c_int32),
+                ("filter_gamma_c", ctypes.c_float), ("filter_radius", ctypes.c_float * 2),
+                ("filter_weights", ctypes.c_float * 16), ("reserved", ctypes.c_int32 * 4)]
+
+
+class Frame(ctypes.Structure):
+    _fields_ = [("matrix", ctypes.c_float * 16), ("eye", ctypes.c_float * 3), ("textureWeight", ctypes.c_float),
+                ("timeSinceStart", ctypes.c_float)]
+
+
+#: every symbol include/sail_b200.h declares: name -> (restype, argtypes)
+_P = ctypes.c_void_p
+_SIGNATURES = {
+    "sail_version": (ctypes.c_char_p, []),
+    "sail_abi_version": (ctypes.c_int, []),
+    "sail_device_count": (ctypes.c_int, []),
+    "sail_create": (ctypes.c_int, [ctypes.POINTER(CreateInfo), ctypes.POINTER(_P)]),
+    "sail_destroy": (None, [_P]),
+    "sail_last_error": (ctypes.c_char_p, [_P]),
+    "sail_default_config": (None, [ctypes.POINTER(Config)]),
+    "sail_configure": (ctypes.c_int, [_P, ctypes.POINTER(Config)]),
+    "sail_upload_scene": (ctypes.c_int, [_P, _P, ctypes.c_int32, _P, ctypes.c_int32, _P, ctypes.c_int32]),
+    "sail_upload_objects": (ctypes.c_int, [_P, _P, ctypes.c_int32]),
+    "sail_reset": (ctypes.c_int, [_P]),
+    "sail_render": (ctypes.c_int, [_P, _P, _P, ctypes.c_float, ctypes.c_float]),
+    "sail_render_n": (ctypes.c_int, [_P, ctypes.POINTER(Frame), ctypes.c_int32]),
+    "sail_synchronize": (ctypes.c_int, [_P]),
+    "sail_read_aov": (ctypes.c_int, [_P, ctypes.c_int32, _P, ctypes.c_size_t]),
+    "sail_read_accum": (ctypes.c_int, [_P, _P, ctypes.c_size_t]),
+    "sail_write_accum": (ctypes.c_int, [_P, _P, ctypes.c_size_t]),
+    "sail_scale_accum": (ctypes.c_int, [_P, ctypes.c_float]),
+    "sail_present": (ctypes.c_int, [_P, _P, _P]),
+    "sail_device_ptr": (_P, [_P, ctypes.c_int32]),
+    "sail_stream": (_P, [_P]),
+    "sail_intersect_rays": (ctypes.c_int, [_P, _P, ctypes.c_int32, _P, _P, _P, _P]),
+    "sail_trace_dump": (ctypes.c_int, [_P, ctypes.POINTER(Frame), _P, _P, _P, _P]),
+    "sail_eval_math": (ctypes.c_int, [_P, ctypes.c_int32, _P, _P, _P, ctypes.c_int32]),
+    "sail_launch_count": (ctypes.c_uint64, [_P]),
+    "sail_last_render_ms": (ctypes.c_int, [_P, ctypes.POINTER(ctypes.c_float)]),
+}
+EXPORTED_SYMBOLS = tuple(_SIGNATURES)
+
+_lib = None
+
+
+def build(verbose=False):
+    """Compile libsail_b200.so in-tree with nvcc for sm_100a (sail_b200/csrc/Makefile)."""
+    out = None if verbose else subprocess.DEVNULL
+    subprocess.check_call(["make", "-C", os.path.join(_HERE, "csrc")], stdout=out)
+
+
+def load():
+    """Load the shared library (never builds implicitly, never falls back)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError("%s is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                              "(there is no CPU fallback)" % LIB_PATH)
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (restype, argtypes) in _SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = restype
+            fn.argtypes = argtypes
+        _lib = lib
+    return _lib
+
+
+def _f32(a, shape=None):
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    return a if shape is None else a.reshape(shape)
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(_P)
+
+
+def make_frame(matrix, eye, textureWeight, timeSinceStart):
+    f = Frame()
+    f.matrix[:] = [float(v) for v in np.asarray(matrix, dtype=np.float32).reshape(16)]
+    f.eye[:] = [float(v) for v in np.asarray(eye, dtype=np.float32).reshape(3)]
+    f.textureWeight = float(textureWeight)
+    f.timeSinceStart = float(timeSinceStart)
+    return f
+
+
+class Context:
+    """One ``sail_ctx``: a device, a stream and the full-image device buffers."""
+
+    def __init__(self, width, height, device=0, rows=None):
+        self.lib = load()
+        self.width, self.height = int(width), int(height)
+        info = CreateInfo(self.width, self.height, int(device), 0, 0)
+        if rows is not None:
+            info.row_begin, info.row_end = int(rows[0]), int(rows[1])
+        handle = _P()
+        rc = self.lib.sail_create(ctypes.byref(info), ctypes.byref(handle))
+        self._h = handle
+        if rc != 0:
+            msg = self.lib.sail_last_error(handle).decode() if handle else "sail_create failed"
+            if handle:
+                self.lib.sail_destroy(handle)
+            self._h = None
+            raise SailError(rc, msg)
+        self.config = Config()
+        self.lib.sail_default_config(ctypes.byref(self.config))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.sail_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _check(self, rc):
+        if rc != 0:
+            raise SailError(rc, self.lib.sail_last_error(self._h).decode())
+
+    # ---- configuration / upload -------------------------------------------------------------------------
+    def configure(self, **kw):
+        """Update fields of the sail_config (max_bounces, accum_mode, kernel, filter_id, filter_gamma_c,
+        filter_radius, filter_weights, *_mask) and apply it."""
+        for k, v in kw.items():
+            if k in ("filter_radius", "filter_weights"):
+                arr = getattr(self.config, k)
+                arr[:] = [float(x) for x in v]
+            else:
+                if not hasattr(self.config, k):
+                    raise AttributeError("sail_config has no field %r" % k)
+                setattr(self.config, k, v)
+        self._check(self.lib.sail_configure(self._h, ctypes.byref(self.config)))
+
+    def upload_scene(self, objects, texparams, lights):
+        o, t, l = _f32(objects).reshape(-1), _f32(texparams).reshape(-1), _f32(lights).reshape(-1)
+        if o.size % 18 or t.size % 16 or l.size % 18:
+            raise SailError(ERR_INVALID, "table sizes must be multiples of 18 / 16 / 18 floats")
+        self._check(self.lib.sail_upload_scene(self._h, _ptr(o) if o.size else None, o.size // 18,
+                                               _ptr(t) if t.size else None, t.size // 16,
+                                               _ptr(l) if l.size else None, l.size // 18))
+
+    def upload_objects(self, objects):
+        o = _f32(objects).reshape(-1)
+        self._check(self.lib.sail_upload_objects(self._h, _ptr(o) if o.size else None, o.size // 18))
+
+    def reset(self):
+        self._check(self.lib.sail_reset(self._h))
+
+    # ---- rendering ------------------------------------------------------------------------------------
+    def render(self, matrix, eye, textureWeight, timeSinceStart):
+        m, e = _f32(matrix, 16), _f32(eye, 3)
+        self._check(self.lib.sail_render(self._h, _ptr(m), _ptr(e), float(textureWeight), float(timeSinceStart)))
+
+    def render_n(self, frames):
+        """``frames``: a ctypes array of Frame (see ``frame_array``) or a list of Frame."""
+        if isinstance(frames, (list, tuple)):
+            frames = (Frame * len(frames))(*frames)
+        count = len(frames)
+        for start in range(0, count, MAX_FRAMES_PER_CALL):
+            n = min(MAX_FRAMES_PER_CALL, count - start)
+            chunk = ctypes.cast(ctypes.byref(frames, start * ctypes.sizeof(Frame)), ctypes.POINTER(Frame))
+            self._check(self.lib.sail_render_n(self._h, chunk, n))
+
+    def synchronize(self):
+        self._check(self.lib.sail_synchronize(self._h))
+
+    def last_render_ms(self):
+        ms = ctypes.c_float()
+        self._check(self.lib.sail_last_render_ms(self._h, ctypes.byref(ms)))
+        return ms.value
+
+    def launch_count(self):
+        return int(self.lib.sail_launch_count(self._h))
+
+    # ---- outputs -------------------------------------------------------------------------------------
+    def read_aov(self, which, out=None):
+        H, W = self.height, self.width
+        if which in (AOV_COLOR, AOV_NORMAL, AOV_POSITION):
+            shape, dtype = (H, W, 3), np.float32
+        elif which == AOV_HIT_ID:
+            shape, dtype = (H, W), np.int32
+        elif which == AOV_DEPTH:
+            shape, dtype = (H, W), np.float32
+        else:
+            raise SailError(ERR_INVALID, "unknown AOV %r" % (which,))
+        if out is None:
+            out = np.empty(shape, dtype)
+        assert out.shape == shape and out.dtype == dtype and out.flags.c_contiguous
+        self._check(self.lib.sail_read_aov(self._h, which, _ptr(out), out.nbytes))
+        return out
+
+    def read_accum(self, out=None):
+        return self.read_aov(AOV_COLOR, out)
+
+    def write_accum(self, rgb):
+        a = _f32(rgb, (self.height, self.width, 3))
+        self._check(self.lib.sail_write_accum(self._h, _ptr(a), a.nbytes))
+
+    def scale_accum(self, s):
+        self._check(self.lib.sail_scale_accum(self._h, float(s)))
+
+    def present(self, as_u8=False, both=False):
+        H, W = self.height, self.width
+        f32 = np.empty((H, W, 4), np.float32) if (both or not as_u8) else None
+        u8 = np.empty((H, W, 4), np.uint8) if (both or as_u8) else None
+        self._check(self.lib.sail_present(self._h, _ptr(f32), _ptr(u8)))
+        if both:
+            return f32, u8
+        return u8 if as_u8 else f32
+
+    def device_ptr(self, which):
+        return self.lib.sail_device_ptr(self._h, which)
+
+    def stream(self):
+        return self.lib.sail_stream(self._h)
+
+    # ---- diagnostics ------------------------------------------------------------------------------------
+    def intersect_rays(self, rays):
+        r = _f32(rays).reshape(-1, 6)
+        n = r.shape[0]
+        ids, t = np.empty(n, np.int32), np.empty(n, np.float32)
+        normal, mat = np.empty((n, 3), np.float32), np.empty(n, np.int32)
+        self._check(self.lib.sail_intersect_rays(self._h, _ptr(r), n, _ptr(ids), _ptr(t), _ptr(normal), _ptr(mat)))
+        return ids, t, normal, mat
+
+    def trace_dump(self, frame):
+        H, W, B = self.height, self.width, int(self.config.max_bounces)
+        hit, t = np.empty((H, W, B), np.int32), np.empty((H, W, B), np.float32)
+        rays, rad = np.empty((H, W, B, 6), np.float32), np.empty((H, W, 3), np.float32)
+        self._check(self.lib.sail_trace_dump(self._h, ctypes.byref(frame), _ptr(hit), _ptr(t), _ptr(rays), _ptr(rad)))
+        return {"hit_id": hit, "t": t, "rays": rays, "radiance": rad}
+
+    def eval_math(self, which, a, b=None):
+        names = {"sin": 0, "cos": 1, "tan": 2, "atan": 3, "acos": 4, "asin": 5, "exp": 6, "log": 7, "atan2": 8,
+                 "pow": 9, "div": 10, "sqrt": 11}
+        a = _f32(a).reshape(-1)
+        bb = None if b is None else _f32(b).reshape(-1)
+        out = np.empty_like(a)
+        self._check(self.lib.sail_eval_math(self._h, names[which], _ptr(a), _ptr(bb), _ptr(out), a.size))
+        return out
+
+
+def frame_array(frames):
+    return (Frame * len(frames))(*frames)
+
+
+def device_count():
+    return int(load().sail_device_count())

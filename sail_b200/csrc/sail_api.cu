@@ -1,0 +1,444 @@
+// sail_api.cu -- libsail_b200.so: the C ABI of include/sail_b200.h over the sm_100a kernels.
+//
+// Stands in for the reference's render orchestration + GPU abstraction on the hot path:
+// Renderer/Tracer (/root/reference/src/core/renderer.js:8-73, src/core/tracer.js:8-101) and ShaderProgram's
+// framebuffer/texture/uniform plumbing (src/core/webgl.js:4-135).  Device-resident FP32 buffers replace
+// ShaderProgram.frameCache[0..3]; a packed scene block replaces the three R32F textures; CUDA kernels
+// replace the trace and render programs.  No CPU fallback exists in this file or anywhere in the library.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <new>
+#include <vector>
+
+#include "../../include/sail_b200.h"
+#include "sail_mega.cuh"
+#include "sail_present.cuh"
+#include "sail_wavefront.cuh"
+
+struct sail_ctx {
+    int device = 0;
+    int W = 0, H = 0, y0 = 0, y1 = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t evStart = nullptr, evStop = nullptr;
+    bool timed = false;
+    sail_config cfg;
+    bool sceneLoaded = false;
+    std::vector<float> texparams, lights;  // kept for sail_upload_objects (tracer.js:25-40 re-uses them)
+    int tn = 0, ln = 0;
+    SailSceneBlock hostScene;
+    SailSceneBlock* dScene = nullptr;
+    float *accum = nullptr, *normal = nullptr, *position = nullptr, *depth = nullptr;
+    int* hitId = nullptr;
+    float* presentF32 = nullptr;
+    unsigned char* presentU8 = nullptr;
+    SailWavefront wf;
+    uint64_t launches = 0;
+    char err[512];
+    sail_ctx() { err[0] = 0; }
+};
+
+namespace {
+
+int setErr(sail_ctx* c, int code, const char* fmt, ...) {
+    if (c) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(c->err, sizeof(c->err), fmt, ap);
+        va_end(ap);
+    }
+    return code;
+}
+#define CU(call)                                                                                          \
+    do {                                                                                                  \
+        cudaError_t e_ = (call);                                                                          \
+        if (e_ != cudaSuccess) return setErr(ctx, SAIL_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); \
+    } while (0)
+
+size_t npix(const sail_ctx* c) { return (size_t)c->W * c->H; }
+
+// vstrace.glsl:4-7 for the four quad corners + the edge differences of the interpolation, in the FP32
+// arithmetic of the shader (this file is compiled with -ffp-contract=off on the host side).
+struct H3 { float x, y, z; };
+H3 cornerRay(const float* M, const float* eye, float vx, float vy) {
+    const float vz = 0.0f, vw = 1.0f;
+    float px = M[0] * vx + M[4] * vy + M[8] * vz + M[12] * vw;
+    float py = M[1] * vx + M[5] * vy + M[9] * vz + M[13] * vw;
+    float pz = M[2] * vx + M[6] * vy + M[10] * vz + M[14] * vw;
+    float pw = M[3] * vx + M[7] * vy + M[11] * vz + M[15] * vw;
+    float rw = dm_rcp(pw);
+    H3 d{px * rw - eye[0], py * rw - eye[1], pz * rw - eye[2]};  // ensure3byW(...) - eye
+    float inv = dm_rcp(dm_sqrt(d.x * d.x + d.y * d.y + d.z * d.z));
+    return H3{d.x * inv, d.y * inv, d.z * inv};
+}
+void sub3(float* out, H3 a, H3 b) { out[0] = a.x - b.x; out[1] = a.y - b.y; out[2] = a.z - b.z; }
+void lowerFrame(const sail_frame& f, SailFrameDev& o) {
+    H3 d0 = cornerRay(f.matrix, f.eye, -1.0f, -1.0f), d1 = cornerRay(f.matrix, f.eye, -1.0f, 1.0f);
+    H3 d2 = cornerRay(f.matrix, f.eye, 1.0f, -1.0f), d3 = cornerRay(f.matrix, f.eye, 1.0f, 1.0f);
+    o.d0[0] = d0.x; o.d0[1] = d0.y; o.d0[2] = d0.z;
+    o.d3[0] = d3.x; o.d3[1] = d3.y; o.d3[2] = d3.z;
+    sub3(o.e20, d2, d0); sub3(o.e10, d1, d0); sub3(o.e13, d1, d3); sub3(o.e23, d2, d3);
+    for (int k = 0; k < 3; k++) o.eye[k] = f.eye[k];
+    o.textureWeight = f.textureWeight;
+    o.timeSinceStart = f.timeSinceStart;
+    o.pad = 0.0f;
+}
+
+int uploadBlock(sail_ctx* ctx) {
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemcpyAsync(ctx->dScene, &ctx->hostScene, sizeof(SailSceneBlock), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));  // hostScene may be rewritten by the next upload
+    ctx->sceneLoaded = true;
+    return SAIL_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* sail_version(void) { return "sail-b200 0.1 (sm_100a)"; }
+int sail_abi_version(void) { return SAIL_ABI_VERSION; }
+
+int sail_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    int ok = 0;
+    for (int i = 0; i < n; i++) {
+        cudaDeviceProp p;
+        if (cudaGetDeviceProperties(&p, i) == cudaSuccess && p.major == 10) ok++;
+    }
+    return ok;
+}
+
+void sail_default_config(sail_config* cfg) {
+    if (!cfg) return;
+    memset(cfg, 0, sizeof(*cfg));
+    cfg->shape_mask = cfg->material_mask = cfg->texture_mask = cfg->light_mask = 0xffffffffu;
+    cfg->trace_id = 0;
+    cfg->max_bounces = 5;  // const/define.glsl:6
+    cfg->accum_mode = SAIL_ACCUM_MEAN;
+    cfg->kernel = SAIL_KERNEL_MEGA;
+    cfg->filter_id = SAIL_FILTER_COLOR;
+    cfg->filter_gamma_c = 2.2f;
+}
+
+int sail_create(const sail_create_info* info, sail_ctx** out) {
+    if (!info || !out) return SAIL_ERR_INVALID;
+    *out = nullptr;
+    sail_ctx* ctx = new (std::nothrow) sail_ctx();
+    if (!ctx) return SAIL_ERR_NOMEM;
+    *out = ctx;  // returned even on failure so the caller can read sail_last_error(); destroy it afterwards
+    if (info->width <= 0 || info->height <= 0 || (size_t)info->width * info->height > ((size_t)1 << 28))
+        return setErr(ctx, SAIL_ERR_INVALID, "bad image size %dx%d", info->width, info->height);
+    ctx->W = info->width;
+    ctx->H = info->height;
+    ctx->y0 = info->row_begin;
+    ctx->y1 = info->row_end;
+    if (ctx->y0 == 0 && ctx->y1 == 0) ctx->y1 = ctx->H;
+    if (ctx->y0 < 0 || ctx->y1 > ctx->H || ctx->y0 >= ctx->y1)
+        return setErr(ctx, SAIL_ERR_INVALID, "bad row range [%d,%d) for height %d", ctx->y0, ctx->y1, ctx->H);
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return setErr(ctx, SAIL_ERR_CUDA, "no CUDA device (%s); libsail_b200 has no CPU path", e == cudaSuccess ? "count = 0" : cudaGetErrorString(e));
+    }
+    if (info->device < 0 || info->device >= ndev) return setErr(ctx, SAIL_ERR_INVALID, "device %d out of range (%d devices)", info->device, ndev);
+    ctx->device = info->device;
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, ctx->device));
+    if (prop.major != 10)
+        return setErr(ctx, SAIL_ERR_CUDA, "device %d is sm_%d%d; this library carries sm_100a code only", ctx->device, prop.major, prop.minor);
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&ctx->evStart));
+    CU(cudaEventCreate(&ctx->evStop));
+    size_t n = npix(ctx);
+    CU(cudaMalloc(&ctx->dScene, sizeof(SailSceneBlock)));
+    CU(cudaMalloc(&ctx->accum, n * 3 * sizeof(float)));
+    CU(cudaMalloc(&ctx->normal, n * 3 * sizeof(float)));
+    CU(cudaMalloc(&ctx->position, n * 3 * sizeof(float)));
+    CU(cudaMalloc(&ctx->depth, n * sizeof(float)));
+    CU(cudaMalloc(&ctx->hitId, n * sizeof(int)));
+    sail_default_config(&ctx->cfg);
+    return sail_reset(ctx);
+}
+
+void sail_destroy(sail_ctx* ctx) {
+    if (!ctx) return;
+    if (ctx->stream) {
+        cudaSetDevice(ctx->device);
+        cudaStreamSynchronize(ctx->stream);
+    }
+    ctx->wf.release();
+    cudaFree(ctx->dScene); cudaFree(ctx->accum); cudaFree(ctx->normal); cudaFree(ctx->position);
+    cudaFree(ctx->depth); cudaFree(ctx->hitId); cudaFree(ctx->presentF32); cudaFree(ctx->presentU8);
+    if (ctx->evStart) cudaEventDestroy(ctx->evStart);
+    if (ctx->evStop) cudaEventDestroy(ctx->evStop);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char* sail_last_error(const sail_ctx* ctx) { return ctx ? ctx->err : "null context"; }
+
+int sail_configure(sail_ctx* ctx, const sail_config* cfg) {
+    if (!ctx || !cfg) return SAIL_ERR_INVALID;
+    if (cfg->trace_id != 0) return setErr(ctx, SAIL_ERR_INVALID, "unknown trace plugin id %d (only 0 = path)", cfg->trace_id);
+    if (cfg->max_bounces < 0 || cfg->max_bounces > 1024) return setErr(ctx, SAIL_ERR_INVALID, "max_bounces %d out of range", cfg->max_bounces);
+    if (cfg->filter_id < 0 || cfg->filter_id > SAIL_FILTER_TONEMAPPING) return setErr(ctx, SAIL_ERR_INVALID, "unknown filter id %d", cfg->filter_id);
+    if (cfg->accum_mode != SAIL_ACCUM_MEAN && cfg->accum_mode != SAIL_ACCUM_SUM) return setErr(ctx, SAIL_ERR_INVALID, "unknown accum_mode %d", cfg->accum_mode);
+    if (cfg->kernel != SAIL_KERNEL_MEGA && cfg->kernel != SAIL_KERNEL_WAVEFRONT) return setErr(ctx, SAIL_ERR_INVALID, "unknown kernel %d", cfg->kernel);
+    ctx->cfg = *cfg;
+    return SAIL_OK;
+}
+
+int sail_upload_scene(sail_ctx* ctx, const float* objects, int32_t n, const float* texparams, int32_t tn,
+                      const float* lights, int32_t ln) {
+    if (!ctx) return SAIL_ERR_INVALID;
+    if (!ctx->dScene) return setErr(ctx, SAIL_ERR_STATE, "context was not created successfully");
+    char msg[256];
+    msg[0] = 0;
+    int rc = sail_pack_scene(objects, n, texparams, tn, lights, ln, &ctx->hostScene, msg, sizeof(msg));
+    if (rc) return setErr(ctx, rc, "sail_upload_scene: %s", msg);
+    ctx->texparams.assign(texparams, texparams + (size_t)tn * SAIL_TEXPARAMS_LENGTH);
+    ctx->lights.assign(lights, lights + (size_t)ln * SAIL_LIGHTS_LENGTH);
+    ctx->tn = tn;
+    ctx->ln = ln;
+    return uploadBlock(ctx);
+}
+
+int sail_upload_objects(sail_ctx* ctx, const float* objects, int32_t n) {
+    if (!ctx) return SAIL_ERR_INVALID;
+    if (!ctx->sceneLoaded) return setErr(ctx, SAIL_ERR_STATE, "sail_upload_objects before sail_upload_scene");
+    char msg[256];
+    msg[0] = 0;
+    int rc = sail_pack_scene(objects, n, ctx->texparams.data(), ctx->tn, ctx->lights.data(), ctx->ln, &ctx->hostScene, msg, sizeof(msg));
+    if (rc) return setErr(ctx, rc, "sail_upload_objects: %s", msg);
+    return uploadBlock(ctx);
+}
+
+int sail_reset(sail_ctx* ctx) {
+    if (!ctx || !ctx->accum) return SAIL_ERR_INVALID;
+    CU(cudaSetDevice(ctx->device));
+    size_t n = npix(ctx);
+    CU(cudaMemsetAsync(ctx->accum, 0, n * 3 * sizeof(float), ctx->stream));
+    CU(cudaMemsetAsync(ctx->normal, 0, n * 3 * sizeof(float), ctx->stream));
+    CU(cudaMemsetAsync(ctx->position, 0, n * 3 * sizeof(float), ctx->stream));
+    CU(cudaMemsetAsync(ctx->depth, 0, n * sizeof(float), ctx->stream));
+    CU(cudaMemsetAsync(ctx->hitId, 0xff, n * sizeof(int), ctx->stream));
+    return SAIL_OK;
+}
+
+int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
+    if (!ctx || !frames) return SAIL_ERR_INVALID;
+    if (!ctx->sceneLoaded) return setErr(ctx, SAIL_ERR_STATE, "sail_render before sail_upload_scene");
+    if (count <= 0 || count > SAIL_MAX_FRAMES_PER_CALL) return setErr(ctx, SAIL_ERR_INVALID, "frame count %d not in 1..%d", count, SAIL_MAX_FRAMES_PER_CALL);
+    CU(cudaSetDevice(ctx->device));
+    SailLaunch L;
+    L.W = ctx->W; L.H = ctx->H; L.y0 = ctx->y0; L.y1 = ctx->y1;
+    L.maxBounces = ctx->cfg.max_bounces;
+    L.nframes = count;
+    L.accumMode = ctx->cfg.accum_mode;
+    L.writeAov = 1;
+    L.rcpW = dm_rcp((float)ctx->W);
+    L.rcpH = dm_rcp((float)ctx->H);
+    L.accum = ctx->accum; L.normal = ctx->normal; L.position = ctx->position; L.hitId = ctx->hitId; L.depth = ctx->depth;
+    L.scene = ctx->dScene;
+    for (int k = 0; k < count; k++) lowerFrame(frames[k], L.frames[k]);
+    CU(cudaEventRecord(ctx->evStart, ctx->stream));
+    if (ctx->cfg.kernel == SAIL_KERNEL_WAVEFRONT) {
+        int launched = 0;
+        cudaError_t e = ctx->wf.render(L, ctx->stream, &launched);
+        ctx->launches += launched;
+        if (e != cudaSuccess) return setErr(ctx, SAIL_ERR_CUDA, "wavefront render failed: %s", cudaGetErrorString(e));
+    } else {
+        dim3 grid((ctx->W + SAIL_TILE_W - 1) / SAIL_TILE_W, (ctx->y1 - ctx->y0 + SAIL_TILE_H - 1) / SAIL_TILE_H);
+        sail_trace_megakernel<<<grid, SAIL_CTA_THREADS, 0, ctx->stream>>>(L);
+        ctx->launches++;
+        CU(cudaGetLastError());
+    }
+    CU(cudaEventRecord(ctx->evStop, ctx->stream));
+    ctx->timed = true;
+    return SAIL_OK;
+}
+
+int sail_render(sail_ctx* ctx, const float matrix_colmajor[16], const float eye[3], float textureWeight, float timeSinceStart) {
+    if (!ctx || !matrix_colmajor || !eye) return SAIL_ERR_INVALID;
+    sail_frame f;
+    memcpy(f.matrix, matrix_colmajor, sizeof(f.matrix));
+    memcpy(f.eye, eye, sizeof(f.eye));
+    f.textureWeight = textureWeight;
+    f.timeSinceStart = timeSinceStart;
+    return sail_render_n(ctx, &f, 1);
+}
+
+int sail_synchronize(sail_ctx* ctx) {
+    if (!ctx || !ctx->stream) return SAIL_ERR_INVALID;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return SAIL_OK;
+}
+
+void* sail_device_ptr(sail_ctx* ctx, int32_t which) {
+    if (!ctx) return nullptr;
+    switch (which) {
+        case SAIL_AOV_COLOR: return ctx->accum;
+        case SAIL_AOV_NORMAL: return ctx->normal;
+        case SAIL_AOV_POSITION: return ctx->position;
+        case SAIL_AOV_HIT_ID: return ctx->hitId;
+        case SAIL_AOV_DEPTH: return ctx->depth;
+    }
+    return nullptr;
+}
+void* sail_stream(sail_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+int sail_read_aov(sail_ctx* ctx, int32_t which, void* out, size_t out_bytes) {
+    if (!ctx || !out) return SAIL_ERR_INVALID;
+    void* src = sail_device_ptr(ctx, which);
+    if (!src) return setErr(ctx, SAIL_ERR_INVALID, "unknown AOV %d", which);
+    size_t bytes = npix(ctx) * ((which == SAIL_AOV_HIT_ID || which == SAIL_AOV_DEPTH) ? 4 : 12);
+    if (out_bytes != bytes) return setErr(ctx, SAIL_ERR_INVALID, "AOV %d needs %zu bytes, caller gave %zu", which, bytes, out_bytes);
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemcpyAsync(out, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return SAIL_OK;
+}
+int sail_read_accum(sail_ctx* ctx, float* rgb, size_t out_bytes) { return sail_read_aov(ctx, SAIL_AOV_COLOR, rgb, out_bytes); }
+
+int sail_write_accum(sail_ctx* ctx, const float* rgb, size_t in_bytes) {
+    if (!ctx || !rgb) return SAIL_ERR_INVALID;
+    size_t bytes = npix(ctx) * 12;
+    if (in_bytes != bytes) return setErr(ctx, SAIL_ERR_INVALID, "accumulation buffer is %zu bytes, caller gave %zu", bytes, in_bytes);
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemcpyAsync(ctx->accum, rgb, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return SAIL_OK;
+}
+
+int sail_scale_accum(sail_ctx* ctx, float s) {
+    if (!ctx || !ctx->accum) return SAIL_ERR_INVALID;
+    CU(cudaSetDevice(ctx->device));
+    size_t n = npix(ctx) * 3;
+    sail_scale_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->accum, n, s);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return SAIL_OK;
+}
+
+int sail_present(sail_ctx* ctx, float* rgba_f32, uint8_t* rgba8) {
+    if (!ctx || !ctx->accum) return SAIL_ERR_INVALID;
+    CU(cudaSetDevice(ctx->device));
+    size_t n = npix(ctx);
+    if (rgba_f32 && !ctx->presentF32) CU(cudaMalloc(&ctx->presentF32, n * 4 * sizeof(float)));
+    if (rgba8 && !ctx->presentU8) CU(cudaMalloc(&ctx->presentU8, n * 4));
+    PresentParams P;
+    P.W = ctx->W; P.H = ctx->H;
+    P.filter_id = ctx->cfg.filter_id;
+    P.gamma_c = ctx->cfg.filter_gamma_c;
+    P.radius[0] = ctx->cfg.filter_radius[0]; P.radius[1] = ctx->cfg.filter_radius[1];
+    memcpy(P.weights, ctx->cfg.filter_weights, sizeof(P.weights));
+    P.color = ctx->accum; P.normal = ctx->normal; P.position = ctx->position;
+    P.out_f32 = rgba_f32 ? ctx->presentF32 : nullptr;
+    P.out_u8 = rgba8 ? ctx->presentU8 : nullptr;
+    dim3 grid((ctx->W + 31) / 32, (ctx->H + 7) / 8);
+    sail_present_kernel<<<grid, 256, 0, ctx->stream>>>(P);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    if (rgba_f32) CU(cudaMemcpyAsync(rgba_f32, ctx->presentF32, n * 4 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    if (rgba8) CU(cudaMemcpyAsync(rgba8, ctx->presentU8, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return SAIL_OK;
+}
+
+int sail_intersect_rays(sail_ctx* ctx, const float* rays, int32_t count, int32_t* hit_id, float* t, float* normal, int32_t* mat_category) {
+    if (!ctx || !rays || count < 0) return SAIL_ERR_INVALID;
+    if (!ctx->sceneLoaded) return setErr(ctx, SAIL_ERR_STATE, "sail_intersect_rays before sail_upload_scene");
+    if (count == 0) return SAIL_OK;
+    CU(cudaSetDevice(ctx->device));
+    float *dR = nullptr, *dT = nullptr, *dN = nullptr;
+    int *dI = nullptr, *dM = nullptr;
+    size_t c = (size_t)count;
+    CU(cudaMalloc(&dR, c * 6 * sizeof(float)));
+    CU(cudaMalloc(&dT, c * sizeof(float)));
+    CU(cudaMalloc(&dN, c * 3 * sizeof(float)));
+    CU(cudaMalloc(&dI, c * sizeof(int)));
+    CU(cudaMalloc(&dM, c * sizeof(int)));
+    CU(cudaMemcpyAsync(dR, rays, c * 6 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    sail_intersect_kernel<<<(unsigned)((c + SAIL_CTA_THREADS - 1) / SAIL_CTA_THREADS), SAIL_CTA_THREADS, 0, ctx->stream>>>(ctx->dScene, dR, count, dI, dT, dN, dM);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    if (hit_id) CU(cudaMemcpyAsync(hit_id, dI, c * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    if (t) CU(cudaMemcpyAsync(t, dT, c * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    if (normal) CU(cudaMemcpyAsync(normal, dN, c * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    if (mat_category) CU(cudaMemcpyAsync(mat_category, dM, c * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    cudaFree(dR); cudaFree(dT); cudaFree(dN); cudaFree(dI); cudaFree(dM);
+    return SAIL_OK;
+}
+
+int sail_trace_dump(sail_ctx* ctx, const sail_frame* frame, int32_t* hit_id, float* t, float* rays, float* radiance) {
+    if (!ctx || !frame) return SAIL_ERR_INVALID;
+    if (!ctx->sceneLoaded) return setErr(ctx, SAIL_ERR_STATE, "sail_trace_dump before sail_upload_scene");
+    CU(cudaSetDevice(ctx->device));
+    size_t n = npix(ctx), B = (size_t)ctx->cfg.max_bounces;
+    if (B == 0) return setErr(ctx, SAIL_ERR_INVALID, "max_bounces is 0");
+    SailDumpLaunch L;
+    L.W = ctx->W; L.H = ctx->H; L.maxBounces = (int)B;
+    L.rcpW = dm_rcp((float)ctx->W); L.rcpH = dm_rcp((float)ctx->H);
+    L.scene = ctx->dScene;
+    L.hitId = nullptr; L.t = nullptr; L.rays = nullptr; L.radiance = nullptr;
+    lowerFrame(*frame, L.frame);
+    if (hit_id) CU(cudaMalloc(&L.hitId, n * B * sizeof(int)));
+    if (t) CU(cudaMalloc(&L.t, n * B * sizeof(float)));
+    if (rays) CU(cudaMalloc(&L.rays, n * B * 6 * sizeof(float)));
+    if (radiance) CU(cudaMalloc(&L.radiance, n * 3 * sizeof(float)));
+    dim3 grid((ctx->W + SAIL_TILE_W - 1) / SAIL_TILE_W, (ctx->H + SAIL_TILE_H - 1) / SAIL_TILE_H);
+    sail_trace_dump_kernel<<<grid, SAIL_CTA_THREADS, 0, ctx->stream>>>(L);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    if (hit_id) CU(cudaMemcpyAsync(hit_id, L.hitId, n * B * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    if (t) CU(cudaMemcpyAsync(t, L.t, n * B * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    if (rays) CU(cudaMemcpyAsync(rays, L.rays, n * B * 6 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    if (radiance) CU(cudaMemcpyAsync(radiance, L.radiance, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    cudaFree(L.hitId); cudaFree(L.t); cudaFree(L.rays); cudaFree(L.radiance);
+    return SAIL_OK;
+}
+
+int sail_eval_math(sail_ctx* ctx, int32_t which, const float* a, const float* b, float* out, int32_t count) {
+    if (!ctx || !a || !out || count < 0 || which < 0 || which > 11) return SAIL_ERR_INVALID;
+    if (count == 0) return SAIL_OK;
+    CU(cudaSetDevice(ctx->device));
+    float *dA = nullptr, *dB = nullptr, *dO = nullptr;
+    size_t bytes = (size_t)count * sizeof(float);
+    CU(cudaMalloc(&dA, bytes));
+    CU(cudaMalloc(&dO, bytes));
+    CU(cudaMemcpyAsync(dA, a, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    if (b) {
+        CU(cudaMalloc(&dB, bytes));
+        CU(cudaMemcpyAsync(dB, b, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    sail_eval_math_kernel<<<(count + 255) / 256, 256, 0, ctx->stream>>>(which, dA, dB, dO, count);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(out, dO, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    cudaFree(dA); cudaFree(dB); cudaFree(dO);
+    return SAIL_OK;
+}
+
+uint64_t sail_launch_count(const sail_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int sail_last_render_ms(sail_ctx* ctx, float* ms) {
+    if (!ctx || !ms) return SAIL_ERR_INVALID;
+    if (!ctx->timed) return setErr(ctx, SAIL_ERR_STATE, "no render has been issued yet");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaEventSynchronize(ctx->evStop));
+    CU(cudaEventElapsedTime(ms, ctx->evStart, ctx->evStop));
+    return SAIL_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,219 @@
+// sail_mega.cuh -- the megakernel: one thread carries one pixel through ray generation, the bounce
+// loop, next-event estimation and progressive accumulation, for up to SAIL_MAX_FRAMES_PER_CALL
+// consecutive frames per launch.
+//
+// Replaces the full-screen-quad draw of the trace program
+// (/root/reference/src/core/webgl.js:82-83 -> src/shader/main/vstrace.glsl:4-7, main/fstrace.glsl:6-17)
+// and the ping-pong colour accumulator (webgl.js:65-73,88-92).  B200 mapping:
+//   * CTA = 128 threads = a 16x8 pixel tile, each warp an 8x4 sub-tile, so neighbouring lanes hit the
+//     same objects / materials on the first bounces and the accumulator rows of a warp are contiguous;
+//   * the packed scene block (sail_scene.h) is staged once per CTA into shared memory and read with
+//     warp-uniform addresses in the object scan (broadcast, no bank conflicts);
+//   * frame uniforms travel as a __grid_constant__ kernel parameter (constant bank, broadcast);
+//   * the running mean of a pixel lives in registers across the frames of a launch: HBM traffic is one
+//     12 B read + one 12 B write per pixel per launch instead of per frame (the reference re-reads and
+//     re-writes its accumulation texture every frame).
+#ifndef SAIL_MEGA_CUH
+#define SAIL_MEGA_CUH
+#include "sail_shade.cuh"
+
+#define SAIL_MAX_BATCH 32
+#define SAIL_TILE_W 16
+#define SAIL_TILE_H 8
+#define SAIL_CTA_THREADS 128
+
+// Per-frame constants derived on the host from (matrix, eye): the four corner rays of vstrace.glsl:4-7
+// and the edge differences used by the rasteriser-style interpolation (DESIGN.md "Primary rays").
+struct SailFrameDev {
+    float d0[3], e20[3], e10[3];  // lower-left triangle: d0 + a*(d2-d0) + b*(d1-d0)
+    float d3[3], e13[3], e23[3];  // upper-right triangle: d3 + (1-a)*(d1-d3) + (1-b)*(d2-d3)
+    float eye[3];
+    float textureWeight, timeSinceStart;
+    float pad;
+};
+
+struct SailLaunch {
+    int W, H;
+    int y0, y1;          // rows rendered by this launch
+    int maxBounces;
+    int nframes;
+    int accumMode;       // SAIL_ACCUM_*
+    int writeAov;
+    float rcpW, rcpH;
+    float* accum;        // W*H*3
+    float* normal;       // W*H*3
+    float* position;     // W*H*3
+    int* hitId;          // W*H
+    float* depth;        // W*H
+    const SailSceneBlock* scene;
+    SailFrameDev frames[SAIL_MAX_BATCH];
+};
+
+// Stage the used part of the scene block into shared memory (16-byte copies).
+SD void stageScene(SailSceneBlock& dst, const SailSceneBlock* __restrict__ src) {
+    const int n = src->n, ln = src->ln;
+    const uint4* s4 = reinterpret_cast<const uint4*>(src);
+    uint4* d4 = reinterpret_cast<uint4*>(&dst);
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const int shapeOff = (int)(offsetof(SailSceneBlock, shape) / 16), surfOff = (int)(offsetof(SailSceneBlock, surf) / 16);
+    const int lightOff = (int)(offsetof(SailSceneBlock, light) / 16);
+    if (tid == 0) d4[0] = s4[0];
+    for (int i = tid; i < n * (int)(sizeof(SailShape) / 16); i += nt) d4[shapeOff + i] = s4[shapeOff + i];
+    for (int i = tid; i < n * (int)(sizeof(SailSurface) / 16); i += nt) d4[surfOff + i] = s4[surfOff + i];
+    for (int i = tid; i < (ln + 1) * (int)(sizeof(SailLight) / 16); i += nt) d4[lightOff + i] = s4[lightOff + i];
+    __syncthreads();
+}
+
+// Interpolated primary ray direction at the centre of pixel (x, y): not renormalised.
+SD V3 primaryDir(const SailFrameDev& f, float a, float b) {
+    if (a + b < 1.0f) return ld3(f.d0) + a * ld3(f.e20) + b * ld3(f.e10);
+    return ld3(f.d3) + (1.0f - a) * ld3(f.e13) + (1.0f - b) * ld3(f.e23);
+}
+SD float nanToZero(float v) { return (v == v) ? v : 0.0f; }
+
+__global__ void __launch_bounds__(SAIL_CTA_THREADS) sail_trace_megakernel(const __grid_constant__ SailLaunch L) {
+    __shared__ SailSceneBlock sc;
+    stageScene(sc, L.scene);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int x = blockIdx.x * SAIL_TILE_W + (warp & 1) * 8 + (lane & 7);
+    const int y = L.y0 + blockIdx.y * SAIL_TILE_H + (warp >> 1) * 4 + (lane >> 3);
+    if (x >= L.W || y >= L.y1) return;
+
+    const size_t pix = (size_t)y * L.W + x;
+    // gl_FragCoord of the full-screen quad at z = 0 (depth 0.5)
+    const float fx = (float)x + 0.5f, fy = (float)y + 0.5f, fz = 0.5f;
+    const float a = fx * L.rcpW, b = fy * L.rcpH;
+
+    V3 c = mk3(L.accum[3 * pix], L.accum[3 * pix + 1], L.accum[3 * pix + 2]);
+    FirstHit first;
+    for (int k = 0; k < L.nframes; k++) {
+        const SailFrameDev& f = L.frames[k];
+        Ray ray;
+        ray.o = ld3(f.eye);
+        ray.d = primaryDir(f, a, b);
+        V3 e = tracePath(sc, ray, L.maxBounces, fx, fy, fz, f.timeSinceStart, first);
+        e = mk3(nanToZero(e.x), nanToZero(e.y), nanToZero(e.z));
+        if (L.accumMode == 0) c = mix3(e, c, f.textureWeight);  // fstrace.glsl:14
+        else c = c + e;
+    }
+    L.accum[3 * pix] = c.x;
+    L.accum[3 * pix + 1] = c.y;
+    L.accum[3 * pix + 2] = c.z;
+    if (L.writeAov) {
+        // fstrace.glsl:15-16: out_normal = n/2+0.5, out_position = normalize(p)
+        V3 on = vdivs(first.n, 2.0f) + 0.5f;
+        V3 op = normalize3(first.p);
+        L.normal[3 * pix] = on.x; L.normal[3 * pix + 1] = on.y; L.normal[3 * pix + 2] = on.z;
+        L.position[3 * pix] = op.x; L.position[3 * pix + 1] = op.y; L.position[3 * pix + 2] = op.z;
+        L.hitId[pix] = first.id;
+        L.depth[pix] = first.t;
+    }
+}
+
+// ---- diagnostics ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(SAIL_CTA_THREADS) sail_intersect_kernel(const SailSceneBlock* __restrict__ scene,
+                                                                          const float* __restrict__ rays, int count, int* hitId,
+                                                                          float* t, float* normal, int* matCategory) {
+    __shared__ SailSceneBlock sc;
+    stageScene(sc, scene);
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    Ray r;
+    r.o = ld3(rays + 6 * i);
+    r.d = ld3(rays + 6 * i + 3);
+    Hit h;
+    h.n = splat3(0.0f);
+    h.matCategory = 0;
+    bool ok = intersectObjects(sc, r, h);
+    if (hitId) hitId[i] = h.index;
+    if (t) t[i] = h.d;
+    if (normal) { normal[3 * i] = ok ? h.n.x : 0.0f; normal[3 * i + 1] = ok ? h.n.y : 0.0f; normal[3 * i + 2] = ok ? h.n.z : 0.0f; }
+    if (matCategory) matCategory[i] = ok ? h.matCategory : 0;
+}
+
+struct SailDumpLaunch {
+    int W, H, maxBounces;
+    float rcpW, rcpH;
+    const SailSceneBlock* scene;
+    int* hitId;
+    float* t;
+    float* rays;
+    float* radiance;
+    SailFrameDev frame;
+};
+// trace() with per-bounce records; the loop body is the one of tracePath().
+__global__ void __launch_bounds__(SAIL_CTA_THREADS) sail_trace_dump_kernel(const __grid_constant__ SailDumpLaunch L) {
+    __shared__ SailSceneBlock sc;
+    stageScene(sc, L.scene);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int x = blockIdx.x * SAIL_TILE_W + (warp & 1) * 8 + (lane & 7);
+    const int y = blockIdx.y * SAIL_TILE_H + (warp >> 1) * 4 + (lane >> 3);
+    if (x >= L.W || y >= L.H) return;
+    const size_t pix = (size_t)y * L.W + x;
+    const float fx = (float)x + 0.5f, fy = (float)y + 0.5f, fz = 0.5f;
+    Ray ray;
+    ray.o = ld3(L.frame.eye);
+    ray.d = primaryDir(L.frame, fx * L.rcpW, fy * L.rcpH);
+    const int B = L.maxBounces;
+    for (int k = 0; k < B; k++) {
+        if (L.hitId) L.hitId[pix * B + k] = -2;
+        if (L.t) L.t[pix * B + k] = 0.0f;
+        if (L.rays) for (int j = 0; j < 6; j++) L.rays[(pix * B + k) * 6 + j] = 0.0f;
+    }
+    V3 fpdf = splat3(1.0f), e = splat3(0.0f);
+    int deepth = 0;
+    while (deepth++ < B) {
+        Hit h;
+        bool ok = intersectObjects(sc, ray, h);
+        size_t o = pix * B + (deepth - 1);
+        if (L.hitId) L.hitId[o] = h.index;
+        if (L.t) L.t[o] = h.d;
+        if (L.rays) {
+            float* r = L.rays + o * 6;
+            r[0] = ray.o.x; r[1] = ray.o.y; r[2] = ray.o.z; r[3] = ray.d.x; r[4] = ray.d.y; r[5] = ray.d.z;
+        }
+        if (!ok) break;
+        float seed = L.frame.timeSinceStart + (float)deepth;
+        V2 u = random2(fx, fy, fz, seed);
+        V3 wi, _fpdf;
+        e = e + shade(sc, h, u, -ray.d, wi, _fpdf) * fpdf;
+        fpdf = fpdf * _fpdf;
+        float outdot = dot3(h.n, wi);
+        ray.o = h.p + h.n * (outdot > SAIL_EPSILON ? 0.0001f : -0.0001f);
+        ray.d = wi;
+    }
+    if (L.radiance) {
+        L.radiance[3 * pix] = nanToZero(e.x);
+        L.radiance[3 * pix + 1] = nanToZero(e.y);
+        L.radiance[3 * pix + 2] = nanToZero(e.z);
+    }
+}
+
+__global__ void sail_eval_math_kernel(int which, const float* a, const float* b, float* out, int count) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    float x = a[i], y = b ? b[i] : 0.0f, r = 0.0f;
+    switch (which) {
+        case 0: r = dm_sin(x); break;
+        case 1: r = dm_cos(x); break;
+        case 2: r = dm_tan(x); break;
+        case 3: r = dm_atan(x); break;
+        case 4: r = dm_acos(x); break;
+        case 5: r = dm_asin(x); break;
+        case 6: r = dm_exp(x); break;
+        case 7: r = dm_log(x); break;
+        case 8: r = dm_atan2(x, y); break;
+        case 9: r = dm_pow(x, y); break;
+        case 10: r = dm_div(x, y); break;
+        case 11: r = dm_sqrt(x); break;
+    }
+    out[i] = r;
+}
+
+__global__ void sail_scale_kernel(float* p, size_t count, float s) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) p[i] = p[i] * s;
+}
+
+#endif

@@ -1,0 +1,196 @@
+// sail_present.cuh -- the display pass: RenderShader's full-screen quad
+// (/root/reference/src/core/renderer.js:63, src/shader/main/vsrender.glsl:4-7, main/fsrender.glsl:4-6)
+// with the filter plugins of src/shader/filter/: color.glsl, gamma.glsl, tonemapping.glsl, normal.glsl,
+// position.glsl, window.glsl (box / gaussian / mitchell / sinc / triangle share it, the 16 weights come
+// from the host) and wavelet.glsl.
+//
+// The canvas becomes a headless RGBA buffer.  colorMap / normalMap / positionMap are the FP32 device
+// buffers of the trace pass, sampled like the reference's LINEAR + REPEAT textures
+// (src/core/webgl.js:153-156) with 8-bit bilinear weights; 512 is generalised to W / H and 1280 to
+// 2.5 W / 2.5 H.
+#ifndef SAIL_PRESENT_CUH
+#define SAIL_PRESENT_CUH
+#include "sail_vec.cuh"
+
+struct V4 { float x, y, z, w; };
+SD V4 mk4(float x, float y, float z, float w) { V4 v; v.x = x; v.y = y; v.z = z; v.w = w; return v; }
+SD V4 operator+(V4 a, V4 b) { return mk4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
+SD V4 operator-(V4 a, V4 b) { return mk4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w); }
+SD V4 operator*(V4 a, float s) { return mk4(a.x * s, a.y * s, a.z * s, a.w * s); }
+SD float dot4(V4 a, V4 b) { return a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w; }
+
+struct PresentParams {
+    int W, H;
+    int filter_id;
+    float gamma_c;
+    float radius[2];
+    float weights[16];
+    const float* color;
+    const float* normal;
+    const float* position;
+    float* out_f32;        // W*H*4 or NULL
+    unsigned char* out_u8; // W*H*4 or NULL
+};
+
+SD int wrapIndex(int i, int n) {
+    int m = i % n;
+    return m < 0 ? m + n : m;
+}
+SD V4 texelRGB(const float* img, int W, int H, int x, int y) {
+    const float* p = img + 3 * ((size_t)wrapIndex(y, H) * W + wrapIndex(x, W));
+    return mk4(__ldg(p), __ldg(p + 1), __ldg(p + 2), 1.0f);
+}
+SD void linearCoord(float u, int size, int& i0, float& t) {
+    float f = u * (float)size - 0.5f;
+    if (!(f == f) || !(f > -1e9f && f < 1e9f)) { i0 = 0; t = 0.0f; return; }
+    float fl = dm_floor(f);
+    i0 = (int)fl;
+    t = dm_floor((f - fl) * 256.0f + 0.5f) * (1.0f / 256.0f);
+}
+SD V4 textureLinear(const float* img, int W, int H, float u, float v) {
+    int x0, y0;
+    float tx, ty;
+    linearCoord(u, W, x0, tx);
+    linearCoord(v, H, y0, ty);
+    V4 c00 = texelRGB(img, W, H, x0, y0), c10 = texelRGB(img, W, H, x0 + 1, y0);
+    V4 c01 = texelRGB(img, W, H, x0, y0 + 1), c11 = texelRGB(img, W, H, x0 + 1, y0 + 1);
+    V4 a = c00 * (1.0f - tx) + c10 * tx;
+    V4 b = c01 * (1.0f - tx) + c11 * tx;
+    return a * (1.0f - ty) + b * ty;
+}
+
+// window.glsl:1-8
+SD V3 windowSampler(const PresentParams& P, float cx, float cy, int& count) {
+    if (cx < 0.0f || cx > 1.0f || cy < 0.0f || cy > 1.0f) return splat3(0.0f);
+    count++;
+    V4 c = textureLinear(P.color, P.W, P.H, cx, cy);
+    return mk3(c.x, c.y, c.z);
+}
+// window.glsl:26-44 (table lookup i*j+j as written)
+SD V4 filterWindow(const PresentParams& P, float tx, float ty) {
+    V3 color = splat3(0.0f);
+    float weightSum = 0.0f;
+    const float rW = dm_rcp((float)P.W), rH = dm_rcp((float)P.H);
+    for (int i = 0; i < 4; i++) {
+        for (int j = 0; j < 4; j++) {
+            float oi = fdiv(((float)j + 0.5f) * P.radius[0], 4.0f);
+            float oj = fdiv(((float)i + 0.5f) * P.radius[1], 4.0f);
+            // window.glsl:10-24: x = vec2(i/W, 0), y = vec2(0, j/H)
+            float xx = oi * rW, yy = oj * rH;
+            int count = 0;
+            V3 tmp = splat3(0.0f);
+            tmp = tmp + windowSampler(P, tx + xx + 0.0f, ty + 0.0f + yy, count);
+            tmp = tmp + windowSampler(P, tx + xx - 0.0f, ty + 0.0f - yy, count);
+            tmp = tmp + windowSampler(P, tx - xx + 0.0f, ty - 0.0f + yy, count);
+            tmp = tmp + windowSampler(P, tx - xx - 0.0f, ty - 0.0f - yy, count);
+            float weight = P.weights[i * j + j];
+            weightSum += weight * (float)count;
+            color = color + tmp * weight;
+        }
+    }
+    V3 c = vdivs(color, weightSum);
+    return mk4(c.x, c.y, c.z, 1.0f);
+}
+// wavelet.glsl:1-54
+SD V4 filterWavelet(const PresentParams& P, float tx, float ty) {
+    V4 color = mk4(0.0f, 0.0f, 0.0f, 0.0f);
+    float weightSum = 0.0f;
+    V4 cval = textureLinear(P.color, P.W, P.H, tx, ty);
+    V4 pval = textureLinear(P.position, P.W, P.H, tx, ty);
+    const float h[5] = {0.375f, 0.25f, 0.0625f, 0.0625f, 0.25f};
+    const float Rx = P.radius[0], Ry = P.radius[1];
+    const float Wf = (float)P.W, Hf = (float)P.H;
+    for (int n = 0; n < 3; n++) {
+        float stepwidth = (float)(1 << n) - 1.0f;
+        int step = toInt(stepwidth) + 1;
+        int count = 0;
+        for (int i = 0; i < 5; i++) {
+            for (int j = 0; j < 5; j++, count++) {
+                int delt = abs(count - 12);
+                float _h = 0.0f;
+                if (delt % step == 0) _h = h[(delt / step) % 5];
+                if (_h == 0.0f) continue;
+                float u = tx - fdiv(Rx, Wf) + fdiv(((float)j + 0.5f) * Rx, 2.5f * Wf);
+                float v = ty - fdiv(Ry, Hf) + fdiv(((float)i + 0.5f) * Ry, 2.5f * Hf);
+                // W(), wavelet.glsl:5-20: the "normal" weight reuses the colour difference as written
+                V4 ctmp = textureLinear(P.color, P.W, P.H, u, v);
+                V4 t = cval - ctmp;
+                float dist2 = dot4(t, t);
+                float c_w = fmin2(dm_exp(fdiv(-dist2, 4.0f)), 1.0f);
+                dist2 = fmax2(fdiv(dot4(t, t), stepwidth * stepwidth), 0.0f);
+                float n_w = fmin2(dm_exp(fdiv(-dist2, 128.0f)), 1.0f);
+                V4 ptmp = textureLinear(P.position, P.W, P.H, u, v);
+                t = pval - ptmp;
+                dist2 = dot4(t, t);
+                float p_w = fmin2(dm_exp(fdiv(-dist2, 1.0f)), 1.0f);
+                float weight = c_w * n_w * p_w * _h;
+                ctmp = ctmp * weight;
+                weightSum += weight;
+                color = color + ctmp;
+            }
+        }
+    }
+    float r = dm_rcp(weightSum);
+    return mk4(color.x * r, color.y * r, color.z * r, color.w * r);
+}
+// tonemapping.glsl:1-4
+SD float tonemap1(float c) {
+    float x = fmax2(0.0f, c - 0.004f);
+    return fdiv(x * (6.2f * x + 0.5f), x * (6.2f * x + 1.7f) + 0.06f);
+}
+
+__global__ void __launch_bounds__(256) sail_present_kernel(const __grid_constant__ PresentParams P) {
+    int x = blockIdx.x * 32 + (threadIdx.x & 31);
+    int y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= P.W || y >= P.H) return;
+    // vsrender.glsl:5: texCoord = vertex.xy*0.5+0.5 interpolated to the pixel centre
+    float tx = fdiv((float)x + 0.5f, (float)P.W), ty = fdiv((float)y + 0.5f, (float)P.H);
+    V4 v;
+    switch (P.filter_id) {
+        case 0: {  // color.glsl
+            V4 c = textureLinear(P.color, P.W, P.H, tx, ty);
+            v = mk4(c.x, c.y, c.z, 1.0f);
+            break;
+        }
+        case 1: {  // gamma.glsl
+            V4 c = textureLinear(P.color, P.W, P.H, tx, ty);
+            float g = dm_rcp(P.gamma_c);
+            v = mk4(dm_pow(c.x, g), dm_pow(c.y, g), dm_pow(c.z, g), 1.0f);
+            break;
+        }
+        case 10: {  // tonemapping.glsl
+            V4 c = textureLinear(P.color, P.W, P.H, tx, ty);
+            v = mk4(tonemap1(c.x), tonemap1(c.y), tonemap1(c.z), 1.0f);
+            break;
+        }
+        case 7: {  // normal.glsl
+            V4 c = textureLinear(P.normal, P.W, P.H, tx, ty);
+            v = mk4(c.x, c.y, c.z, 1.0f);
+            break;
+        }
+        case 8: {  // position.glsl
+            V4 c = textureLinear(P.position, P.W, P.H, tx, ty);
+            v = mk4(c.x, c.y, c.z, 1.0f);
+            break;
+        }
+        case 9: v = filterWavelet(P, tx, ty); break;
+        case 2: case 3: case 4: case 5: case 6: v = filterWindow(P, tx, ty); break;
+        default: v = mk4(0.0f, 0.0f, 0.0f, 0.0f);
+    }
+    size_t i = (size_t)y * P.W + x;
+    const float comp[4] = {v.x, v.y, v.z, v.w};
+    if (P.out_f32) {
+        reinterpret_cast<float4*>(P.out_f32)[i] = make_float4(v.x, v.y, v.z, v.w);
+    }
+    if (P.out_u8) {
+        unsigned char b[4];
+        for (int k = 0; k < 4; k++) {
+            float f = comp[k];
+            f = (f == f) ? dm_min(dm_max(f, 0.0f), 1.0f) : 0.0f;  // canvas: clamp, NaN -> 0
+            b[k] = (unsigned char)dm_floor(f * 255.0f + 0.5f);
+        }
+        reinterpret_cast<uchar4*>(P.out_u8)[i] = make_uchar4(b[0], b[1], b[2], b[3]);
+    }
+}
+
+#endif

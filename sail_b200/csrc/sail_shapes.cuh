@@ -1,0 +1,445 @@
+// sail_shapes.cuh -- analytic ray/primitive intersection for the nine Sail shapes, split B200-first
+// into (1) a nearest-hit *scan* that computes only the hit distance of every object (what
+// `Intersect.d` would be) and (2) a *hit record* evaluated once, for the winning object only.
+//
+// The reference evaluates the whole hit record -- uv, dpdu/dpdv, normal, surface colour, frame
+// transforms -- for every object a ray touches and throws all but the nearest away
+// (/root/reference/src/shader/shape/shader.shape.js:28-51).  Because the winner is chosen on `d` alone
+// (strict `<`, ascending index, shader.shape.js:36) the two-phase form returns identical values.
+// Shadow rays (src/shader/light/shader.light.js:24-31) only ever read `d`, so they run the scan only.
+//
+// Divisions by ray.dir share one reciprocal per ray (GLSL `/` is a*rcp(b), DESIGN.md "Arithmetic").
+#ifndef SAIL_SHAPES_CUH
+#define SAIL_SHAPES_CUH
+#include "sail_scene.h"
+#include "sail_vec.cuh"
+
+#define SAIL_MAX_DISTANCE 1e5f
+#define SAIL_EPSILON 1e-5f
+#define SAIL_ONEMINUSEPSILON 0.9999f
+#define SAIL_INF 1e5f
+#define SAIL_PI 3.141592653589793f
+#define SAIL_TWO_PI (2.0f * SAIL_PI)
+#define SAIL_INVPI 0.3183098861837907f
+#define SAIL_PIOVER2 1.570796326794896f
+#define SAIL_PIOVER4 0.785398163397448f
+// phi / (2.0*PI) and theta / PI multiply by the correctly rounded reciprocal of the FP32 constant.
+#define SAIL_RCP_TWO_PI (1.0f / SAIL_TWO_PI)
+#define SAIL_RCP_PI (1.0f / SAIL_PI)
+
+struct Ray {
+    V3 o, d;
+};
+
+// The winning hit (const/struct.glsl:1-13 minus the dead dpdv / seed fields).
+struct Hit {
+    float d;
+    int index;       // object id, -1 on a miss (the HIT_ID AOV)
+    V3 p, n, dpdu;   // world space; n already flipped toward the ray (shader.shape.js:39-40)
+    V3 sc, emission;
+    int matCategory;
+    bool into;
+};
+
+// ---- util/utility.glsl:37-51 -----------------------------------------------------------------
+SD bool quadratic(float A, float B, float C, float& t0, float& t1) {
+    float discrim = B * B - 4.0f * A * C;
+    if (discrim < 0.0f) return false;
+    float rootDiscrim = dm_sqrt(discrim);
+    float q;
+    if (B < 0.0f) q = -0.5f * (B - rootDiscrim);
+    else q = -0.5f * (B + rootDiscrim);
+    t0 = fdiv(q, A);
+    t1 = fdiv(C, q);
+    if (t0 > t1) { float tmp = t0; t0 = t1; t1 = tmp; }
+    return true;
+}
+
+// ---- shape/boundbox.glsl:6-17 and the slab core of cube.glsl:65-74 / cornellbox.glsl:67-76 ----
+// `first`/`second` are box.min/box.max in the order the shader's min()/max() sees them.
+SD void slab(V3 first, V3 second, V3 o, V3 rd, float& tNear, float& tFar) {
+    V3 tMin = (first - o) * rd;
+    V3 tMax = (second - o) * rd;
+    V3 t1 = mk3(fmin2(tMin.x, tMax.x), fmin2(tMin.y, tMax.y), fmin2(tMin.z, tMax.z));
+    V3 t2 = mk3(fmax2(tMin.x, tMax.x), fmax2(tMin.y, tMax.y), fmax2(tMin.z, tMax.z));
+    tNear = fmax2(fmax2(t1.x, t1.y), t1.z);
+    tFar = fmin2(fmin2(t2.x, t2.y), t2.z);
+}
+// testBoundbox with Boundbox(lo, hi): the constructor order is (max, min), so box.min = hi.
+SD bool boundsHit(const SailShape& s, V3 o, V3 rd) {
+    float tNear, tFar;
+    slab(ld3(s.hi), ld3(s.lo), o, rd, tNear, tFar);
+    if (tNear < 0.0f && tFar < 0.0f) return false;
+    return tNear < tFar;
+}
+
+// Quadric tail shared by cone / cylinder / hyperboloid / paraboloid (e.g. cone.glsl:62-79):
+// choose the root, retry with the far root when the near one is outside [zLo, zHi].
+SD float quadricRoot(float a, float b, float c, V3 ol, V3 dl, float zLo, float zHi) {
+    float t1, t2;
+    if (!quadratic(a, b, c, t1, t2)) return SAIL_MAX_DISTANCE;
+    if (t2 < -SAIL_EPSILON) return SAIL_MAX_DISTANCE;
+    float t = t1;
+    if (t1 < SAIL_EPSILON) t = t2;
+    float hz = ol.z + t * dl.z;
+    if (hz < zLo || hz > zHi) {
+        if (t == t2) return SAIL_MAX_DISTANCE;
+        t = t2;
+        hz = ol.z + t * dl.z;
+        if (hz < zLo || hz > zHi) return SAIL_MAX_DISTANCE;
+    }
+    if (t >= SAIL_MAX_DISTANCE) return SAIL_MAX_DISTANCE;
+    return t;
+}
+
+// Phase 1: the value intersectX() would leave in `result.d` (MAX_DISTANCE = no hit).
+SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd) {
+    const float* q = s.q;
+    switch (s.category) {
+        case SAIL_CUBE: {  // cube.glsl:65-79
+            float tNear, tFar;
+            slab(ld3(s.lo), ld3(s.hi), ray.o, rd, tNear, tFar);
+            float t = -1.0f;
+            if (tNear > SAIL_EPSILON && tNear < tFar) t = tNear;
+            else if (tNear < tFar) t = tFar;
+            return (t > SAIL_EPSILON) ? t : SAIL_MAX_DISTANCE;
+        }
+        case SAIL_CORNELLBOX: {  // cornellbox.glsl:67-81: always the far slab hit
+            float tNear, tFar;
+            slab(ld3(s.lo), ld3(s.hi), ray.o, rd, tNear, tFar);
+            float t = -1.0f;
+            if (tNear < tFar) t = tFar;
+            return (t > SAIL_EPSILON) ? t : SAIL_MAX_DISTANCE;
+        }
+        case SAIL_SPHERE: {  // sphere.glsl:10-16,45-62
+            if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
+            V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_SPH_C));
+            float a = dot3(dl, dl);
+            float b = 2.0f * dot3(ol, dl);
+            float c = dot3(ol, ol) - q[SQ_SPH_RR];
+            float t1, t2;
+            if (!quadratic(a, b, c, t1, t2)) return SAIL_MAX_DISTANCE;
+            if (t2 < SAIL_EPSILON) return SAIL_MAX_DISTANCE;
+            float t = t1;
+            if (t1 < SAIL_EPSILON) t = t2;
+            if (t >= SAIL_MAX_DISTANCE) return SAIL_MAX_DISTANCE;
+            return t;
+        }
+        case SAIL_RECTANGLE: {  // rectangle.glsl:32-55
+            V3 nn = ld3(q + SQ_RECT_N), ss = ld3(q + SQ_RECT_SS), ts = ld3(q + SQ_RECT_TS);
+            V3 dl = worldToLocal(ray.d, nn, ss, ts);
+            V3 ol = worldToLocal(ray.o - ld3(s.lo), nn, ss, ts);
+            if (dl.z == 0.0f) return SAIL_MAX_DISTANCE;
+            float t = fdiv(-ol.z, dl.z);
+            if (t < SAIL_EPSILON) return SAIL_MAX_DISTANCE;
+            float hx = ol.x + t * dl.x, hy = ol.y + t * dl.y;
+            if (hx > q[SQ_RECT_MAXX] || hy > q[SQ_RECT_MAXY] || hx < -SAIL_EPSILON || hy < -SAIL_EPSILON)
+                return SAIL_MAX_DISTANCE;
+            return t;
+        }
+        case SAIL_CONE: {  // cone.glsl:11-17,48-81
+            if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
+            V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_CONE_P));
+            float k = q[SQ_CONE_K], h = q[SQ_CONE_H];
+            float a = dl.x * dl.x + dl.y * dl.y - k * dl.z * dl.z;
+            float b = 2.0f * (dl.x * ol.x + dl.y * ol.y - k * dl.z * (ol.z - h));
+            float c = ol.x * ol.x + ol.y * ol.y - k * (ol.z - h) * (ol.z - h);
+            return quadricRoot(a, b, c, ol, dl, -SAIL_EPSILON, h);
+        }
+        case SAIL_CYLINDER: {  // cylinder.glsl:11-17,40-72
+            if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
+            V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_CYL_P));
+            float a = dl.x * dl.x + dl.y * dl.y;
+            float b = 2.0f * (dl.x * ol.x + dl.y * ol.y);
+            float c = ol.x * ol.x + ol.y * ol.y - q[SQ_CYL_RR];
+            return quadricRoot(a, b, c, ol, dl, -SAIL_EPSILON, q[SQ_CYL_H]);
+        }
+        case SAIL_DISK: {  // disk.glsl:36-53
+            V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_DISK_P));
+            if (dl.z == 0.0f) return SAIL_MAX_DISTANCE;
+            float t = fdiv(-ol.z, dl.z);
+            if (t <= 0.0f) return SAIL_MAX_DISTANCE;
+            float hx = ol.x + t * dl.x, hy = ol.y + t * dl.y;
+            float dist2 = hx * hx + hy * hy;
+            if (dist2 > q[SQ_DISK_RR] || dist2 < q[SQ_DISK_IRR]) return SAIL_MAX_DISTANCE;
+            if (t >= SAIL_MAX_DISTANCE) return SAIL_MAX_DISTANCE;
+            return t;
+        }
+        case SAIL_HYPERBOLOID: {  // hyperboloid.glsl:13-24,60-90
+            if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
+            V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_HYP_P));
+            float ah = q[SQ_HYP_AH], ch = q[SQ_HYP_CH];
+            float a = ah * dl.x * dl.x + ah * dl.y * dl.y - ch * dl.z * dl.z;
+            float b = 2.0f * (ah * dl.x * ol.x + ah * dl.y * ol.y - ch * dl.z * ol.z);
+            float c = ah * ol.x * ol.x + ah * ol.y * ol.y - ch * ol.z * ol.z - 1.0f;
+            return quadricRoot(a, b, c, ol, dl, q[SQ_HYP_ZMIN], q[SQ_HYP_ZMAX]);
+        }
+        case SAIL_PARABOLOID: {  // paraboloid.glsl:12-20,51-82
+            if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
+            V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_PAR_P));
+            float k = q[SQ_PAR_K];
+            float a = k * (dl.x * dl.x + dl.y * dl.y);
+            float b = 2.0f * k * (dl.x * ol.x + dl.y * ol.y) - dl.z;
+            float c = k * (ol.x * ol.x + ol.y * ol.y) - ol.z;
+            return quadricRoot(a, b, c, ol, dl, q[SQ_PAR_ZMIN], q[SQ_PAR_ZMAX]);
+        }
+    }
+    return SAIL_MAX_DISTANCE;
+}
+
+// shader.shape.js:28-37: nearest object by strict `<` in ascending index.  Returns the object index
+// or -1; `best` receives ins.d.
+SD int nearestObject(const SailSceneBlock& sc, const Ray& ray, float& best) {
+    V3 rd = mk3(dm_rcp(ray.d.x), dm_rcp(ray.d.y), dm_rcp(ray.d.z));
+    best = SAIL_MAX_DISTANCE;
+    int id = -1;
+    const int n = sc.n;
+    for (int i = 0; i < n; i++) {
+        float t = shapeDistance(sc.shape[i], ray, rd);
+        if (t < best) { best = t; id = i; }
+    }
+    return id;
+}
+
+// ---- procedural textures (texture/shader.texture.js:22-29) -------------------------------------
+SD bool textureNeedsUV(int texCategory) {
+    return texCategory == SAIL_CHECKERBOARD || texCategory == SAIL_CHECKERBOARD2 || texCategory == SAIL_BILERP ||
+           texCategory == SAIL_UVF;
+}
+SD V3 surfaceColor(const SailSurface& u, V2 uv) {
+    const float* t = u.t;
+    switch (u.texCategory) {
+        case SAIL_CHECKERBOARD: {  // checkerboard.glsl:6-20
+            float ax = uv.x * t[13], ay = uv.y * t[13], width = t[14];
+            float fx = ax - dm_floor(ax), fy = ay - dm_floor(ay);
+            bool in_outline = (fx < width || fx > 1.0f - width) || (fy < width || fy > 1.0f - width);
+            return in_outline ? splat3(0.5f) : splat3(1.0f);
+        }
+        case SAIL_CHECKERBOARD2: {  // checkerboard2.glsl:7-16
+            float ux = dm_floor(uv.x * t[13]), uy = dm_floor(uv.y * t[13]);
+            return (toInt(ux + uy) % 2 == 0) ? ld3(t + ST_C1) : ld3(t + ST_C2);
+        }
+        case SAIL_BILERP: {  // bilerp.glsl:1-14 (broken in the reference, SURVEY Q12: evident intent)
+            float ux = uv.x, uy = uv.y;
+            return (1.0f - ux) * (1.0f - uy) * ld3(t + ST_B00) + (1.0f - ux) * uy * ld3(t + ST_B01) +
+                   ux * (1.0f - uy) * ld3(t + ST_B10) + ux * uy * ld3(t + ST_B11);
+        }
+        case SAIL_UVF:  // uvf.glsl:1-3
+            return mk3(uv.x - dm_floor(uv.x), uv.y - dm_floor(uv.y), 0.0f);
+    }
+    return ld3(t + ST_RGB);  // UNIFORM_COLOR, and MIXF / SCALE folded to a constant at upload
+}
+
+SD float azimuthU(float hx, float hy) {  // phi = atan(y,x); if (phi<0) phi += 2PI; u = phi/(2PI)
+    float phi = dm_atan2(hy, hx);
+    if (phi < 0.0f) phi += SAIL_TWO_PI;
+    return phi * SAIL_RCP_TWO_PI;
+}
+SD V3 dpduAround(float hx, float hy) { return mk3(-2.0f * SAIL_PI * hy, 2.0f * SAIL_PI * hx, 0.0f); }
+
+// cube.glsl:25-38 / cornellbox.glsl:39-51 face selection
+SD V3 boxFaceNormal(V3 hit, V3 mn, V3 mx, float c) {
+    if (hit.x < mn.x + 0.0001f) return mk3(c * -1.0f, c * 0.0f, c * 0.0f);
+    else if (hit.x > mx.x - 0.0001f) return mk3(c * 1.0f, c * 0.0f, c * 0.0f);
+    else if (hit.y < mn.y + 0.0001f) return mk3(c * 0.0f, c * -1.0f, c * 0.0f);
+    else if (hit.y > mx.y - 0.0001f) return mk3(c * 0.0f, c * 1.0f, c * 0.0f);
+    else if (hit.z < mn.z + 0.0001f) return mk3(c * 0.0f, c * 0.0f, c * -1.0f);
+    else return mk3(c * 0.0f, c * 0.0f, c * 1.0f);
+}
+SD V3 boxDpdu(V3 normal) {  // cube.glsl:40-48
+    if (dm_abs(normal.x) < 0.5f) return cross3(normal, mk3(1.0f, 0.0f, 0.0f));
+    return cross3(normal, mk3(0.0f, 1.0f, 0.0f));
+}
+
+// Phase 2: the full hit record of object `i` at distance `t` (the body of intersectX() after the hit
+// test, the per-arm emission mask of shader.shape.js:47-49 and the tail of :38-40).
+SD void hitRecord(const SailSceneBlock& sc, int i, float t, const Ray& ray, Hit& h) {
+    const SailShape& s = sc.shape[i];
+    const SailSurface& u = sc.surf[i];
+    const float* q = s.q;
+    const bool wantUV = textureNeedsUV(u.texCategory);
+    V3 gn;  // geometric normal as intersectX() returns it
+    V2 uv = mk2(0.0f, 0.0f);
+    h.d = t;
+    h.index = i;
+    switch (s.category) {
+        case SAIL_CUBE: {  // cube.glsl:79-85
+            V3 mn = ld3(s.lo), mx = ld3(s.hi);
+            h.p = ray.o + t * ray.d;
+            gn = boxFaceNormal(h.p, mn, mx, s.rev);
+            h.dpdu = boxDpdu(gn);
+            if (wantUV) {  // getCubeUV, cube.glsl:54-63 (compares the *shifted* hit, as written)
+                V3 tr = mx - mn, hs = h.p - mn;
+                if (hs.x < mn.x + 0.0001f || hs.x > mx.x - 0.0001f) uv = mk2(fdiv(hs.y, tr.y), fdiv(hs.z, tr.z));
+                else if (hs.y < mn.y + 0.0001f || hs.y > mx.y - 0.0001f) uv = mk2(fdiv(hs.x, tr.x), fdiv(hs.z, tr.z));
+                else uv = mk2(fdiv(hs.x, tr.x), fdiv(hs.y, tr.y));
+            }
+            h.sc = surfaceColor(u, uv);
+            break;
+        }
+        case SAIL_CORNELLBOX: {  // cornellbox.glsl:23-37,81-88
+            V3 mn = ld3(s.lo), mx = ld3(s.hi);
+            h.p = ray.o + t * ray.d;
+            gn = -boxFaceNormal(h.p, mn, mx, 1.0f);
+            h.dpdu = boxDpdu(gn);
+            if (h.p.x < mn.x + 0.0001f) h.sc = mk3(0.25f, 0.75f, 0.25f);       // GREEN
+            else if (h.p.x > mx.x - 0.0001f) h.sc = mk3(0.25f, 0.25f, 0.75f);  // BLUE
+            else if (h.p.y < mn.y + 0.0001f) h.sc = splat3(1.0f);
+            else if (h.p.y > mx.y - 0.0001f) h.sc = splat3(1.0f);
+            else if (h.p.z > mn.z + 0.0001f) h.sc = splat3(1.0f);
+            else h.sc = splat3(0.0f);
+            break;
+        }
+        case SAIL_SPHERE: {  // sphere.glsl:33-43,62-84
+            V3 c = ld3(q + SQ_SPH_C);
+            V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - c);
+            V3 hl = ol + t * dl;
+            float r = q[SQ_SPH_R];
+            float theta = dm_acos(fclamp(hl.z * q[SQ_SPH_INVR], -1.0f, 1.0f));
+            if (wantUV) {
+                float gx = hl.x;
+                if (hl.x == 0.0f && hl.y == 0.0f) gx = 1e-5f * r;  // guards phi only (Q18)
+                uv = mk2(azimuthU(gx, hl.y), theta * SAIL_RCP_PI);
+            }
+            float zRadius = dm_sqrt(hl.x * hl.x + hl.y * hl.y);
+            float invZRadius = dm_rcp(zRadius);
+            float cosPhi = hl.x * invZRadius, sinPhi = hl.y * invZRadius;
+            V3 dpdu = dpduAround(hl.x, hl.y);
+            V3 dpdv = SAIL_PI * mk3(hl.z * cosPhi, hl.z * sinPhi, -r * dm_sin(theta));
+            V3 nl = normalize3(cross3(dpdv, dpdu));
+            h.sc = surfaceColor(u, uv);
+            h.p = objToWorld(hl) + c;
+            gn = objToWorld(nl);
+            h.dpdu = objToWorld(dpdu);
+            break;
+        }
+        case SAIL_RECTANGLE: {  // rectangle.glsl:36-62
+            V3 nn = ld3(q + SQ_RECT_N), ss = ld3(q + SQ_RECT_SS), ts = ld3(q + SQ_RECT_TS), mn = ld3(s.lo);
+            V3 dl = worldToLocal(ray.d, nn, ss, ts);
+            V3 ol = worldToLocal(ray.o - mn, nn, ss, ts);
+            V3 hl = ol + t * dl;
+            if (wantUV) uv = mk2(hl.x * q[SQ_RECT_INVMAXX], hl.y * q[SQ_RECT_INVMAXY]);
+            h.sc = surfaceColor(u, uv);
+            h.p = localToWorld(hl, nn, ss, ts) + mn;
+            gn = nn;
+            h.dpdu = ld3(q + SQ_RECT_DPDU);
+            break;
+        }
+        case SAIL_CONE: {  // cone.glsl:31-36,83-98
+            V3 p = ld3(q + SQ_CONE_P);
+            V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - p);
+            V3 hl = ol + t * dl;
+            float v = hl.z * q[SQ_CONE_INVH];
+            if (wantUV) uv = mk2(azimuthU(hl.x, hl.y), v);
+            V3 dpdu = dpduAround(hl.x, hl.y);
+            float inv = dm_rcp(1.0f - v);
+            V3 dpdv = mk3(-hl.x * inv, -hl.y * inv, q[SQ_CONE_H]);
+            V3 nl = normalize3(cross3(dpdu, dpdv));
+            h.sc = surfaceColor(u, uv);
+            h.p = objToWorld(hl) + p;
+            gn = objToWorld(nl);
+            h.dpdu = objToWorld(dpdu);
+            break;
+        }
+        case SAIL_CYLINDER: {  // cylinder.glsl:31-34,74-89
+            V3 p = ld3(q + SQ_CYL_P);
+            V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - p);
+            V3 hl = ol + t * dl;
+            if (wantUV) uv = mk2(azimuthU(hl.x, hl.y), hl.z * q[SQ_CYL_INVH]);
+            V3 dpdu = dpduAround(hl.x, hl.y);
+            V3 dpdv = mk3(0.0f, 0.0f, q[SQ_CYL_H]);
+            V3 nl = normalize3(cross3(dpdu, dpdv));
+            h.sc = surfaceColor(u, uv);
+            h.p = objToWorld(hl) + p;
+            gn = objToWorld(nl);
+            h.dpdu = objToWorld(dpdu);
+            break;
+        }
+        case SAIL_DISK: {  // disk.glsl:27-30,55-74
+            V3 p = ld3(q + SQ_DISK_P);
+            V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - p);
+            V3 hl = ol + t * dl;
+            float dist2 = hl.x * hl.x + hl.y * hl.y;
+            float rHit = dm_sqrt(dist2);
+            if (wantUV) {
+                float oneMinusV = (rHit - q[SQ_DISK_INNER]) * q[SQ_DISK_INVDR];
+                uv = mk2(azimuthU(hl.x, hl.y), 1.0f - oneMinusV);
+            }
+            V3 dpdu = dpduAround(hl.x, hl.y);
+            V3 dpdv = vdivs(mk3(hl.x, hl.y, 0.0f) * q[SQ_DISK_DIFF], rHit);
+            V3 nl = normalize3(cross3(dpdu, dpdv));
+            h.sc = surfaceColor(u, uv);
+            h.p = objToWorld(hl) + p;
+            gn = objToWorld(nl);
+            h.dpdu = objToWorld(dpdu);
+            break;
+        }
+        case SAIL_HYPERBOLOID: {  // hyperboloid.glsl:41-46,92-110
+            V3 p = ld3(q + SQ_HYP_P), p1 = ld3(q + SQ_HYP_P1), p2 = ld3(q + SQ_HYP_P2);
+            V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - p);
+            V3 hl = ol + t * dl;
+            float v = (hl.z - p1.z) * q[SQ_HYP_INVDZ];
+            V3 pr = (1.0f - v) * p1 + v * p2;
+            float phi = dm_atan2(pr.x * hl.y - hl.x * pr.y, hl.x * pr.x + hl.y * pr.y);
+            if (phi < 0.0f) phi += SAIL_TWO_PI;
+            uv = mk2(phi * SAIL_RCP_TWO_PI, v);
+            float sinPhi, cosPhi;
+            dm_sincos(phi, &sinPhi, &cosPhi);
+            V3 dpdu = dpduAround(hl.x, hl.y);
+            V3 dpdv = mk3((p2.x - p1.x) * cosPhi - (p2.y - p1.y) * sinPhi, (p2.x - p1.x) * sinPhi + (p2.y - p1.y) * cosPhi,
+                          p2.z - p1.z);
+            V3 nl = normalize3(cross3(dpdu, dpdv));
+            h.sc = surfaceColor(u, uv);
+            h.p = objToWorld(hl) + p;
+            gn = objToWorld(nl);
+            h.dpdu = objToWorld(dpdu);
+            break;
+        }
+        default: {  // SAIL_PARABOLOID: paraboloid.glsl:35-40,84-102
+            V3 p = ld3(q + SQ_PAR_P);
+            V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - p);
+            V3 hl = ol + t * dl;
+            if (wantUV) uv = mk2(azimuthU(hl.x, hl.y), (hl.z - q[SQ_PAR_ZMIN]) * q[SQ_PAR_INVDZ]);
+            V3 dpdu = dpduAround(hl.x, hl.y);
+            float inv = dm_rcp(2.0f * hl.z);
+            V3 dpdv = q[SQ_PAR_DZ] * mk3(hl.x * inv, hl.y * inv, 1.0f);
+            V3 nl = normalize3(cross3(dpdu, dpdv));
+            h.sc = surfaceColor(u, uv);
+            h.p = objToWorld(hl) + p;
+            gn = objToWorld(nl);
+            h.dpdu = objToWorld(dpdu);
+            break;
+        }
+    }
+    // shader.shape.js:47-49: emission only when the ray faces the (possibly reversed) normal.
+    V3 fn = s.rev * gn;
+    bool faceObj = dot3(fn, ray.d) < -SAIL_EPSILON;
+    h.emission = faceObj ? ld3(s.emission) : splat3(0.0f);
+    // shader.shape.js:38-40
+    h.matCategory = s.matCategory;
+    h.into = dot3(gn, ray.d) < -SAIL_EPSILON;
+    h.n = h.into ? gn : -gn;
+}
+
+// intersectObjects() as one call (shader.shape.js:28-51).  Returns false on a miss.
+SD bool intersectObjects(const SailSceneBlock& sc, const Ray& ray, Hit& h) {
+    float t;
+    int id = nearestObject(sc, ray, t);
+    h.d = t;
+    h.index = id;
+    if (id < 0) return false;
+    hitRecord(sc, id, t, ray, h);
+    return true;
+}
+
+// testShadow(), shader.light.js:24-31: distance only.
+SD bool testShadow(const SailSceneBlock& sc, V3 origin, V3 toLight) {
+    Ray r;
+    r.o = origin;
+    r.d = toLight;
+    float d;
+    nearestObject(sc, r, d);
+    return d > SAIL_EPSILON && d < SAIL_ONEMINUSEPSILON;
+}
+
+#endif
