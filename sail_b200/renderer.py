@@ -1,0 +1,100 @@
+"""Renderer / Tracer: the host-side mirror of the reference's render orchestration
+(/root/reference/src/core/renderer.js:8-73, src/core/tracer.js:8-101), driving libsail_b200.so.
+
+Same names, argument meaning and call order as the reference: ``renderer.update(scene)`` commits the
+scene (plugin config + the three wire-format tables), ``renderer.render(scene)`` traces one sample per
+pixel and runs the display filter, ``renderer.updateObjects(scene)`` re-uploads the objects table.
+Differences forced by the platform: the canvas is a ``(width, height)`` pair, the displayed image is
+returned as an array instead of being drawn, and the wall-clock seed / ``Math.random()`` jitter of
+tracer.js:94-98 come from an explicit :class:`FrameSchedule` so frames are reproducible.
+"""
+import numpy as np
+
+from . import capi
+from .filters import lower_filter
+from .scene import plugin_masks
+from .schedule import FrameSchedule, frame_matrix
+from .wire import serialize_objects, serialize_scene
+
+
+class Tracer:
+    """tracer.js:8-101."""
+
+    def __init__(self, ctx, schedule=None):
+        self.ctx = ctx
+        self.schedule = schedule or FrameSchedule()
+        self.n = self.tn = self.ln = 0
+
+    def updateObjects(self, scene):
+        """tracer.js:25-40."""
+        objects = serialize_objects(scene)
+        self.n = objects.shape[0]
+        self.ctx.upload_objects(objects)
+
+    def update(self, scene):
+        """tracer.js:42-90: setProgram(new TraceShader(scene.tracerConfig())) + table upload."""
+        masks = plugin_masks(scene.tracerConfig())
+        self.ctx.configure(**masks)
+        objects, texparams, lights = serialize_scene(scene)
+        self.n, self.tn, self.ln = objects.shape[0], texparams.shape[0], lights.shape[0]
+        self.ctx.upload_scene(objects, texparams, lights)
+
+    def frame(self, modelviewProjection, eye, sampleCount):
+        """The uniforms of tracer.js:92-98 for progressive sample ``sampleCount``."""
+        k = int(sampleCount)
+        m = frame_matrix(modelviewProjection, self.schedule.jitter_unit(k), self.ctx.width, self.ctx.height)
+        return capi.make_frame(m, eye, k / (k + 1.0), self.schedule.time(k))
+
+    def render(self, modelviewProjection, eye, sampleCount):
+        """tracer.js:92-101."""
+        f = self.frame(modelviewProjection, eye, sampleCount)
+        self.ctx.render_n([f])
+
+
+class Renderer:
+    """renderer.js:8-73.  ``canvas`` is ``(width, height)`` or an object with ``width``/``height``."""
+
+    def __init__(self, canvas, device=0, rows=None, schedule=None):
+        if isinstance(canvas, (tuple, list)):
+            width, height = canvas
+        elif isinstance(canvas, dict):
+            width, height = canvas["width"], canvas["height"]
+        else:
+            width, height = canvas.width, canvas.height
+        self.ctx = capi.Context(width, height, device=device, rows=rows)
+        self.tracer = Tracer(self.ctx, schedule)
+        self._filter = None
+
+    def close(self):
+        self.ctx.close()
+
+    def updateObjects(self, scene):
+        self.tracer.updateObjects(scene)
+
+    def update(self, scene):
+        """renderer.js:45-52."""
+        f = lower_filter(scene.rendererConfig()["filter"])
+        self._filter = f
+        self.ctx.configure(filter_id=f["filter_id"], filter_gamma_c=f["gamma_c"], filter_radius=f["radius"],
+                           filter_weights=f["weights"])
+        self.tracer.update(scene)
+
+    def trace(self, scene, frames=1):
+        """``frames`` progressive samples without the display pass (batched through sail_render_n)."""
+        if scene.moving:
+            scene.sampleCount = 0
+            self.updateObjects(scene)
+        if scene.sampleCount == 0:
+            self.ctx.reset()
+        fr = [self.tracer.frame(scene.mat, scene.eye, scene.sampleCount + i) for i in range(frames)]
+        scene.sampleCount += frames
+        self.ctx.render_n(fr)
+
+    def render(self, scene, as_u8=True):
+        """renderer.js:54-72: one progressive sample, then the display pass; returns the displayed image
+        (H x W x 4, row 0 = bottom).  The selection wireframe (renderer.js:65-71) is editor UI, out of scope."""
+        self.trace(scene, 1)
+        return self.ctx.present(as_u8=as_u8)
+
+    def readPixels(self, which=capi.AOV_COLOR):
+        return self.ctx.read_aov(which)

@@ -1,0 +1,205 @@
+"""GPU parity: the CUDA path (through the C ABI of include/sail_b200.h) against the CPU oracle on the same
+seeded inputs.  Bar: hit ids exact; strict-arithmetic build is compared BIT-EXACT for
+depth, AOVs and colour as well (tolerance 0), so any tolerance a caller wants is met a fortiori."""
+import numpy as np
+import pytest
+
+from conftest import bits_equal, frame_uniforms, mismatch_report, scene_tables
+
+pytestmark = pytest.mark.gpu
+
+SIZES = {1: (96, 96), 2: (128, 72), 3: (128, 72), 5: (128, 72)}
+
+
+@pytest.fixture(scope="module")
+def capi():
+    from sail_b200 import capi as c
+    assert c.device_count() >= 1, "no sm_100 device: the CUDA path cannot run (there is no fallback)"
+    return c
+
+
+def _render_both(capi, oracle, cfg, nframes, kernel=0, batch=False):
+    W, H = SIZES[cfg]
+    scene, o, t, l, bounces = scene_tables(cfg, W, H)
+    oracle.set_scene(o, t, l)
+    ctx = capi.Context(W, H)
+    ctx.configure(max_bounces=bounces, kernel=kernel)
+    ctx.upload_scene(o, t, l)
+    acc = np.zeros((H, W, 3), np.float32)
+    frames = []
+    ref = None
+    for k in range(nframes):
+        m, eye, w, tm = frame_uniforms(scene, k, W, H)
+        ref = oracle.render_frame(W, H, m, eye, w, tm, acc, max_bounces=bounces, aovs=True)
+        if batch:
+            frames.append(capi.make_frame(m, eye, w, tm))
+        else:
+            ctx.render(m, eye, w, tm)
+    if batch:
+        ctx.render_n(frames)
+    out = {"color": ctx.read_accum(), "normal": ctx.read_aov(capi.AOV_NORMAL), "position": ctx.read_aov(capi.AOV_POSITION),
+           "hit_id": ctx.read_aov(capi.AOV_HIT_ID), "depth": ctx.read_aov(capi.AOV_DEPTH)}
+    ctx.close()
+    ref["color"] = acc
+    return out, ref
+
+
+@pytest.mark.parametrize("cfg", [1, 2, 3, 5])
+def test_frames_bit_exact(capi, oracle, cfg):
+    out, ref = _render_both(capi, oracle, cfg, 4)
+    assert np.array_equal(out["hit_id"], ref["hit_id"]), "primary hit ids differ"
+    for name in ("depth", "normal", "position", "color"):
+        assert bits_equal(out[name], ref[name]), mismatch_report(out[name], ref[name], "cfg%d %s" % (cfg, name))
+
+
+@pytest.mark.parametrize("cfg", [1, 2])
+def test_render_n_equals_single_calls(capi, oracle, cfg):
+    a, _ = _render_both(capi, oracle, cfg, 6, batch=False)
+    b, ref = _render_both(capi, oracle, cfg, 6, batch=True)
+    for name in ("color", "normal", "position", "depth"):
+        assert bits_equal(a[name], b[name]), name
+    assert bits_equal(b["color"], ref["color"])
+
+
+@pytest.mark.parametrize("cfg", [1, 2, 3, 5])
+def test_bounce_replay(capi, oracle, cfg):
+    """Per-bounce rays / hit ids / distances of one frame: every bounce must agree exactly."""
+    W, H = SIZES[cfg]
+    scene, o, t, l, bounces = scene_tables(cfg, W, H)
+    oracle.set_scene(o, t, l)
+    m, eye, w, tm = frame_uniforms(scene, 2, W, H)
+    ref = oracle.trace_dump(W, H, m, eye, tm, max_bounces=bounces)
+    with capi.Context(W, H) as ctx:
+        ctx.configure(max_bounces=bounces)
+        ctx.upload_scene(o, t, l)
+        out = ctx.trace_dump(capi.make_frame(m, eye, w, tm))
+    assert np.array_equal(out["hit_id"], ref["hit_id"])
+    for name in ("t", "rays", "radiance"):
+        assert bits_equal(out[name], ref[name]), mismatch_report(out[name], ref[name], name)
+
+
+@pytest.mark.parametrize("cfg", [1, 2, 3])
+def test_intersect_fuzz(capi, oracle, cfg):
+    """1e5 random rays from inside the box (SURVEY.md 8(d) fuzz set): ids exact, t / normal bit-exact."""
+    W, H = 16, 16
+    scene, o, t, l, _ = scene_tables(cfg, W, H)
+    oracle.set_scene(o, t, l)
+    rng = np.random.default_rng(cfg)
+    n = 100000
+    org = rng.uniform([0.1, 0.1, -4.5], [5.4, 5.3, 5.5], size=(n, 3))
+    d = rng.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d[: n // 10] *= rng.uniform(0.2, 3.0, size=(n // 10, 1))  # un-normalised directions too (Q6, shadow rays)
+    d[n // 10: n // 10 + 64, 0] = 0.0                           # axis-parallel components
+    rays = np.concatenate([org, d], axis=1).astype(np.float32)
+    rid, rt, rn, rm = oracle.intersect_rays(rays)
+    with capi.Context(W, H) as ctx:
+        ctx.upload_scene(o, t, l)
+        gid, gt, gn, gm = ctx.intersect_rays(rays)
+    assert np.array_equal(gid, rid)
+    assert bits_equal(gt, rt), mismatch_report(gt, rt, "t")
+    hit = rid >= 0
+    assert bits_equal(gn[hit], rn[hit]), mismatch_report(gn[hit], rn[hit], "normal")
+    assert np.array_equal(gm[hit], rm[hit])
+
+
+def test_device_math_matches_host(capi, oracle):
+    """detmath.h on sm_100a vs the same header compiled by g++: bit-exact, incl. the RNG's sin range."""
+    rng = np.random.default_rng(7)
+    cases = {
+        "sin": rng.uniform(-3e5, 3e5, 200000), "cos": rng.uniform(-3e5, 3e5, 200000), "tan": rng.uniform(-10, 10, 50000),
+        "atan": rng.normal(scale=10, size=50000), "acos": rng.uniform(-1, 1, 50000), "asin": rng.uniform(-1, 1, 50000),
+        "exp": rng.uniform(-90, 90, 50000), "log": rng.uniform(1e-30, 1e30, 50000),
+    }
+    with capi.Context(16, 16) as ctx:
+        for name, a in cases.items():
+            a = a.astype(np.float32)
+            assert bits_equal(ctx.eval_math(name, a), oracle.detmath(name, a)), name
+        a = rng.normal(size=50000).astype(np.float32)
+        b = rng.normal(size=50000).astype(np.float32)
+        assert bits_equal(ctx.eval_math("atan2", a, b), oracle.detmath("atan2", a, b))
+        a = rng.uniform(0, 4, 50000).astype(np.float32)
+        b = rng.uniform(-3, 3, 50000).astype(np.float32)
+        assert bits_equal(ctx.eval_math("pow", a, b), oracle.detmath("pow", a, b))
+        # a/b := a * rcp_rn(b) and sqrt correctly rounded
+        a64, b64 = a.astype(np.float32), (b + np.float32(3.5)).astype(np.float32)
+        want = (a64 * (np.float32(1.0) / b64)).astype(np.float32)
+        assert bits_equal(ctx.eval_math("div", a64, b64), want)
+        assert bits_equal(ctx.eval_math("sqrt", a), np.sqrt(a))
+
+
+FILTERS = [("color", {}), ("gamma", {"c": "2.2"}), ("tonemapping", {}), ("normal", {}), ("position", {}),
+           ("box", {"r": "vec2(2.0,2.0)"}), ("gaussian", {"r": "vec2(2.0,2.0)", "alpha": "2.0"}),
+           ("sinc", {"r": "vec2(2.0,2.0)", "tau": "3.0"}), ("mitchell", {"r": "vec2(2.0,2.0)", "b": "0.3", "c": "0.3"}),
+           ("triangle", {"r": "vec2(1.5,2.5)"}), ("wavelet", {"r": "vec2(2.0,2.0)"})]
+
+
+@pytest.mark.parametrize("name,params", FILTERS)
+def test_present_filters(capi, oracle, name, params):
+    from sail_b200.filters import lower_filter
+    from sail_b200.generator import PluginParams
+    W, H = SIZES[2]
+    scene, o, t, l, bounces = scene_tables(2, W, H)
+    pp = PluginParams(name)
+    for k, v in params.items():
+        pp.addParam(k, v)
+    f = lower_filter(pp)
+    with capi.Context(W, H) as ctx:
+        ctx.configure(max_bounces=bounces, filter_id=f["filter_id"], filter_gamma_c=f["gamma_c"], filter_radius=f["radius"],
+                      filter_weights=f["weights"])
+        ctx.upload_scene(o, t, l)
+        frames = []
+        for k in range(4):
+            m, eye, w, tm = frame_uniforms(scene, k, W, H)
+            frames.append(capi.make_frame(m, eye, w, tm))
+        ctx.render_n(frames)
+        color, normal, position = ctx.read_accum(), ctx.read_aov(capi.AOV_NORMAL), ctx.read_aov(capi.AOV_POSITION)
+        g32, g8 = ctx.present(both=True)
+    r32, r8 = oracle.present(color, normal, position, f, as_u8=True)
+    assert bits_equal(g32, r32), mismatch_report(g32, r32, name)
+    assert np.array_equal(g8, r8)
+
+
+def test_tile_rows_and_sum_mode(capi, oracle):
+    """Row-sharded contexts reproduce the full frame; SUM accumulation equals the mean within rounding."""
+    W, H = SIZES[2]
+    scene, o, t, l, bounces = scene_tables(2, W, H)
+    frames = [capi.make_frame(*frame_uniforms(scene, k, W, H)) for k in range(8)]
+    with capi.Context(W, H) as full:
+        full.configure(max_bounces=bounces)
+        full.upload_scene(o, t, l)
+        full.render_n(frames)
+        want = full.read_accum()
+    got = np.zeros_like(want)
+    for rows in ((0, 24), (24, 56), (56, H)):
+        with capi.Context(W, H, rows=rows) as part:
+            part.configure(max_bounces=bounces)
+            part.upload_scene(o, t, l)
+            part.render_n(frames)
+            got[rows[0]:rows[1]] = part.read_accum()[rows[0]:rows[1]]
+    assert bits_equal(got, want)
+    with capi.Context(W, H) as s:
+        s.configure(max_bounces=bounces, accum_mode=capi.ACCUM_SUM)
+        s.upload_scene(o, t, l)
+        s.render_n(frames)
+        s.scale_accum(1.0 / len(frames))
+        summed = s.read_accum()
+    # summation order differs from the running mean: 1e-5 relative-or-absolute
+    assert np.all(np.abs(summed - want) <= 1e-5 * np.maximum(1.0, np.abs(want)))
+
+
+def test_error_paths(capi):
+    with pytest.raises(capi.SailError):
+        capi.Context(0, 10)
+    with capi.Context(32, 32) as ctx:
+        m = np.eye(4, dtype=np.float32)
+        with pytest.raises(capi.SailError) as ei:
+            ctx.render(m, [0, 0, 0], 0.0, 0.0)  # render before upload
+        assert ei.value.code == capi.ERR_STATE
+        bad = np.zeros((1, 18), np.float32)
+        bad[0, 0] = 42
+        with pytest.raises(capi.SailError) as ei:
+            ctx.upload_scene(bad, np.zeros((2, 16), np.float32), np.zeros((0, 18), np.float32))
+        assert ei.value.code == capi.ERR_INVALID
+        with pytest.raises(capi.SailError):
+            ctx.configure(filter_id=99)
