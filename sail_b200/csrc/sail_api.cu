@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "../../include/sail_b200.h"
+#include "sail_diag.cuh"
 #include "sail_mega.cuh"
 #include "sail_present.cuh"
 #include "sail_wavefront.cuh"
@@ -41,7 +42,24 @@ struct sail_ctx {
     sail_ctx() { err[0] = 0; }
 };
 
+extern "C" {
+cudaError_t sail_launch_mega_g0(int F, const SailLaunch* L, dim3 grid, cudaStream_t stream);
+cudaError_t sail_launch_mega_g1(int F, const SailLaunch* L, dim3 grid, cudaStream_t stream);
+cudaError_t sail_launch_mega_g2(int F, const SailLaunch* L, dim3 grid, cudaStream_t stream);
+cudaError_t sail_launch_mega_g3(int F, const SailLaunch* L, dim3 grid, cudaStream_t stream);
+}
+
 namespace {
+
+cudaError_t launchMega(int F, const SailLaunch& L, dim3 grid, cudaStream_t stream) {
+    switch (F >> 2) {
+        case 0: return sail_launch_mega_g0(F, &L, grid, stream);
+        case 1: return sail_launch_mega_g1(F, &L, grid, stream);
+        case 2: return sail_launch_mega_g2(F, &L, grid, stream);
+        case 3: return sail_launch_mega_g3(F, &L, grid, stream);
+    }
+    return cudaErrorInvalidValue;
+}
 
 int setErr(sail_ctx* c, int code, const char* fmt, ...) {
     if (c) {
@@ -256,9 +274,9 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
         if (e != cudaSuccess) return setErr(ctx, SAIL_ERR_CUDA, "wavefront render failed: %s", cudaGetErrorString(e));
     } else {
         dim3 grid((ctx->W + SAIL_TILE_W - 1) / SAIL_TILE_W, (ctx->y1 - ctx->y0 + SAIL_TILE_H - 1) / SAIL_TILE_H);
-        sail_trace_megakernel<<<grid, SAIL_CTA_THREADS, 0, ctx->stream>>>(L);
+        // the variant follows the scene's content, never the caller's mask hints
+        CU(launchMega(ctx->hostScene.features & SAIL_F_ALL, L, grid, ctx->stream));
         ctx->launches++;
-        CU(cudaGetLastError());
     }
     CU(cudaEventRecord(ctx->evStop, ctx->stream));
     ctx->timed = true;

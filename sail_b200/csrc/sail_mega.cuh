@@ -71,6 +71,7 @@ SD V3 primaryDir(const SailFrameDev& f, float a, float b) {
 }
 SD float nanToZero(float v) { return (v == v) ? v : 0.0f; }
 
+template <int F>
 __global__ void __launch_bounds__(SAIL_CTA_THREADS) sail_trace_megakernel(const __grid_constant__ SailLaunch L) {
     __shared__ SailSceneBlock sc;
     stageScene(sc, L.scene);
@@ -92,7 +93,7 @@ __global__ void __launch_bounds__(SAIL_CTA_THREADS) sail_trace_megakernel(const 
         Ray ray;
         ray.o = ld3(f.eye);
         ray.d = primaryDir(f, a, b);
-        V3 e = tracePath(sc, ray, L.maxBounces, fx, fy, fz, f.timeSinceStart, first);
+        V3 e = tracePath<F>(sc, ray, L.maxBounces, fx, fy, fz, f.timeSinceStart, first);
         e = mk3(nanToZero(e.x), nanToZero(e.y), nanToZero(e.z));
         if (L.accumMode == 0) c = mix3(e, c, f.textureWeight);  // fstrace.glsl:14
         else c = c + e;
@@ -109,111 +110,6 @@ __global__ void __launch_bounds__(SAIL_CTA_THREADS) sail_trace_megakernel(const 
         L.hitId[pix] = first.id;
         L.depth[pix] = first.t;
     }
-}
-
-// ---- diagnostics ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(SAIL_CTA_THREADS) sail_intersect_kernel(const SailSceneBlock* __restrict__ scene,
-                                                                          const float* __restrict__ rays, int count, int* hitId,
-                                                                          float* t, float* normal, int* matCategory) {
-    __shared__ SailSceneBlock sc;
-    stageScene(sc, scene);
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= count) return;
-    Ray r;
-    r.o = ld3(rays + 6 * i);
-    r.d = ld3(rays + 6 * i + 3);
-    Hit h;
-    h.n = splat3(0.0f);
-    h.matCategory = 0;
-    bool ok = intersectObjects(sc, r, h);
-    if (hitId) hitId[i] = h.index;
-    if (t) t[i] = h.d;
-    if (normal) { normal[3 * i] = ok ? h.n.x : 0.0f; normal[3 * i + 1] = ok ? h.n.y : 0.0f; normal[3 * i + 2] = ok ? h.n.z : 0.0f; }
-    if (matCategory) matCategory[i] = ok ? h.matCategory : 0;
-}
-
-struct SailDumpLaunch {
-    int W, H, maxBounces;
-    float rcpW, rcpH;
-    const SailSceneBlock* scene;
-    int* hitId;
-    float* t;
-    float* rays;
-    float* radiance;
-    SailFrameDev frame;
-};
-// trace() with per-bounce records; the loop body is the one of tracePath().
-__global__ void __launch_bounds__(SAIL_CTA_THREADS) sail_trace_dump_kernel(const __grid_constant__ SailDumpLaunch L) {
-    __shared__ SailSceneBlock sc;
-    stageScene(sc, L.scene);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int x = blockIdx.x * SAIL_TILE_W + (warp & 1) * 8 + (lane & 7);
-    const int y = blockIdx.y * SAIL_TILE_H + (warp >> 1) * 4 + (lane >> 3);
-    if (x >= L.W || y >= L.H) return;
-    const size_t pix = (size_t)y * L.W + x;
-    const float fx = (float)x + 0.5f, fy = (float)y + 0.5f, fz = 0.5f;
-    Ray ray;
-    ray.o = ld3(L.frame.eye);
-    ray.d = primaryDir(L.frame, fx * L.rcpW, fy * L.rcpH);
-    const int B = L.maxBounces;
-    for (int k = 0; k < B; k++) {
-        if (L.hitId) L.hitId[pix * B + k] = -2;
-        if (L.t) L.t[pix * B + k] = 0.0f;
-        if (L.rays) for (int j = 0; j < 6; j++) L.rays[(pix * B + k) * 6 + j] = 0.0f;
-    }
-    V3 fpdf = splat3(1.0f), e = splat3(0.0f);
-    int deepth = 0;
-    while (deepth++ < B) {
-        Hit h;
-        bool ok = intersectObjects(sc, ray, h);
-        size_t o = pix * B + (deepth - 1);
-        if (L.hitId) L.hitId[o] = h.index;
-        if (L.t) L.t[o] = h.d;
-        if (L.rays) {
-            float* r = L.rays + o * 6;
-            r[0] = ray.o.x; r[1] = ray.o.y; r[2] = ray.o.z; r[3] = ray.d.x; r[4] = ray.d.y; r[5] = ray.d.z;
-        }
-        if (!ok) break;
-        float seed = L.frame.timeSinceStart + (float)deepth;
-        V2 u = random2(fx, fy, fz, seed);
-        V3 wi, _fpdf;
-        e = e + shade(sc, h, u, -ray.d, wi, _fpdf) * fpdf;
-        fpdf = fpdf * _fpdf;
-        float outdot = dot3(h.n, wi);
-        ray.o = h.p + h.n * (outdot > SAIL_EPSILON ? 0.0001f : -0.0001f);
-        ray.d = wi;
-    }
-    if (L.radiance) {
-        L.radiance[3 * pix] = nanToZero(e.x);
-        L.radiance[3 * pix + 1] = nanToZero(e.y);
-        L.radiance[3 * pix + 2] = nanToZero(e.z);
-    }
-}
-
-__global__ void sail_eval_math_kernel(int which, const float* a, const float* b, float* out, int count) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= count) return;
-    float x = a[i], y = b ? b[i] : 0.0f, r = 0.0f;
-    switch (which) {
-        case 0: r = dm_sin(x); break;
-        case 1: r = dm_cos(x); break;
-        case 2: r = dm_tan(x); break;
-        case 3: r = dm_atan(x); break;
-        case 4: r = dm_acos(x); break;
-        case 5: r = dm_asin(x); break;
-        case 6: r = dm_exp(x); break;
-        case 7: r = dm_log(x); break;
-        case 8: r = dm_atan2(x, y); break;
-        case 9: r = dm_pow(x, y); break;
-        case 10: r = dm_div(x, y); break;
-        case 11: r = dm_sqrt(x); break;
-    }
-    out[i] = r;
-}
-
-__global__ void sail_scale_kernel(float* p, size_t count, float s) {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < count) p[i] = p[i] * s;
 }
 
 #endif

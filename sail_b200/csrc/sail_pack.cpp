@@ -235,6 +235,16 @@ int sail_pack_scene(const float* objects, int n, const float* texparams, int tn,
         }
     }
 
+    // ---- kernel features actually needed by this scene ----
+    int feat = (ln > 0) ? SAIL_FEAT_NEE : 0;
+    for (int i = 0; i < n; i++) {
+        int c = out->shape[i].category, m = out->surf[i].matCategory, tc = out->surf[i].texCategory;
+        if (c == SAIL_CONE || c == SAIL_CYLINDER || c == SAIL_DISK || c == SAIL_HYPERBOLOID || c == SAIL_PARABOLOID) feat |= SAIL_FEAT_QUADRICS;
+        if (m == SAIL_METAL || m == SAIL_GLASS) feat |= SAIL_FEAT_GLOSSY;
+        if (tc == SAIL_CHECKERBOARD || tc == SAIL_CHECKERBOARD2 || tc == SAIL_BILERP || tc == SAIL_UVF) feat |= SAIL_FEAT_TEXTURED;
+    }
+    out->features = feat;
+
     // ---- lights: one resolved entry per drawable index (shader.light.js:12-22) ----
     for (int index = 0; ln > 0 && index <= ln; index++) {
         SailLight& l = out->light[index];

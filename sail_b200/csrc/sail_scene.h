@@ -25,6 +25,8 @@ enum { SAIL_CUBE = 1, SAIL_SPHERE = 2, SAIL_RECTANGLE = 3, SAIL_CONE = 4, SAIL_C
        SAIL_HYPERBOLOID = 7, SAIL_PARABOLOID = 8, SAIL_CORNELLBOX = 9 };
 enum { SAIL_AREA = 0, SAIL_POINT = 1, SAIL_SPOT = 2 };
 enum { SAIL_MATTE = 1, SAIL_MIRROR = 2, SAIL_METAL = 3, SAIL_GLASS = 4 };
+// Feature bits for kernel specialisation (see sail_shapes.cuh).
+enum { SAIL_FEAT_QUADRICS = 1, SAIL_FEAT_GLOSSY = 2, SAIL_FEAT_TEXTURED = 4, SAIL_FEAT_NEE = 8 };
 enum { SAIL_UNIFORM_COLOR = 0, SAIL_CHECKERBOARD = 5, SAIL_CHECKERBOARD2 = 7, SAIL_BILERP = 8, SAIL_MIXF = 9,
        SAIL_SCALE = 10, SAIL_UVF = 11 };
 
@@ -77,7 +79,8 @@ struct __attribute__((aligned(16))) SailLight {
 
 struct __attribute__((aligned(16))) SailSceneBlock {
     int n, ln;      // object count, light count (uniforms n, ln; src/core/shader.js:41-43)
-    int pad0, pad1;
+    int features;   // SAIL_F_* bits the scene content needs (kernel variant selection)
+    int pad1;
     SailShape shape[SAIL_MAX_OBJECTS];
     SailSurface surf[SAIL_MAX_OBJECTS];
     SailLight light[SAIL_MAX_LIGHTS + 1];

@@ -18,21 +18,21 @@ SD V2 random2(float fx, float fy, float fz, float seed) {
     float ax = fx + seed, ay = fy + seed, az = fz + seed;
     float d1 = ax * 12.9898f + ay * 78.233f + az * 151.7182f;
     float d2 = ax * 63.7264f + ay * 10.873f + az * 623.6736f;
-    return mk2(ffract(dm_sin(d1) * 43758.5453f + seed), ffract(dm_sin(d2) * 43758.5453f + seed));
+    return mk2(ffract(sail_sin(d1) * 43758.5453f + seed), ffract(sail_sin(d2) * 43758.5453f + seed));
 }
 
 // ---- util/sampler.glsl ---------------------------------------------------------------------------
 SD V3 uniformSampleSphere(V2 u) {
     float z = 1.0f - 2.0f * u.x;
     float r = dm_sqrt(1.0f - z * z);
-    float s, c;
-    dm_sincos(SAIL_TWO_PI * u.y, &s, &c);
+    float2 sc2 = sail_sincos(SAIL_TWO_PI * u.y);
+    float s = sc2.x, c = sc2.y;
     return mk3(r * c, r * s, z);
 }
 SD V3 cosineSampleHemisphere(V2 u) {
     float r = dm_sqrt(u.x);
-    float s, c;
-    dm_sincos(SAIL_TWO_PI * u.y, &s, &c);
+    float2 sc2 = sail_sincos(SAIL_TWO_PI * u.y);
+    float s = sc2.x, c = sc2.y;
     return mk3(r * c, r * s, dm_sqrt(1.0f - u.x));
 }
 SD V2 concentricSampleDisk(V2 u) {
@@ -47,8 +47,8 @@ SD V2 concentricSampleDisk(V2 u) {
         r = vOffset;
         theta = SAIL_PIOVER2 - fdiv(uOffset, vOffset) * SAIL_PIOVER4;
     }
-    float s, c;
-    dm_sincos(theta, &s, &c);
+    float2 sc2 = sail_sincos(theta);
+    float s = sc2.x, c = sc2.y;
     return mk2(r * c, r * s);
 }
 
@@ -118,16 +118,16 @@ SD V3 trowbridgeReitz_sample_wh(V2 u, float alphax, float alphay, V3 wo) {
     } else {
         phi = dm_atan(fdiv(alphay, alphax) * dm_tan(SAIL_PIOVER2 + SAIL_TWO_PI * u.x));
         if (u.x > 0.5f) phi += SAIL_PI;
-        float sp, cp;
-        dm_sincos(phi, &sp, &cp);
+        float2 sc2 = sail_sincos(phi);
+        float sp = sc2.x, cp = sc2.y;
         float alphax2 = alphax * alphax, alphay2 = alphay * alphay;
         float alpha2 = dm_rcp(fdiv(cp * cp, alphax2) + fdiv(sp * sp, alphay2));
         float tanTheta2 = fdiv(alpha2 * u.x, 1.0f - u.x);
         cosTheta_ = dm_rcp(dm_sqrt(1.0f + tanTheta2));
     }
     float sinTheta_ = dm_sqrt(fmax2(0.0f, 1.0f - cosTheta_ * cosTheta_));
-    float sp, cp;
-    dm_sincos(phi, &sp, &cp);
+    float2 scw = sail_sincos(phi);
+    float sp = scw.x, cp = scw.y;
     V3 wh = mk3(sinTheta_ * cp, sinTheta_ * sp, cosTheta_);  // sphericalDirection, utility.glsl:53-56
     if (!sameHemisphere(wo, wh)) wh = -wh;
     return wh;
@@ -230,12 +230,13 @@ SD V3 orenNayar_f(V3 R, float A, float B, V3 wo, V3 wi) {
 
 // ---- material(): shader.material.js:21-29 + matte/mirror/metal/glass.glsl ---------------------------
 // Returns fpdf (unclamped); writes wi (local frame) and, for matte only, f = matte_f().
+template <int F>
 SD V3 material(const SailSurface& su, int matCategory, V3 sc, bool into, V2 u, V3 wo, V3& wi, V3& f) {
     const float* m = su.m;
     wi = splat3(0.0f);
     f = splat3(0.0f);
     float pdf = 0.0f;
-    V3 fs;
+    V3 fs = splat3(0.0f);
     switch (matCategory) {
         case SAIL_MATTE: {  // matte.glsl:8-37
             V3 R = m[SM_MATTE_KD] * sc;
@@ -253,7 +254,7 @@ SD V3 material(const SailSurface& su, int matCategory, V3 sc, bool into, V2 u, V
             fs = vdivs(splat3(1.0f) * R, absCosTheta(wi));
             break;
         }
-        case SAIL_METAL: {  // metal.glsl:8-23
+        case SAIL_METAL: if (F & SAIL_F_GLOSSY) {  // metal.glsl:8-23
             MicroR mr;
             mr.R = sc;
             mr.fresnelKind = 1;
@@ -265,12 +266,12 @@ SD V3 material(const SailSurface& su, int matCategory, V3 sc, bool into, V2 u, V
             fs = microfacet_r_sample_f(mr, u, wo, wi, pdf);
             break;
         }
-        case SAIL_GLASS: {  // glass.glsl:10-35
+        case SAIL_GLASS: if (F & SAIL_F_GLOSSY) {  // glass.glsl:10-35
             float kr = m[SM_GLASS_KR], kt = m[SM_GLASS_KT], eta = m[SM_GLASS_ETA];
             float ur = m[SM_GLASS_UR], vr = m[SM_GLASS_VR];
             if (ur < SAIL_EPSILON && vr < SAIL_EPSILON) {  // bsdf.glsl:141-158 SpecularFr(1, eta)
-                float F = frDielectric(wo.z, 1.0f, eta);
-                if (u.x < F) {
+                float Fr = frDielectric(wo.z, 1.0f, eta);
+                if (u.x < Fr) {
                     wi = mk3(-wo.x, -wo.y, wo.z);
                     pdf = 1.0f;
                     fs = vdivs(kr * sc, absCosTheta(wi));
@@ -278,7 +279,7 @@ SD V3 material(const SailSurface& su, int matCategory, V3 sc, bool into, V2 u, V
                     float etaI = into ? 1.0f : eta;
                     float etaT = into ? eta : 1.0f;
                     wi = refract3(-wo, mk3(0.0f, 0.0f, 1.0f), fdiv(etaI, etaT));
-                    V3 ft = (kt * sc) * (1.0f - F);
+                    V3 ft = (kt * sc) * (1.0f - Fr);
                     pdf = 1.0f;
                     fs = vdivs(ft, absCosTheta(wi));
                 }
@@ -317,13 +318,14 @@ SD V3 material(const SailSurface& su, int matCategory, V3 sc, bool into, V2 u, V
 // ---- sampleGeometry(), shader.shape.js:53-67 ----------------------------------------------------------
 // Only sphere / rectangle / disk have a sampler; the other shapes return BLACK and leave pdf unwritten
 // (cube.glsl:50-52 ...), after which normalForX(BLACK) is still evaluated.
+template <int F>
 static __device__ __noinline__ V3 stubShapeNormal(const SailShape& s) {
     const float* q = s.q;
     const V3 hit = splat3(0.0f);
     switch (s.category) {
         case SAIL_CUBE: return boxFaceNormal(hit, ld3(s.lo), ld3(s.hi), s.rev);       // cube.glsl:25-38
         case SAIL_CORNELLBOX: return boxFaceNormal(hit, ld3(s.lo), ld3(s.hi), 1.0f);  // cornellbox.glsl:39-51
-        case SAIL_CONE: {  // cone.glsl:38-46
+        case SAIL_CONE: if (F & SAIL_F_QUADRICS) {  // cone.glsl:38-46
             V3 hh = hit - ld3(q + SQ_CONE_P);
             float d = dm_sqrt(hh.x * hh.x + hh.y * hh.y);
             float x1 = d * q[SQ_CONE_INVTANA];
@@ -331,21 +333,21 @@ static __device__ __noinline__ V3 stubShapeNormal(const SailShape& s) {
             V3 no = mk3(0.0f, 0.0f, q[SQ_CONE_H] - x1 - x2);
             return s.rev * normalize3(hh - no);
         }
-        case SAIL_CYLINDER:  // cylinder.glsl:36-38
+        case SAIL_CYLINDER: if (F & SAIL_F_QUADRICS)  // cylinder.glsl:36-38
             return s.rev * normalize3(mk3(hit.x - q[SQ_CYL_P], hit.y - q[SQ_CYL_P + 1], 0.0f));
-        case SAIL_HYPERBOLOID: {  // hyperboloid.glsl:48-58
+        case SAIL_HYPERBOLOID: if (F & SAIL_F_QUADRICS) {  // hyperboloid.glsl:48-58
             V3 p1 = ld3(q + SQ_HYP_P1), p2 = ld3(q + SQ_HYP_P2);
             float v = (hit.z - p1.z) * q[SQ_HYP_INVDZ];
             V3 pr = (1.0f - v) * p1 + v * p2;
-            float phi = dm_atan2(pr.x * hit.y - hit.x * pr.y, hit.x * pr.x + hit.y * pr.y);
+            float phi = sail_atan2(pr.x * hit.y - hit.x * pr.y, hit.x * pr.x + hit.y * pr.y);
             if (phi < 0.0f) phi += SAIL_TWO_PI;
-            float sp, cp;
-            dm_sincos(phi, &sp, &cp);
+            float2 sc2 = sail_sincos(phi);
+            float sp = sc2.x, cp = sc2.y;
             V3 dpdu = dpduAround(hit.x, hit.y);
             V3 dpdv = mk3((p2.x - p1.x) * cp - (p2.y - p1.y) * sp, (p2.x - p1.x) * sp + (p2.y - p1.y) * cp, p2.z - p1.z);
             return s.rev * objToWorld(normalize3(cross3(dpdu, dpdv)));
         }
-        case SAIL_PARABOLOID: {  // paraboloid.glsl:42-49
+        case SAIL_PARABOLOID: if (F & SAIL_F_QUADRICS) {  // paraboloid.glsl:42-49
             V3 dpdu = dpduAround(hit.x, hit.y);
             float inv = dm_rcp(2.0f * hit.z);
             V3 dpdv = q[SQ_PAR_DZ] * mk3(hit.x * inv, hit.y * inv, 1.0f);
@@ -354,6 +356,7 @@ static __device__ __noinline__ V3 stubShapeNormal(const SailShape& s) {
     }
     return splat3(0.0f);
 }
+template <int F>
 SD V3 sampleGeometry(const SailSceneBlock& sc, V2 u, int i, V3& normal, float& pdf) {
     normal = splat3(0.0f);
     pdf = 0.0f;
@@ -374,7 +377,7 @@ SD V3 sampleGeometry(const SailSceneBlock& sc, V2 u, int i, V3& normal, float& p
             normal = s.rev * ld3(q + SQ_RECT_N);
             return p;
         }
-        case SAIL_DISK: {  // disk.glsl:32-34,77-83
+        case SAIL_DISK: if (F & SAIL_F_QUADRICS) {  // disk.glsl:32-34,77-83
             V2 pd = concentricSampleDisk(u);
             V3 p = mk3(pd.x * q[SQ_DISK_R] + q[SQ_DISK_P], q[SQ_DISK_P + 1], pd.y * q[SQ_DISK_R] + q[SQ_DISK_P + 2]);
             pdf = q[SQ_DISK_PDF];
@@ -382,11 +385,12 @@ SD V3 sampleGeometry(const SailSceneBlock& sc, V2 u, int i, V3& normal, float& p
             return p;
         }
     }
-    normal = stubShapeNormal(s);
+    normal = stubShapeNormal<F>(s);
     return splat3(0.0f);
 }
 
 // ---- light_sample(), shader.light.js:12-22 + area/point/spot.glsl -----------------------------------
+template <int F>
 SD V3 light_sample(const SailSceneBlock& sc, V2 u, V3 hit, V3 insNormal) {
     const int ln = sc.ln;
     if (ln == 0) return splat3(0.0f);
@@ -397,21 +401,21 @@ SD V3 light_sample(const SailSceneBlock& sc, V2 u, V3 hit, V3 insNormal) {
         case SAIL_AREA: {  // area.glsl:13-23
             V3 normal;
             float pdf;
-            V3 p = sampleGeometry(sc, u, l.object, normal, pdf);
+            V3 p = sampleGeometry<F>(sc, u, l.object, normal, pdf);
             V3 toLight = p - hit;
             V3 normToLight = normalize3(toLight);
-            if (testShadow(sc, hit, toLight)) return splat3(0.0f);
+            if (testShadow<F>(sc, hit, toLight)) return splat3(0.0f);
             return vdivs(ld3(l.emission) * fmax2(0.0f, dot3(normal, -normToLight)) * fmax2(0.0f, dot3(normToLight, insNormal)), pdf);
         }
         case SAIL_POINT: {  // point.glsl:13-20
             V3 p = ld3(l.from) + uniformSampleSphere(u) * 0.1f;
             V3 toLight = p - hit;
-            if (testShadow(sc, hit, toLight)) return splat3(0.0f);
+            if (testShadow<F>(sc, hit, toLight)) return splat3(0.0f);
             return ld3(l.emission) * fmax2(0.0f, dot3(normalize3(toLight), insNormal));
         }
         case SAIL_SPOT: {  // spot.glsl:17-39 (axis fixed to -y)
             V3 toLight = ld3(l.from) - hit;
-            if (testShadow(sc, hit, toLight)) return splat3(0.0f);
+            if (testShadow<F>(sc, hit, toLight)) return splat3(0.0f);
             V3 normToLight = normalize3(toLight);
             float d = length3(toLight);
             V3 w = -normToLight;
@@ -431,14 +435,15 @@ SD V3 light_sample(const SailSceneBlock& sc, V2 u, V3 hit, V3 insNormal) {
 }
 
 // ---- shade(), path.glsl:1-14 ----------------------------------------------------------------------------
+template <int F>
 SD V3 shade(const SailSceneBlock& sc, const Hit& h, V2 u, V3 wo, V3& wi, V3& fpdf) {
     V3 f;
     V3 ss = normalize3(h.dpdu), ts = cross3(h.n, ss);
     wo = worldToLocal(wo, h.n, ss, ts);
-    fpdf = vclamp01(material(sc.surf[h.index], h.matCategory, h.sc, h.into, u, wo, wi, f));
+    fpdf = vclamp01(material<F>(sc.surf[h.index], h.matCategory, h.sc, h.into, u, wo, wi, f));
     wi = localToWorld(wi, h.n, ss, ts);
     V3 direct = splat3(0.0f);
-    if (isblack(h.emission) && h.matCategory == SAIL_MATTE) direct = direct + light_sample(sc, u, h.p, h.n) * f;
+    if ((F & SAIL_F_NEE) && isblack(h.emission) && h.matCategory == SAIL_MATTE) direct = direct + light_sample<F>(sc, u, h.p, h.n) * f;
     return h.emission + direct;
 }
 
@@ -451,6 +456,7 @@ struct FirstHit {
 
 // ---- trace(), path.glsl:16-38 -----------------------------------------------------------------------------
 // fx, fy, fz = gl_FragCoord.xyz.  Returns the radiance sample e.
+template <int F>
 SD V3 tracePath(const SailSceneBlock& sc, Ray ray, int maxBounces, float fx, float fy, float fz, float timeSinceStart,
                 FirstHit& first) {
     V3 fpdf = splat3(1.0f), e = splat3(0.0f);
@@ -461,14 +467,14 @@ SD V3 tracePath(const SailSceneBlock& sc, Ray ray, int maxBounces, float fx, flo
     int deepth = 0;
     while (deepth++ < maxBounces) {
         Hit h;
-        bool ok = intersectObjects(sc, ray, h);
+        bool ok = intersectObjects<F>(sc, ray, h);
         if (deepth == 1) { first.id = h.index; first.t = h.d; }
         if (!ok) break;
         if (deepth == 1) { first.n = h.n; first.p = h.p; }
         float seed = timeSinceStart + (float)deepth;
         V2 u = random2(fx, fy, fz, seed);
         V3 wi, _fpdf;
-        e = e + shade(sc, h, u, -ray.d, wi, _fpdf) * fpdf;
+        e = e + shade<F>(sc, h, u, -ray.d, wi, _fpdf) * fpdf;
         fpdf = fpdf * _fpdf;
         float outdot = dot3(h.n, wi);
         ray.o = h.p + h.n * (outdot > SAIL_EPSILON ? 0.0001f : -0.0001f);

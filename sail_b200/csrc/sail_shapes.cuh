@@ -31,6 +31,22 @@ struct Ray {
     V3 o, d;
 };
 
+// Kernel specialisation: the reference compiles only the plugins a scene uses into its trace program
+// (/root/reference/src/scene/scene.js:70-112, src/shader/generator.js:107-123).  The AOT equivalent is one
+// kernel instantiation per feature set F; code for absent features is not emitted (smaller I-cache
+// footprint, fewer registers).  A variant is chosen from the *content* of the uploaded scene.
+enum { SAIL_F_QUADRICS = 1,  // cone, cylinder, disk, hyperboloid, paraboloid present
+       SAIL_F_GLOSSY = 2,    // metal or glass present
+       SAIL_F_TEXTURED = 4,  // a uv-dependent texture (checkerboard, checkerboard2, bilerp, uvf) present
+       SAIL_F_NEE = 8,       // ln > 0: next-event estimation + shadow rays
+       SAIL_F_ALL = 15 };
+
+// Out-of-line transcendentals: one copy per kernel instead of one per call site (I-cache footprint).
+static __device__ __noinline__ float sail_sin(float x) { return dm_sin(x); }
+static __device__ __noinline__ float2 sail_sincos(float x) { float s, c; dm_sincos(x, &s, &c); return make_float2(s, c); }
+static __device__ __noinline__ float sail_acos(float x) { return dm_acos(x); }
+static __device__ __noinline__ float sail_atan2(float y, float x) { return dm_atan2(y, x); }
+
 // The winning hit (const/struct.glsl:1-13 minus the dead dpdv / seed fields).
 struct Hit {
     float d;
@@ -93,6 +109,7 @@ SD float quadricRoot(float a, float b, float c, V3 ol, V3 dl, float zLo, float z
 }
 
 // Phase 1: the value intersectX() would leave in `result.d` (MAX_DISTANCE = no hit).
+template <int F>
 SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd) {
     const float* q = s.q;
     switch (s.category) {
@@ -137,7 +154,7 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd) {
                 return SAIL_MAX_DISTANCE;
             return t;
         }
-        case SAIL_CONE: {  // cone.glsl:11-17,48-81
+        case SAIL_CONE: if (F & SAIL_F_QUADRICS) {  // cone.glsl:11-17,48-81
             if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_CONE_P));
             float k = q[SQ_CONE_K], h = q[SQ_CONE_H];
@@ -146,7 +163,7 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd) {
             float c = ol.x * ol.x + ol.y * ol.y - k * (ol.z - h) * (ol.z - h);
             return quadricRoot(a, b, c, ol, dl, -SAIL_EPSILON, h);
         }
-        case SAIL_CYLINDER: {  // cylinder.glsl:11-17,40-72
+        case SAIL_CYLINDER: if (F & SAIL_F_QUADRICS) {  // cylinder.glsl:11-17,40-72
             if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_CYL_P));
             float a = dl.x * dl.x + dl.y * dl.y;
@@ -154,7 +171,7 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd) {
             float c = ol.x * ol.x + ol.y * ol.y - q[SQ_CYL_RR];
             return quadricRoot(a, b, c, ol, dl, -SAIL_EPSILON, q[SQ_CYL_H]);
         }
-        case SAIL_DISK: {  // disk.glsl:36-53
+        case SAIL_DISK: if (F & SAIL_F_QUADRICS) {  // disk.glsl:36-53
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_DISK_P));
             if (dl.z == 0.0f) return SAIL_MAX_DISTANCE;
             float t = fdiv(-ol.z, dl.z);
@@ -165,7 +182,7 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd) {
             if (t >= SAIL_MAX_DISTANCE) return SAIL_MAX_DISTANCE;
             return t;
         }
-        case SAIL_HYPERBOLOID: {  // hyperboloid.glsl:13-24,60-90
+        case SAIL_HYPERBOLOID: if (F & SAIL_F_QUADRICS) {  // hyperboloid.glsl:13-24,60-90
             if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_HYP_P));
             float ah = q[SQ_HYP_AH], ch = q[SQ_HYP_CH];
@@ -174,7 +191,7 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd) {
             float c = ah * ol.x * ol.x + ah * ol.y * ol.y - ch * ol.z * ol.z - 1.0f;
             return quadricRoot(a, b, c, ol, dl, q[SQ_HYP_ZMIN], q[SQ_HYP_ZMAX]);
         }
-        case SAIL_PARABOLOID: {  // paraboloid.glsl:12-20,51-82
+        case SAIL_PARABOLOID: if (F & SAIL_F_QUADRICS) {  // paraboloid.glsl:12-20,51-82
             if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_PAR_P));
             float k = q[SQ_PAR_K];
@@ -189,13 +206,14 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd) {
 
 // shader.shape.js:28-37: nearest object by strict `<` in ascending index.  Returns the object index
 // or -1; `best` receives ins.d.
-SD int nearestObject(const SailSceneBlock& sc, const Ray& ray, float& best) {
+template <int F>
+static __device__ __noinline__ int nearestObject(const SailSceneBlock& sc, const Ray& ray, float& best) {
     V3 rd = mk3(dm_rcp(ray.d.x), dm_rcp(ray.d.y), dm_rcp(ray.d.z));
     best = SAIL_MAX_DISTANCE;
     int id = -1;
     const int n = sc.n;
     for (int i = 0; i < n; i++) {
-        float t = shapeDistance(sc.shape[i], ray, rd);
+        float t = shapeDistance<F>(sc.shape[i], ray, rd);
         if (t < best) { best = t; id = i; }
     }
     return id;
@@ -206,9 +224,10 @@ SD bool textureNeedsUV(int texCategory) {
     return texCategory == SAIL_CHECKERBOARD || texCategory == SAIL_CHECKERBOARD2 || texCategory == SAIL_BILERP ||
            texCategory == SAIL_UVF;
 }
+template <int F>
 SD V3 surfaceColor(const SailSurface& u, V2 uv) {
     const float* t = u.t;
-    switch (u.texCategory) {
+    if (F & SAIL_F_TEXTURED) switch (u.texCategory) {
         case SAIL_CHECKERBOARD: {  // checkerboard.glsl:6-20
             float ax = uv.x * t[13], ay = uv.y * t[13], width = t[14];
             float fx = ax - dm_floor(ax), fy = ay - dm_floor(ay);
@@ -231,7 +250,7 @@ SD V3 surfaceColor(const SailSurface& u, V2 uv) {
 }
 
 SD float azimuthU(float hx, float hy) {  // phi = atan(y,x); if (phi<0) phi += 2PI; u = phi/(2PI)
-    float phi = dm_atan2(hy, hx);
+    float phi = sail_atan2(hy, hx);
     if (phi < 0.0f) phi += SAIL_TWO_PI;
     return phi * SAIL_RCP_TWO_PI;
 }
@@ -253,12 +272,13 @@ SD V3 boxDpdu(V3 normal) {  // cube.glsl:40-48
 
 // Phase 2: the full hit record of object `i` at distance `t` (the body of intersectX() after the hit
 // test, the per-arm emission mask of shader.shape.js:47-49 and the tail of :38-40).
+template <int F>
 SD void hitRecord(const SailSceneBlock& sc, int i, float t, const Ray& ray, Hit& h) {
     const SailShape& s = sc.shape[i];
     const SailSurface& u = sc.surf[i];
     const float* q = s.q;
-    const bool wantUV = textureNeedsUV(u.texCategory);
-    V3 gn;  // geometric normal as intersectX() returns it
+    const bool wantUV = (F & SAIL_F_TEXTURED) && textureNeedsUV(u.texCategory);
+    V3 gn = splat3(0.0f);  // geometric normal as intersectX() returns it
     V2 uv = mk2(0.0f, 0.0f);
     h.d = t;
     h.index = i;
@@ -274,7 +294,7 @@ SD void hitRecord(const SailSceneBlock& sc, int i, float t, const Ray& ray, Hit&
                 else if (hs.y < mn.y + 0.0001f || hs.y > mx.y - 0.0001f) uv = mk2(fdiv(hs.x, tr.x), fdiv(hs.z, tr.z));
                 else uv = mk2(fdiv(hs.x, tr.x), fdiv(hs.y, tr.y));
             }
-            h.sc = surfaceColor(u, uv);
+            h.sc = surfaceColor<F>(u, uv);
             break;
         }
         case SAIL_CORNELLBOX: {  // cornellbox.glsl:23-37,81-88
@@ -295,7 +315,7 @@ SD void hitRecord(const SailSceneBlock& sc, int i, float t, const Ray& ray, Hit&
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - c);
             V3 hl = ol + t * dl;
             float r = q[SQ_SPH_R];
-            float theta = dm_acos(fclamp(hl.z * q[SQ_SPH_INVR], -1.0f, 1.0f));
+            float theta = sail_acos(fclamp(hl.z * q[SQ_SPH_INVR], -1.0f, 1.0f));
             if (wantUV) {
                 float gx = hl.x;
                 if (hl.x == 0.0f && hl.y == 0.0f) gx = 1e-5f * r;  // guards phi only (Q18)
@@ -305,9 +325,9 @@ SD void hitRecord(const SailSceneBlock& sc, int i, float t, const Ray& ray, Hit&
             float invZRadius = dm_rcp(zRadius);
             float cosPhi = hl.x * invZRadius, sinPhi = hl.y * invZRadius;
             V3 dpdu = dpduAround(hl.x, hl.y);
-            V3 dpdv = SAIL_PI * mk3(hl.z * cosPhi, hl.z * sinPhi, -r * dm_sin(theta));
+            V3 dpdv = SAIL_PI * mk3(hl.z * cosPhi, hl.z * sinPhi, -r * sail_sin(theta));
             V3 nl = normalize3(cross3(dpdv, dpdu));
-            h.sc = surfaceColor(u, uv);
+            h.sc = surfaceColor<F>(u, uv);
             h.p = objToWorld(hl) + c;
             gn = objToWorld(nl);
             h.dpdu = objToWorld(dpdu);
@@ -319,13 +339,13 @@ SD void hitRecord(const SailSceneBlock& sc, int i, float t, const Ray& ray, Hit&
             V3 ol = worldToLocal(ray.o - mn, nn, ss, ts);
             V3 hl = ol + t * dl;
             if (wantUV) uv = mk2(hl.x * q[SQ_RECT_INVMAXX], hl.y * q[SQ_RECT_INVMAXY]);
-            h.sc = surfaceColor(u, uv);
+            h.sc = surfaceColor<F>(u, uv);
             h.p = localToWorld(hl, nn, ss, ts) + mn;
             gn = nn;
             h.dpdu = ld3(q + SQ_RECT_DPDU);
             break;
         }
-        case SAIL_CONE: {  // cone.glsl:31-36,83-98
+        case SAIL_CONE: if (F & SAIL_F_QUADRICS) {  // cone.glsl:31-36,83-98
             V3 p = ld3(q + SQ_CONE_P);
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - p);
             V3 hl = ol + t * dl;
@@ -335,13 +355,13 @@ SD void hitRecord(const SailSceneBlock& sc, int i, float t, const Ray& ray, Hit&
             float inv = dm_rcp(1.0f - v);
             V3 dpdv = mk3(-hl.x * inv, -hl.y * inv, q[SQ_CONE_H]);
             V3 nl = normalize3(cross3(dpdu, dpdv));
-            h.sc = surfaceColor(u, uv);
+            h.sc = surfaceColor<F>(u, uv);
             h.p = objToWorld(hl) + p;
             gn = objToWorld(nl);
             h.dpdu = objToWorld(dpdu);
             break;
         }
-        case SAIL_CYLINDER: {  // cylinder.glsl:31-34,74-89
+        case SAIL_CYLINDER: if (F & SAIL_F_QUADRICS) {  // cylinder.glsl:31-34,74-89
             V3 p = ld3(q + SQ_CYL_P);
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - p);
             V3 hl = ol + t * dl;
@@ -349,13 +369,13 @@ SD void hitRecord(const SailSceneBlock& sc, int i, float t, const Ray& ray, Hit&
             V3 dpdu = dpduAround(hl.x, hl.y);
             V3 dpdv = mk3(0.0f, 0.0f, q[SQ_CYL_H]);
             V3 nl = normalize3(cross3(dpdu, dpdv));
-            h.sc = surfaceColor(u, uv);
+            h.sc = surfaceColor<F>(u, uv);
             h.p = objToWorld(hl) + p;
             gn = objToWorld(nl);
             h.dpdu = objToWorld(dpdu);
             break;
         }
-        case SAIL_DISK: {  // disk.glsl:27-30,55-74
+        case SAIL_DISK: if (F & SAIL_F_QUADRICS) {  // disk.glsl:27-30,55-74
             V3 p = ld3(q + SQ_DISK_P);
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - p);
             V3 hl = ol + t * dl;
@@ -368,34 +388,34 @@ SD void hitRecord(const SailSceneBlock& sc, int i, float t, const Ray& ray, Hit&
             V3 dpdu = dpduAround(hl.x, hl.y);
             V3 dpdv = vdivs(mk3(hl.x, hl.y, 0.0f) * q[SQ_DISK_DIFF], rHit);
             V3 nl = normalize3(cross3(dpdu, dpdv));
-            h.sc = surfaceColor(u, uv);
+            h.sc = surfaceColor<F>(u, uv);
             h.p = objToWorld(hl) + p;
             gn = objToWorld(nl);
             h.dpdu = objToWorld(dpdu);
             break;
         }
-        case SAIL_HYPERBOLOID: {  // hyperboloid.glsl:41-46,92-110
+        case SAIL_HYPERBOLOID: if (F & SAIL_F_QUADRICS) {  // hyperboloid.glsl:41-46,92-110
             V3 p = ld3(q + SQ_HYP_P), p1 = ld3(q + SQ_HYP_P1), p2 = ld3(q + SQ_HYP_P2);
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - p);
             V3 hl = ol + t * dl;
             float v = (hl.z - p1.z) * q[SQ_HYP_INVDZ];
             V3 pr = (1.0f - v) * p1 + v * p2;
-            float phi = dm_atan2(pr.x * hl.y - hl.x * pr.y, hl.x * pr.x + hl.y * pr.y);
+            float phi = sail_atan2(pr.x * hl.y - hl.x * pr.y, hl.x * pr.x + hl.y * pr.y);
             if (phi < 0.0f) phi += SAIL_TWO_PI;
             uv = mk2(phi * SAIL_RCP_TWO_PI, v);
-            float sinPhi, cosPhi;
-            dm_sincos(phi, &sinPhi, &cosPhi);
+            float2 scp = sail_sincos(phi);
+            float sinPhi = scp.x, cosPhi = scp.y;
             V3 dpdu = dpduAround(hl.x, hl.y);
             V3 dpdv = mk3((p2.x - p1.x) * cosPhi - (p2.y - p1.y) * sinPhi, (p2.x - p1.x) * sinPhi + (p2.y - p1.y) * cosPhi,
                           p2.z - p1.z);
             V3 nl = normalize3(cross3(dpdu, dpdv));
-            h.sc = surfaceColor(u, uv);
+            h.sc = surfaceColor<F>(u, uv);
             h.p = objToWorld(hl) + p;
             gn = objToWorld(nl);
             h.dpdu = objToWorld(dpdu);
             break;
         }
-        default: {  // SAIL_PARABOLOID: paraboloid.glsl:35-40,84-102
+        default: if (F & SAIL_F_QUADRICS) {  // SAIL_PARABOLOID: paraboloid.glsl:35-40,84-102
             V3 p = ld3(q + SQ_PAR_P);
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - p);
             V3 hl = ol + t * dl;
@@ -404,7 +424,7 @@ SD void hitRecord(const SailSceneBlock& sc, int i, float t, const Ray& ray, Hit&
             float inv = dm_rcp(2.0f * hl.z);
             V3 dpdv = q[SQ_PAR_DZ] * mk3(hl.x * inv, hl.y * inv, 1.0f);
             V3 nl = normalize3(cross3(dpdu, dpdv));
-            h.sc = surfaceColor(u, uv);
+            h.sc = surfaceColor<F>(u, uv);
             h.p = objToWorld(hl) + p;
             gn = objToWorld(nl);
             h.dpdu = objToWorld(dpdu);
@@ -422,23 +442,25 @@ SD void hitRecord(const SailSceneBlock& sc, int i, float t, const Ray& ray, Hit&
 }
 
 // intersectObjects() as one call (shader.shape.js:28-51).  Returns false on a miss.
+template <int F>
 SD bool intersectObjects(const SailSceneBlock& sc, const Ray& ray, Hit& h) {
     float t;
-    int id = nearestObject(sc, ray, t);
+    int id = nearestObject<F>(sc, ray, t);
     h.d = t;
     h.index = id;
     if (id < 0) return false;
-    hitRecord(sc, id, t, ray, h);
+    hitRecord<F>(sc, id, t, ray, h);
     return true;
 }
 
 // testShadow(), shader.light.js:24-31: distance only.
+template <int F>
 SD bool testShadow(const SailSceneBlock& sc, V3 origin, V3 toLight) {
     Ray r;
     r.o = origin;
     r.d = toLight;
     float d;
-    nearestObject(sc, r, d);
+    nearestObject<F>(sc, r, d);
     return d > SAIL_EPSILON && d < SAIL_ONEMINUSEPSILON;
 }
 
