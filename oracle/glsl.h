@@ -10,7 +10,8 @@
 //   * a / b      := a * rcp(b), rcp correctly rounded  (what shader compilers emit; GLSL ES 3.00 4.5.1).
 //   * sqrt       := correctly rounded.
 //   * sin, cos, tan, atan, acos, asin, exp, log, pow := sail_b200/csrc/detmath.h (shared, deterministic).
-//   * min/max    := NaN-suppressing (C fminf/fmaxf behaviour), first operand wins signed-zero ties.
+//   * min/max    := a NaN operand yields the other operand; -0 orders below +0 (IEEE 754-2019 minimumNumber /
+//                   maximumNumber, which is what the sm_100a FMNMX instruction computes).
 //   * normalize(v) := v * rcp(sqrt(dot(v,v))); length(v) := sqrt(dot(v,v)).
 //   * unwritten `out` parameters and uninitialised locals read as 0: `real` and the
 //     vector types zero-initialise.

@@ -36,17 +36,25 @@ def frame_uniforms(scene, k, W, H, schedule=None):
     return m, np.asarray(scene.eye, np.float32), k / (k + 1.0), s.time(k)
 
 
+def _canon(a):
+    """float32 bits with every NaN mapped to one pattern (x86 and sm_100a generate different default NaNs)."""
+    a = np.ascontiguousarray(a, np.float32)
+    bits = a.view(np.uint32).copy()
+    bits[np.isnan(a)] = 0x7FC00000
+    return bits
+
+
 def bits_equal(a, b):
-    """Bit-exact float comparison (NaN payloads included)."""
+    """Bit-exact float comparison (signed zeros and infinities included; NaN == NaN)."""
     a = np.ascontiguousarray(a, np.float32)
     b = np.ascontiguousarray(b, np.float32)
-    return a.shape == b.shape and np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    return a.shape == b.shape and np.array_equal(_canon(a), _canon(b))
 
 
 def mismatch_report(a, b, name):
     a = np.ascontiguousarray(a, np.float32)
     b = np.ascontiguousarray(b, np.float32)
-    bad = a.view(np.uint32) != b.view(np.uint32)
+    bad = _canon(a) != _canon(b)
     if not bad.any():
         return ""
     idx = np.argwhere(bad)[:5]
