@@ -125,6 +125,17 @@ int sail_upload_scene(sail_ctx* ctx, const float* objects, int32_t n, const floa
 /* Tracer.updateObjects(scene): src/core/tracer.js:25-40 (objects table only; n may change). */
 int sail_upload_objects(sail_ctx* ctx, const float* objects, int32_t n);
 
+/* Validates the three tables exactly as sail_upload_scene() would (no device needed) and returns the
+ * kernel feature bits the scene content selects (1 quadrics, 2 metal/glass, 4 uv textures, 8 lights), or a
+ * negative SAIL_ERR_*.  `err` (may be NULL) receives the message. */
+int sail_scene_features(const float* objects, int32_t n, const float* texparams, int32_t tn, const float* lights,
+                        int32_t ln, char* err, int32_t errlen);
+
+/* Tile sharding with interleaved bands: this context renders the rows y with
+ * (y / band_rows) % band_stride == band_first (band_rows a multiple of 8).  band_stride = 1 restores the
+ * contiguous [row_begin, row_end) range of sail_create(). */
+int sail_set_row_bands(sail_ctx* ctx, int32_t band_rows, int32_t band_stride, int32_t band_first);
+
 /* Clears the accumulation and AOV buffers (a fresh frameCache; the reference instead restarts the running
  * mean with textureWeight = 0 when scene.sampleCount is reset, src/core/renderer.js:57-60). */
 int sail_reset(sail_ctx* ctx);

@@ -57,6 +57,8 @@ _SIGNATURES = {
     "sail_configure": (ctypes.c_int, [_P, ctypes.POINTER(Config)]),
     "sail_upload_scene": (ctypes.c_int, [_P, _P, ctypes.c_int32, _P, ctypes.c_int32, _P, ctypes.c_int32]),
     "sail_upload_objects": (ctypes.c_int, [_P, _P, ctypes.c_int32]),
+    "sail_scene_features": (ctypes.c_int, [_P, ctypes.c_int32, _P, ctypes.c_int32, _P, ctypes.c_int32, ctypes.c_char_p, ctypes.c_int32]),
+    "sail_set_row_bands": (ctypes.c_int, [_P, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32]),
     "sail_reset": (ctypes.c_int, [_P]),
     "sail_render": (ctypes.c_int, [_P, _P, _P, ctypes.c_float, ctypes.c_float]),
     "sail_render_n": (ctypes.c_int, [_P, ctypes.POINTER(Frame), ctypes.c_int32]),
@@ -190,6 +192,9 @@ class Context:
     def reset(self):
         self._check(self.lib.sail_reset(self._h))
 
+    def set_row_bands(self, band_rows, band_stride, band_first):
+        self._check(self.lib.sail_set_row_bands(self._h, int(band_rows), int(band_stride), int(band_first)))
+
     # ---- rendering ------------------------------------------------------------------------------------
     def render(self, matrix, eye, textureWeight, timeSinceStart):
         m, e = _f32(matrix, 16), _f32(eye, 3)
@@ -282,6 +287,17 @@ class Context:
         out = np.empty_like(a)
         self._check(self.lib.sail_eval_math(self._h, names[which], _ptr(a), _ptr(bb), _ptr(out), a.size))
         return out
+
+
+def scene_features(objects, texparams, lights):
+    """Validate tables without a device; returns the feature bits or raises SailError."""
+    o, t, l = _f32(objects).reshape(-1), _f32(texparams).reshape(-1), _f32(lights).reshape(-1)
+    err = ctypes.create_string_buffer(256)
+    rc = load().sail_scene_features(_ptr(o) if o.size else None, o.size // 18, _ptr(t) if t.size else None, t.size // 16,
+                                    _ptr(l) if l.size else None, l.size // 18, err, 256)
+    if rc < 0:
+        raise SailError(rc, err.value.decode())
+    return rc
 
 
 def frame_array(frames):

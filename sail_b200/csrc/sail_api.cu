@@ -23,6 +23,7 @@
 struct sail_ctx {
     int device = 0;
     int W = 0, H = 0, y0 = 0, y1 = 0;
+    int bandRows = 0, bandStride = 1, bandFirst = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t evStart = nullptr, evStop = nullptr;
     bool timed = false;
@@ -238,6 +239,26 @@ int sail_upload_objects(sail_ctx* ctx, const float* objects, int32_t n) {
     return uploadBlock(ctx);
 }
 
+int sail_scene_features(const float* objects, int32_t n, const float* texparams, int32_t tn, const float* lights,
+                        int32_t ln, char* err, int32_t errlen) {
+    SailSceneBlock* blk = new (std::nothrow) SailSceneBlock;
+    if (!blk) return SAIL_ERR_NOMEM;
+    int rc = sail_pack_scene(objects, n, texparams, tn, lights, ln, blk, err, errlen);
+    int feat = blk->features;
+    delete blk;
+    return rc ? rc : feat;
+}
+
+int sail_set_row_bands(sail_ctx* ctx, int32_t band_rows, int32_t band_stride, int32_t band_first) {
+    if (!ctx) return SAIL_ERR_INVALID;
+    if (band_stride < 1 || band_first < 0 || band_first >= band_stride || band_rows < SAIL_TILE_H || band_rows % SAIL_TILE_H)
+        return setErr(ctx, SAIL_ERR_INVALID, "bad row bands: rows %d (multiple of %d), stride %d, first %d", band_rows, SAIL_TILE_H, band_stride, band_first);
+    ctx->bandRows = band_rows;
+    ctx->bandStride = band_stride;
+    ctx->bandFirst = band_first;
+    return SAIL_OK;
+}
+
 int sail_reset(sail_ctx* ctx) {
     if (!ctx || !ctx->accum) return SAIL_ERR_INVALID;
     CU(cudaSetDevice(ctx->device));
@@ -257,6 +278,16 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
     CU(cudaSetDevice(ctx->device));
     SailLaunch L;
     L.W = ctx->W; L.H = ctx->H; L.y0 = ctx->y0; L.y1 = ctx->y1;
+    L.bandRows = ctx->bandRows; L.bandStride = ctx->bandStride; L.bandFirst = ctx->bandFirst;
+    int tileRows = (ctx->y1 - ctx->y0 + SAIL_TILE_H - 1) / SAIL_TILE_H;
+    if (ctx->bandStride > 1) {  // interleaved bands over the whole image
+        int nbands = (ctx->H + ctx->bandRows - 1) / ctx->bandRows;
+        int mine = (nbands - ctx->bandFirst + ctx->bandStride - 1) / ctx->bandStride;
+        if (mine < 0) mine = 0;
+        tileRows = mine * (ctx->bandRows / SAIL_TILE_H);
+        L.y0 = 0; L.y1 = ctx->H;
+        if (tileRows == 0) return SAIL_OK;
+    }
     L.maxBounces = ctx->cfg.max_bounces;
     L.nframes = count;
     L.accumMode = ctx->cfg.accum_mode;
@@ -273,7 +304,7 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
         ctx->launches += launched;
         if (e != cudaSuccess) return setErr(ctx, SAIL_ERR_CUDA, "wavefront render failed: %s", cudaGetErrorString(e));
     } else {
-        dim3 grid((ctx->W + SAIL_TILE_W - 1) / SAIL_TILE_W, (ctx->y1 - ctx->y0 + SAIL_TILE_H - 1) / SAIL_TILE_H);
+        dim3 grid((ctx->W + SAIL_TILE_W - 1) / SAIL_TILE_W, tileRows);
         // the variant follows the scene's content, never the caller's mask hints
         CU(launchMega(ctx->hostScene.features & SAIL_F_ALL, L, grid, ctx->stream));
         ctx->launches++;

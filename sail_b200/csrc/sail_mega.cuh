@@ -35,6 +35,7 @@ struct SailFrameDev {
 struct SailLaunch {
     int W, H;
     int y0, y1;          // rows rendered by this launch
+    int bandRows, bandStride, bandFirst;  // interleaved row bands (bandStride > 1), see sail_set_row_bands()
     int maxBounces;
     int nframes;
     int accumMode;       // SAIL_ACCUM_*
@@ -78,7 +79,12 @@ __global__ void __launch_bounds__(SAIL_CTA_THREADS) sail_trace_megakernel(const 
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int x = blockIdx.x * SAIL_TILE_W + (warp & 1) * 8 + (lane & 7);
-    const int y = L.y0 + blockIdx.y * SAIL_TILE_H + (warp >> 1) * 4 + (lane >> 3);
+    int tileY = L.y0 + blockIdx.y * SAIL_TILE_H;
+    if (L.bandStride > 1) {
+        const int tpb = L.bandRows / SAIL_TILE_H;
+        tileY = (L.bandFirst + ((int)blockIdx.y / tpb) * L.bandStride) * L.bandRows + ((int)blockIdx.y % tpb) * SAIL_TILE_H;
+    }
+    const int y = tileY + (warp >> 1) * 4 + (lane >> 3);
     if (x >= L.W || y >= L.y1) return;
 
     const size_t pix = (size_t)y * L.W + x;

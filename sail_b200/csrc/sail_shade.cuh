@@ -250,9 +250,8 @@ SD V3 material(const SailSurface& su, int matCategory, V3 sc, bool into, V2 u, V
         case SAIL_MIRROR: {  // mirror.glsl:5-16, bsdf.glsl:93-98 with the no-op Fresnel (= WHITE)
             V3 R = m[SM_MIRROR_KR] * sc;
             wi = mk3(-wo.x, -wo.y, wo.z);
-            pdf = 1.0f;
             fs = vdivs(splat3(1.0f) * R, absCosTheta(wi));
-            break;
+            return fs * absCosTheta(wi);  // pdf = 1: `/ pdf` multiplies by rcp(1) = 1 exactly
         }
         case SAIL_METAL: if (F & SAIL_F_GLOSSY) {  // metal.glsl:8-23
             MicroR mr;
@@ -438,7 +437,8 @@ SD V3 light_sample(const SailSceneBlock& sc, V2 u, V3 hit, V3 insNormal) {
 template <int F>
 SD V3 shade(const SailSceneBlock& sc, const Hit& h, V2 u, V3 wo, V3& wi, V3& fpdf) {
     V3 f;
-    V3 ss = normalize3(h.dpdu), ts = cross3(h.n, ss);
+    // box faces: |dpdu| is exactly 1 (components 0 / +-1), so normalize() multiplies by rcp(sqrt(1)) = 1
+    V3 ss = h.unitDpdu ? h.dpdu : normalize3(h.dpdu), ts = cross3(h.n, ss);
     wo = worldToLocal(wo, h.n, ss, ts);
     fpdf = vclamp01(material<F>(sc.surf[h.index], h.matCategory, h.sc, h.into, u, wo, wi, f));
     wi = localToWorld(wi, h.n, ss, ts);

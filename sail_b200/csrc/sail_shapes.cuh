@@ -55,6 +55,7 @@ struct Hit {
     V3 sc, emission;
     int matCategory;
     bool into;
+    bool unitDpdu;   // dpdu is an exact axis unit vector (box faces): normalize() is the identity
 };
 
 // ---- util/utility.glsl:37-51 -----------------------------------------------------------------
@@ -113,19 +114,12 @@ template <int F>
 SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd) {
     const float* q = s.q;
     switch (s.category) {
-        case SAIL_CUBE: {  // cube.glsl:65-79
-            float tNear, tFar;
-            slab(ld3(s.lo), ld3(s.hi), ray.o, rd, tNear, tFar);
-            float t = -1.0f;
-            if (tNear > SAIL_EPSILON && tNear < tFar) t = tNear;
-            else if (tNear < tFar) t = tFar;
-            return (t > SAIL_EPSILON) ? t : SAIL_MAX_DISTANCE;
-        }
+        case SAIL_CUBE:          // cube.glsl:65-79: the near slab hit if it is in front, else the far one
         case SAIL_CORNELLBOX: {  // cornellbox.glsl:67-81: always the far slab hit
             float tNear, tFar;
             slab(ld3(s.lo), ld3(s.hi), ray.o, rd, tNear, tFar);
             float t = -1.0f;
-            if (tNear < tFar) t = tFar;
+            if (tNear < tFar) t = (s.category == SAIL_CUBE && tNear > SAIL_EPSILON) ? tNear : tFar;
             return (t > SAIL_EPSILON) ? t : SAIL_MAX_DISTANCE;
         }
         case SAIL_SPHERE: {  // sphere.glsl:10-16,45-62
@@ -204,19 +198,33 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd) {
     return SAIL_MAX_DISTANCE;
 }
 
-// shader.shape.js:28-37: nearest object by strict `<` in ascending index.  Returns the object index
-// or -1; `best` receives ins.d.
+// shader.shape.js:28-37: nearest object by strict `<` in ascending index.  Returns (ins.d, object index
+// or -1).  Out of line (one copy serves primary/bounce rays and shadow rays); everything travels in
+// registers -- the scene block is addressed by its shared-memory window offset.
+struct Nearest {
+    float t;
+    int id;
+};
 template <int F>
-static __device__ __noinline__ int nearestObject(const SailSceneBlock& sc, const Ray& ray, float& best) {
-    V3 rd = mk3(dm_rcp(ray.d.x), dm_rcp(ray.d.y), dm_rcp(ray.d.z));
-    best = SAIL_MAX_DISTANCE;
-    int id = -1;
+static __device__ __noinline__ Nearest nearestObjectRegs(unsigned scAddr, float ox, float oy, float oz, float dx, float dy, float dz) {
+    const SailSceneBlock& sc = *reinterpret_cast<const SailSceneBlock*>(__cvta_shared_to_generic(scAddr));
+    Ray ray;
+    ray.o = mk3(ox, oy, oz);
+    ray.d = mk3(dx, dy, dz);
+    V3 rd = mk3(dm_rcp(dx), dm_rcp(dy), dm_rcp(dz));
+    Nearest r;
+    r.t = SAIL_MAX_DISTANCE;
+    r.id = -1;
     const int n = sc.n;
     for (int i = 0; i < n; i++) {
         float t = shapeDistance<F>(sc.shape[i], ray, rd);
-        if (t < best) { best = t; id = i; }
+        if (t < r.t) { r.t = t; r.id = i; }
     }
-    return id;
+    return r;
+}
+template <int F>
+SD Nearest nearestObject(const SailSceneBlock& sc, const Ray& ray) {
+    return nearestObjectRegs<F>((unsigned)__cvta_generic_to_shared(&sc), ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z);
 }
 
 // ---- procedural textures (texture/shader.texture.js:22-29) -------------------------------------
@@ -282,6 +290,7 @@ SD void hitRecord(const SailSceneBlock& sc, int i, float t, const Ray& ray, Hit&
     V2 uv = mk2(0.0f, 0.0f);
     h.d = t;
     h.index = i;
+    h.unitDpdu = (s.category == SAIL_CUBE || s.category == SAIL_CORNELLBOX);
     switch (s.category) {
         case SAIL_CUBE: {  // cube.glsl:79-85
             V3 mn = ld3(s.lo), mx = ld3(s.hi);
@@ -444,12 +453,11 @@ SD void hitRecord(const SailSceneBlock& sc, int i, float t, const Ray& ray, Hit&
 // intersectObjects() as one call (shader.shape.js:28-51).  Returns false on a miss.
 template <int F>
 SD bool intersectObjects(const SailSceneBlock& sc, const Ray& ray, Hit& h) {
-    float t;
-    int id = nearestObject<F>(sc, ray, t);
-    h.d = t;
-    h.index = id;
-    if (id < 0) return false;
-    hitRecord<F>(sc, id, t, ray, h);
+    Nearest nr = nearestObject<F>(sc, ray);
+    h.d = nr.t;
+    h.index = nr.id;
+    if (nr.id < 0) return false;
+    hitRecord<F>(sc, nr.id, nr.t, ray, h);
     return true;
 }
 
@@ -459,8 +467,7 @@ SD bool testShadow(const SailSceneBlock& sc, V3 origin, V3 toLight) {
     Ray r;
     r.o = origin;
     r.d = toLight;
-    float d;
-    nearestObject<F>(sc, r, d);
+    float d = nearestObject<F>(sc, r).t;
     return d > SAIL_EPSILON && d < SAIL_ONEMINUSEPSILON;
 }
 
