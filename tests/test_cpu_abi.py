@@ -1,0 +1,99 @@
+"""CPU-side checks of the drop-in boundary: the C-ABI library loads, exports every symbol that
+include/sail_b200.h declares, its structs have the documented layout, validation works without a
+device, and the product path fails loudly (no CPU fallback) when no GPU is present."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, scene_tables
+
+HEADER = os.path.join(ROOT, "include", "sail_b200.h")
+
+
+@pytest.fixture(scope="module")
+def capi():
+    from sail_b200 import capi as c
+    if not os.path.exists(c.LIB_PATH):
+        c.build()
+    return c
+
+
+def declared_functions():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(sail_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_header_declares_and_library_exports(capi):
+    names = declared_functions()
+    assert len(names) >= 25
+    lib = ctypes.CDLL(capi.LIB_PATH)
+    missing = [n for n in names if not hasattr(lib, n)]
+    assert not missing, "declared in include/sail_b200.h but not exported: %s" % missing
+    # the Python binding covers exactly the declared surface
+    assert sorted(capi.EXPORTED_SYMBOLS) == names
+
+
+def test_struct_layouts(capi):
+    assert ctypes.sizeof(capi.CreateInfo) == 32
+    assert ctypes.sizeof(capi.Config) == 4 * 4 + 5 * 4 + 4 + 8 + 64 + 16
+    assert ctypes.sizeof(capi.Frame) == 84
+    assert capi.Frame.eye.offset == 64 and capi.Frame.textureWeight.offset == 76
+    assert capi.Config.filter_weights.offset == 48
+
+
+def test_version_and_defaults(capi):
+    lib = capi.load()
+    assert lib.sail_abi_version() == 1
+    assert b"sm_100a" in lib.sail_version()
+    cfg = capi.Config()
+    lib.sail_default_config(ctypes.byref(cfg))
+    assert cfg.max_bounces == 5 and cfg.trace_id == 0 and cfg.accum_mode == capi.ACCUM_MEAN
+    assert cfg.filter_id == 0 and cfg.kernel == capi.KERNEL_MEGA
+
+
+def test_no_cpu_fallback(capi):
+    """Without a B200 the library must refuse to create a context (and never render on the host)."""
+    if capi.device_count() > 0:
+        pytest.skip("a GPU is present")
+    with pytest.raises(capi.SailError) as ei:
+        capi.Context(64, 64)
+    assert ei.value.code == capi.ERR_CUDA
+    assert "no CPU path" in str(ei.value) or "CUDA" in str(ei.value)
+
+
+def test_product_does_not_touch_oracle():
+    """Nothing under sail_b200/ (the product) may import, link or execute oracle/."""
+    bad = []
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "sail_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")) or f == "Makefile":
+                txt = open(os.path.join(dirpath, f), errors="ignore").read()
+                if re.search(r"^\s*(import|from)\s+oracle\b", txt, flags=re.M) or "liboracle" in txt or '"../../oracle' in txt:
+                    bad.append(f)
+    assert not bad, bad
+
+
+@pytest.mark.parametrize("cfg,expect", [(1, 0), (2, 2 | 8), (3, 15), (5, 2 | 8)])
+def test_scene_features_select_kernel_variant(capi, cfg, expect):
+    _, o, t, l, _ = scene_tables(cfg, 64, 64)
+    assert capi.scene_features(o, t, l) == expect
+
+
+def test_upload_validation_without_device(capi):
+    _, o, t, l, _ = scene_tables(2, 64, 64)
+    bad = o.copy()
+    bad[1, 0] = 17  # unknown shape category
+    with pytest.raises(capi.SailError) as ei:
+        capi.scene_features(bad, t, l)
+    assert ei.value.code == capi.ERR_INVALID and "object 1" in str(ei.value)
+    many = np.tile(o[:1], (65, 1))
+    with pytest.raises(capi.SailError):
+        capi.scene_features(many, t, l)
+    # empty scene and single-row tables (the n-1 = 0 divisions of SURVEY.md Q5) are accepted
+    z18, z16 = np.zeros((0, 18), np.float32), np.zeros((0, 16), np.float32)
+    assert capi.scene_features(z18, z16, z18) == 0
+    assert capi.scene_features(o[:1], t[:2], l[:1]) >= 0

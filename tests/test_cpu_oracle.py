@@ -1,0 +1,167 @@
+"""The oracle against (1) the committed golden fixtures and (2) known-answer tests with analytic results.
+
+The reference has no tests or golden vectors and cannot be run on this box, so parity is
+UNPINNED against the reference itself; these tests pin the oracle's behaviour to independent analytic
+answers and to a committed fixture (tests/golden/oracle_v1.npz, made by tests/golden/make_golden.py)."""
+import math
+import os
+
+import numpy as np
+import pytest
+
+import sail_b200 as Sail
+from conftest import ROOT, bits_equal, frame_uniforms, scene_tables
+from sail_b200 import schedule, wire
+
+GOLD = np.load(os.path.join(ROOT, "tests", "golden", "oracle_v1.npz"))
+SIZES = {1: (32, 32), 2: (48, 27), 3: (48, 27), 5: (48, 27)}
+
+
+@pytest.mark.parametrize("cfg", [1, 2, 3, 5])
+def test_oracle_matches_golden(oracle, cfg):
+    W, H = SIZES[cfg]
+    scene, o, t, l, bounces = scene_tables(cfg, W, H)
+    assert np.array_equal(o, GOLD["c%d_objects" % cfg]) and np.array_equal(t, GOLD["c%d_texparams" % cfg])
+    assert np.array_equal(l, GOLD["c%d_lights" % cfg])
+    oracle.set_scene(o, t, l)
+    acc = np.zeros((H, W, 3), np.float32)
+    for k in range(2):
+        m, eye, w, tm = frame_uniforms(scene, k, W, H)
+        r = oracle.render_frame(W, H, m, eye, w, tm, acc, max_bounces=bounces, aovs=True)
+    assert np.array_equal(r["hit_id"], GOLD["c%d_hit_id" % cfg])
+    assert bits_equal(r["depth"], GOLD["c%d_depth" % cfg]) and bits_equal(r["normal"], GOLD["c%d_normal" % cfg])
+    assert bits_equal(acc, GOLD["c%d_color" % cfg])
+
+
+def test_detmath_golden_and_accuracy(oracle):
+    xs, us = GOLD["dm_x"], GOLD["dm_u"]
+    for name in ("sin", "cos", "tan", "atan", "exp"):
+        assert bits_equal(oracle.detmath(name, xs), GOLD["dm_" + name]), name
+    assert bits_equal(oracle.detmath("acos", us), GOLD["dm_acos"]) and bits_equal(oracle.detmath("asin", us), GOLD["dm_asin"])
+    rng = np.random.default_rng(1)
+    x = rng.uniform(-3e5, 3e5, 200000).astype(np.float32)
+    assert np.max(np.abs(oracle.detmath("sin", x) - np.sin(x.astype(np.float64)))) < 4e-7
+    assert np.max(np.abs(oracle.detmath("cos", x) - np.cos(x.astype(np.float64)))) < 4e-7
+    u = rng.uniform(-1, 1, 100000).astype(np.float32)
+    assert np.max(np.abs(oracle.detmath("acos", u) - np.arccos(u.astype(np.float64)))) < 5e-7
+    a = rng.normal(size=100000).astype(np.float32)
+    b = rng.normal(size=100000).astype(np.float32)
+    assert np.max(np.abs(oracle.detmath("atan2", a, b) - np.arctan2(a.astype(np.float64), b.astype(np.float64)))) < 5e-7
+    e = rng.uniform(-20, 20, 100000).astype(np.float32)
+    assert np.max(np.abs(oracle.detmath("exp", e) / np.exp(e.astype(np.float64)) - 1)) < 3e-7
+    p = rng.uniform(1e-3, 1e3, 100000).astype(np.float32)
+    assert np.max(np.abs(oracle.detmath("log", p) - np.log(p.astype(np.float64)))) < 3e-7
+
+
+def test_rng_matches_formula(oracle):
+    """random.glsl:5-10 in float64 vs the FP32 oracle: the hash amplifies sin() error by 4.4e4, so only a
+    loose agreement is expected -- but values must be in [0,1) and equal the golden bits."""
+    pts = [(0, 0, 1.0), (17, 5, 2.0166667), (511, 511, 5.5), (1919, 1079, 3.25)]
+    got = np.stack([oracle.random2(*p) for p in pts])
+    assert bits_equal(got, GOLD["rng"])
+    assert np.all(got >= 0) and np.all(got < 1)
+    f32 = np.float32
+    for (x, y, s), g in zip(pts, got):
+        # FP32 dot product step by step (the argument reaches 1e5, where 1 ulp is 0.008 rad), float64 sin
+        s = f32(s)
+        ax, ay, az = f32(x + 0.5) + s, f32(y + 0.5) + s, f32(0.5) + s
+        arg = f32(f32(ax * f32(12.9898)) + f32(ay * f32(78.233))) + f32(az * f32(151.7182))
+        v = f32(f32(math.sin(float(arg))) * f32(43758.5453)) + s
+        want = float(v) - math.floor(float(v))
+        d = abs(want - float(g[0]))
+        assert min(d, 1 - d) < 0.02  # sin error 1e-7 x 43758.5
+
+
+def _one_object(obj, material=None, texture=None):
+    scene = Sail.Scene()
+    scene.add(obj)
+    return wire.serialize_scene(scene)
+
+
+def test_intersection_known_answers(oracle):
+    m, w = Sail.Matte(0.7), Sail.Color.WHITE
+    # sphere radius 1 at origin, ray from z=-5 along +z: t = 4, normal (0,0,-1)
+    oracle.set_scene(*_one_object(Sail.Sphere([0, 0, 0], 1.0, m, w)))
+    ids, t, n, mat = oracle.intersect_rays(np.float32([[0, 0, -5, 0, 0, 1], [0, 0, -5, 0, 0, 2], [0, 0, 0, 1, 0, 0], [0, 2, -5, 0, 0, 1], [0, 0, 0, 0, 1, 0]]))
+    assert list(ids) == [0, 0, 0, -1, 0]
+    assert t[0] == pytest.approx(4.0, abs=1e-6) and t[1] == pytest.approx(2.0, abs=1e-6)  # t scales with |dir| (Q6)
+    assert np.allclose(n[0], [0, 0, -1], atol=1e-6)
+    assert t[2] == pytest.approx(1.0, abs=1e-6) and np.allclose(n[2], [-1, 0, 0], atol=1e-6)  # from inside: normal flipped
+    assert t[4] == pytest.approx(1.0, abs=1e-6) and np.all(np.isnan(n[4]))  # world +y is the parametric pole: NaN normal (Q18)
+    assert t[3] == np.float32(1e5) and mat[0] == 1
+    # cube [0,1]^3 from outside (near face) and inside (far face); Cornell box always the far face
+    oracle.set_scene(*_one_object(Sail.Cube([0, 0, 0], [1, 1, 1], m, w)))
+    ids, t, n, _ = oracle.intersect_rays(np.float32([[0.5, 0.5, -2, 0, 0, 1], [0.5, 0.5, 0.5, 1, 0, 0]]))
+    assert t[0] == pytest.approx(2.0, abs=1e-6) and np.allclose(n[0], [0, 0, -1])
+    assert t[1] == pytest.approx(0.5, abs=1e-6) and np.allclose(n[1], [-1, 0, 0])
+    oracle.set_scene(*_one_object(Sail.Cornellbox([0, 0, 0], [1, 1, 1])))
+    ids, t, n, _ = oracle.intersect_rays(np.float32([[0.5, 0.5, -2, 0, 0, 1]]))
+    assert t[0] == pytest.approx(3.0, abs=1e-6) and np.allclose(n[0], [0, 0, -1])
+    d = oracle.intersect_detail(np.float32([0.5, 0.5, 0.5, -1, 0, 0]))
+    assert np.allclose(d["sc"], [0.25, 0.75, 0.25]) and d["into"]  # x- wall is GREEN (cornellbox.glsl:23-37)
+    # rectangle in the plane y = 1 spanning x,z in [0,2]; disk of radius 1 (inner 0.5) at the origin in y = 0
+    oracle.set_scene(*_one_object(Sail.Rectangle([0, 1, 0], [2, 1, 2], m, w)))
+    ids, t, _, _ = oracle.intersect_rays(np.float32([[1, 3, 1, 0, -1, 0], [3, 3, 1, 0, -1, 0]]))
+    assert list(ids) == [0, -1] and t[0] == pytest.approx(2.0, abs=1e-6)
+    oracle.set_scene(*_one_object(Sail.Disk([0, 0, 0], 1.0, 0.5, m, w)))
+    ids, _, _, _ = oracle.intersect_rays(np.float32([[0.75, 1, 0, 0, -1, 0], [0.2, 1, 0, 0, -1, 0], [1.2, 1, 0, 0, -1, 0]]))
+    assert list(ids) == [0, -1, -1]
+    # cylinder radius 0.5 height 2 on the y axis; cone with apex at y = h
+    oracle.set_scene(*_one_object(Sail.Cylinder([0, 0, 0], 2.0, 0.5, m, w)))
+    ids, t, n, _ = oracle.intersect_rays(np.float32([[-3, 1, 0, 1, 0, 0], [-3, 2.5, 0, 1, 0, 0]]))
+    assert list(ids) == [0, -1] and t[0] == pytest.approx(2.5, abs=1e-5) and np.allclose(n[0], [-1, 0, 0], atol=1e-5)
+    oracle.set_scene(*_one_object(Sail.Cone([0, 0, 0], 2.0, 1.0, m, w)))
+    ids, t, _, _ = oracle.intersect_rays(np.float32([[-3, 1, 0, 1, 0, 0]]))
+    assert ids[0] == 0 and t[0] == pytest.approx(2.5, abs=1e-5)  # radius at half height is 0.5
+
+
+def test_nearest_hit_tie_break_and_emission_mask(oracle):
+    """shader.shape.js:36,47-49: equal distances keep the lower index; emission only on the facing side."""
+    m, w = Sail.Matte(0.7), Sail.Color.WHITE
+    scene = Sail.Scene()
+    scene.add(Sail.Cube([0, 0, 0], [1, 1, 1], m, w, [5, 5, 5]))
+    scene.add(Sail.Cube([0, 0, 0], [1, 1, 1], m, w))
+    oracle.set_scene(*wire.serialize_scene(scene))
+    assert oracle.intersect_rays(np.float32([[0.5, 0.5, -2, 0, 0, 1]]))[0][0] == 0
+    out = oracle.intersect_detail(np.float32([0.5, 0.5, -2, 0, 0, 1]))
+    assert np.allclose(out["emission"], [5, 5, 5])
+    inside = oracle.intersect_detail(np.float32([0.5, 0.5, 0.5, 0, 0, 1]))
+    assert np.allclose(inside["emission"], [0, 0, 0])  # back side of the emitter: masked
+
+
+def test_progressive_mean_is_arithmetic_mean(oracle):
+    """fstrace.glsl:14 with textureWeight = k/(k+1) is the running arithmetic mean (what makes SUM sharding legal)."""
+    W, H = 24, 24
+    scene, o, t, l, bounces = scene_tables(1, W, H)
+    oracle.set_scene(o, t, l)
+    acc = np.zeros((H, W, 3), np.float32)
+    samples = []
+    for k in range(6):
+        m, eye, w, tm = frame_uniforms(scene, k, W, H)
+        oracle.render_frame(W, H, m, eye, w, tm, acc, max_bounces=bounces)
+        samples.append(oracle.trace_dump(W, H, m, eye, tm, max_bounces=bounces)["radiance"].astype(np.float64))
+    assert np.allclose(acc, np.mean(samples, axis=0), atol=2e-6)
+
+
+def test_present_window_table_quirk(oracle):
+    """window.glsl:38 reads weights[i*j+j]; a constant image must come back constant for every window filter."""
+    from sail_b200.filters import lower_filter
+    img = np.full((16, 16, 3), 0.25, np.float32)
+    pp = Sail.PluginParams("gaussian")
+    pp.addParam("r", "vec2(2.0,2.0)")
+    pp.addParam("alpha", "2.0")
+    f = lower_filter(pp)
+    assert len(f["weights"]) == 16 and f["weights"][0] > f["weights"][15] >= 0
+    out = oracle.present(img, img, img, f)
+    assert np.allclose(out[..., :3], 0.25, atol=1e-6) and np.all(out[..., 3] == 1)
+    box = lower_filter(_params("box", r="vec2(2.0,2.0)"))
+    assert box["weights"] == [1.0] * 16
+    with pytest.raises(ValueError):
+        lower_filter(Sail.PluginParams("sinc"))  # missing params: the reference's shader would not compile
+
+
+def _params(name, **kw):
+    pp = Sail.PluginParams(name)
+    for k, v in kw.items():
+        pp.addParam(k, v)
+    return pp
