@@ -21,6 +21,9 @@
 #define SAIL_TILE_W 16
 #define SAIL_TILE_H 8
 #define SAIL_CTA_THREADS 128
+// Resident CTAs per SM the register allocation is capped for: 8 (64 registers, 32 warps/SM) for the small
+// variants, 4 for those carrying microfacet BSDFs or quadrics (measured: profiles/r01_notes.md).
+#define SAIL_MIN_CTAS(F) (((F) & (SAIL_F_GLOSSY | SAIL_F_QUADRICS)) ? 4 : 8)
 
 // Per-frame constants derived on the host from (matrix, eye): the four corner rays of vstrace.glsl:4-7
 // and the edge differences used by the rasteriser-style interpolation (DESIGN.md "Primary rays").
@@ -73,7 +76,7 @@ SD V3 primaryDir(const SailFrameDev& f, float a, float b) {
 SD float nanToZero(float v) { return (v == v) ? v : 0.0f; }
 
 template <int F>
-__global__ void __launch_bounds__(SAIL_CTA_THREADS) sail_trace_megakernel(const __grid_constant__ SailLaunch L) {
+__global__ void __launch_bounds__(SAIL_CTA_THREADS, SAIL_MIN_CTAS(F)) sail_trace_megakernel(const __grid_constant__ SailLaunch L) {
     __shared__ SailSceneBlock sc;
     stageScene(sc, L.scene);
 
