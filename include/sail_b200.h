@@ -177,8 +177,11 @@ int sail_intersect_rays(sail_ctx* ctx, const float* rays, int32_t count, int32_t
  * rays W*H*max_bounces*6, radiance W*H*3 (the raw sample e).  Each may be NULL. */
 int sail_trace_dump(sail_ctx* ctx, const sail_frame* frame, int32_t* hit_id, float* t, float* rays, float* radiance);
 /* Elementwise evaluation of the device math library: which = 0 sin, 1 cos, 2 tan, 3 atan, 4 acos, 5 asin,
- * 6 exp, 7 log, 8 atan(a,b), 9 pow(a,b), 10 a/b, 11 sqrt. */
+ * 6 exp, 7 log, 8 atan(a,b), 9 pow(a,b), 10 a/b, 11 sqrt, 12 1/a. */
 int sail_eval_math(sail_ctx* ctx, int32_t which, const float* a, const float* b, float* out, int32_t count);
+/* Runs the device reciprocal over all 2^32 float inputs and counts results that differ from its stated rule
+ * (correctly rounded inside 2^-126 <= |a| <= 2^126, pinned specials outside; sail_b200/csrc/detmath.h). */
+int sail_selftest_math(sail_ctx* ctx, uint64_t* mismatches);
 /* Number of kernels this context has launched since creation. */
 uint64_t sail_launch_count(const sail_ctx* ctx);
 /* Device time of the most recent sail_render() / sail_render_n() call, from CUDA events recorded on the

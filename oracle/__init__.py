@@ -110,7 +110,7 @@ class Oracle:
         return out
 
     def detmath(self, which, a, b=None):
-        names = {"sin": 0, "cos": 1, "tan": 2, "atan": 3, "acos": 4, "asin": 5, "exp": 6, "log": 7, "atan2": 8, "pow": 9}
+        names = {"sin": 0, "cos": 1, "tan": 2, "atan": 3, "acos": 4, "asin": 5, "exp": 6, "log": 7, "atan2": 8, "pow": 9, "rcp": 12}
         a = np.ascontiguousarray(a, dtype=np.float32).reshape(-1)
         out = np.zeros_like(a)
         bb = None if b is None else np.ascontiguousarray(b, dtype=np.float32).reshape(-1)

@@ -161,6 +161,7 @@ void oracle_detmath(int which, int N, const float* a, const float* b, float* out
             case 7: r = dm_log(x); break;
             case 8: r = dm_atan2(x, y); break;
             case 9: r = dm_pow(x, y); break;
+            case 12: r = dm_rcp(x); break;
         }
         out[i] = r;
     }

@@ -73,6 +73,7 @@ _SIGNATURES = {
     "sail_intersect_rays": (ctypes.c_int, [_P, _P, ctypes.c_int32, _P, _P, _P, _P]),
     "sail_trace_dump": (ctypes.c_int, [_P, ctypes.POINTER(Frame), _P, _P, _P, _P]),
     "sail_eval_math": (ctypes.c_int, [_P, ctypes.c_int32, _P, _P, _P, ctypes.c_int32]),
+    "sail_selftest_math": (ctypes.c_int, [_P, ctypes.POINTER(ctypes.c_uint64)]),
     "sail_launch_count": (ctypes.c_uint64, [_P]),
     "sail_last_render_ms": (ctypes.c_int, [_P, ctypes.POINTER(ctypes.c_float)]),
 }
@@ -281,12 +282,21 @@ class Context:
 
     def eval_math(self, which, a, b=None):
         names = {"sin": 0, "cos": 1, "tan": 2, "atan": 3, "acos": 4, "asin": 5, "exp": 6, "log": 7, "atan2": 8,
-                 "pow": 9, "div": 10, "sqrt": 11}
+                 "pow": 9, "div": 10, "sqrt": 11, "rcp": 12}
         a = _f32(a).reshape(-1)
         bb = None if b is None else _f32(b).reshape(-1)
         out = np.empty_like(a)
         self._check(self.lib.sail_eval_math(self._h, names[which], _ptr(a), _ptr(bb), _ptr(out), a.size))
         return out
+
+
+def _selftest_math(self):
+    n = ctypes.c_uint64()
+    self._check(self.lib.sail_selftest_math(self._h, ctypes.byref(n)))
+    return int(n.value)
+
+
+Context.selftest_math = _selftest_math
 
 
 def scene_features(objects, texparams, lights):

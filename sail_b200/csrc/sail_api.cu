@@ -458,7 +458,7 @@ int sail_trace_dump(sail_ctx* ctx, const sail_frame* frame, int32_t* hit_id, flo
 }
 
 int sail_eval_math(sail_ctx* ctx, int32_t which, const float* a, const float* b, float* out, int32_t count) {
-    if (!ctx || !a || !out || count < 0 || which < 0 || which > 11) return SAIL_ERR_INVALID;
+    if (!ctx || !a || !out || count < 0 || which < 0 || which > 12) return SAIL_ERR_INVALID;
     if (count == 0) return SAIL_OK;
     CU(cudaSetDevice(ctx->device));
     float *dA = nullptr, *dB = nullptr, *dO = nullptr;
@@ -476,6 +476,23 @@ int sail_eval_math(sail_ctx* ctx, int32_t which, const float* a, const float* b,
     CU(cudaMemcpyAsync(out, dO, bytes, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     cudaFree(dA); cudaFree(dB); cudaFree(dO);
+    return SAIL_OK;
+}
+
+int sail_selftest_math(sail_ctx* ctx, uint64_t* mismatches) {
+    if (!ctx || !mismatches) return SAIL_ERR_INVALID;
+    CU(cudaSetDevice(ctx->device));
+    unsigned long long* d = nullptr;
+    CU(cudaMalloc(&d, sizeof(unsigned long long)));
+    CU(cudaMemsetAsync(d, 0, sizeof(unsigned long long), ctx->stream));
+    sail_selftest_rcp_kernel<<<(1u << 20) / 256, 256, 0, ctx->stream>>>(d);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    unsigned long long h = 0;
+    CU(cudaMemcpyAsync(&h, d, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    cudaFree(d);
+    *mismatches = h;
     return SAIL_OK;
 }
 

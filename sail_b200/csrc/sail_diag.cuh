@@ -100,8 +100,27 @@ __global__ void sail_eval_math_kernel(int which, const float* a, const float* b,
         case 9: r = dm_pow(x, y); break;
         case 10: r = dm_div(x, y); break;
         case 11: r = dm_sqrt(x); break;
+        case 12: r = dm_rcp(x); break;
     }
     out[i] = r;
+}
+
+// Exhaustive check of dm_rcp over all 2^32 inputs against the rule stated in detmath.h (IEEE __frcp_rn inside
+// 2^-126 <= |a| <= 2^126, pinned values outside).  One thread per 2^12 consecutive bit patterns.
+__global__ void sail_selftest_rcp_kernel(unsigned long long* mismatches) {
+    unsigned base = (blockIdx.x * blockDim.x + threadIdx.x) << 12;
+    unsigned bad = 0;
+    for (unsigned k = 0; k < 4096; k++) {
+        unsigned u = base + k, mag = u & 0x7fffffffu, sign = u & 0x80000000u;
+        float a = __uint_as_float(u), got = dm_rcp(a), want;
+        if (mag > 0x7f800000u) want = a;
+        else if (mag < 0x00800000u) want = __uint_as_float(sign | 0x7f800000u);
+        else if (mag > 0x7e800000u) want = __uint_as_float(sign);
+        else want = __frcp_rn(a);
+        bool same = (got != got && want != want) || __float_as_uint(got) == __float_as_uint(want);
+        bad += same ? 0u : 1u;
+    }
+    if (bad) atomicAdd(mismatches, (unsigned long long)bad);
 }
 
 __global__ void sail_scale_kernel(float* p, size_t count, float s) {

@@ -126,6 +126,13 @@ def test_device_math_matches_host(capi, oracle):
         want = (a64 * (np.float32(1.0) / b64)).astype(np.float32)
         assert bits_equal(ctx.eval_math("div", a64, b64), want)
         assert bits_equal(ctx.eval_math("sqrt", a), np.sqrt(a))
+        # the branch-free reciprocal: all 2^32 inputs on the device, then host == device on specials + a sample
+        assert ctx.selftest_math() == 0
+        edge = np.array([0, 0x80000000, 1, 0x007fffff, 0x00800000, 0x7e800000, 0x7e800001, 0x7f7fffff, 0x7f800000,
+                         0xff800000, 0x7fc00000, 0x3f800000, 0xbf800000, 0x00800001, 0x807fffff], np.uint32).view(np.float32)
+        x = np.concatenate([edge, rng.normal(size=200000).astype(np.float32), (rng.normal(size=50000) * 1e30).astype(np.float32),
+                            (rng.normal(size=50000) * 1e-30).astype(np.float32)])
+        assert bits_equal(ctx.eval_math("rcp", x), oracle.detmath("rcp", x))
 
 
 FILTERS = [("color", {}), ("gamma", {"c": "2.2"}), ("tonemapping", {}), ("normal", {}), ("position", {}),
