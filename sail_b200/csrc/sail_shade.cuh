@@ -29,9 +29,10 @@ SD V3 uniformSampleSphere(V2 u) {
     float s = sc2.x, c = sc2.y;
     return mk3(r * c, r * s, z);
 }
+template <int F>
 SD V3 cosineSampleHemisphere(V2 u) {
     float r = dm_sqrt(u.x);
-    float2 sc2 = sail_sincos(SAIL_TWO_PI * u.y);
+    float2 sc2 = sincosF<F>(SAIL_TWO_PI * u.y);
     float s = sc2.x, c = sc2.y;
     return mk3(r * c, r * s, dm_sqrt(1.0f - u.x));
 }
@@ -240,7 +241,7 @@ SD V3 material(const SailSurface& su, int matCategory, V3 sc, bool into, V2 u, V
     switch (matCategory) {
         case SAIL_MATTE: {  // matte.glsl:8-37
             V3 R = m[SM_MATTE_KD] * sc;
-            wi = cosineSampleHemisphere(u);
+            wi = cosineSampleHemisphere<F>(u);
             pdf = sameHemisphere(wo, wi) ? absCosTheta(wi) * SAIL_INVPI : 0.0f;
             if (m[SM_MATTE_SIGMA] < SAIL_EPSILON) fs = R * SAIL_INVPI;                    // bsdf.glsl:7-19
             else fs = orenNayar_f(R, m[SM_MATTE_A], m[SM_MATTE_B], wo, wi);              // bsdf.glsl:45-76

@@ -46,6 +46,13 @@ static __device__ __noinline__ float sail_sin(float x) { return dm_sin(x); }
 static __device__ __noinline__ float2 sail_sincos(float x) { float s, c; dm_sincos(x, &s, &c); return make_float2(s, c); }
 static __device__ __noinline__ float sail_acos(float x) { return dm_acos(x); }
 static __device__ __noinline__ float sail_atan2(float y, float x) { return dm_atan2(y, x); }
+// Single-use sites of the small variants are inlined instead (no call overhead, code still fits the I-cache).
+#define SAIL_SMALL(F) (!((F) & (SAIL_F_GLOSSY | SAIL_F_QUADRICS | SAIL_F_NEE)))
+template <int F> SD float2 sincosF(float x) {
+    if (SAIL_SMALL(F)) { float s, c; dm_sincos(x, &s, &c); return make_float2(s, c); }
+    return sail_sincos(x);
+}
+template <int F> SD float acosF(float x) { return SAIL_SMALL(F) ? dm_acos(x) : sail_acos(x); }
 
 // The winning hit (const/struct.glsl:1-13 minus the dead dpdv / seed fields).
 struct Hit {
@@ -206,12 +213,8 @@ struct Nearest {
     int id;
 };
 template <int F>
-static __device__ __noinline__ Nearest nearestObjectRegs(unsigned scAddr, float ox, float oy, float oz, float dx, float dy, float dz) {
-    const SailSceneBlock& sc = *reinterpret_cast<const SailSceneBlock*>(__cvta_shared_to_generic(scAddr));
-    Ray ray;
-    ray.o = mk3(ox, oy, oz);
-    ray.d = mk3(dx, dy, dz);
-    V3 rd = mk3(dm_rcp(dx), dm_rcp(dy), dm_rcp(dz));
+SD Nearest nearestObjectInline(const SailSceneBlock& sc, const Ray& ray) {
+    V3 rd = mk3(dm_rcp(ray.d.x), dm_rcp(ray.d.y), dm_rcp(ray.d.z));
     Nearest r;
     r.t = SAIL_MAX_DISTANCE;
     r.id = -1;
@@ -223,7 +226,18 @@ static __device__ __noinline__ Nearest nearestObjectRegs(unsigned scAddr, float 
     return r;
 }
 template <int F>
+static __device__ __noinline__ Nearest nearestObjectRegs(unsigned scAddr, float ox, float oy, float oz, float dx, float dy, float dz) {
+    const SailSceneBlock& sc = *reinterpret_cast<const SailSceneBlock*>(__cvta_shared_to_generic(scAddr));
+    Ray ray;
+    ray.o = mk3(ox, oy, oz);
+    ray.d = mk3(dx, dy, dz);
+    return nearestObjectInline<F>(sc, ray);
+}
+// Variants without next-event estimation have a single call site (the bounce ray): inline it.  With NEE the
+// shadow rays are a second site and one out-of-line copy serves both (I-cache footprint).
+template <int F>
 SD Nearest nearestObject(const SailSceneBlock& sc, const Ray& ray) {
+    if (!(F & SAIL_F_NEE)) return nearestObjectInline<F>(sc, ray);
     return nearestObjectRegs<F>((unsigned)__cvta_generic_to_shared(&sc), ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z);
 }
 
@@ -324,7 +338,7 @@ SD void hitRecord(const SailSceneBlock& sc, int i, float t, const Ray& ray, Hit&
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - c);
             V3 hl = ol + t * dl;
             float r = q[SQ_SPH_R];
-            float theta = sail_acos(fclamp(hl.z * q[SQ_SPH_INVR], -1.0f, 1.0f));
+            float theta = acosF<F>(fclamp(hl.z * q[SQ_SPH_INVR], -1.0f, 1.0f));
             if (wantUV) {
                 float gx = hl.x;
                 if (hl.x == 0.0f && hl.y == 0.0f) gx = 1e-5f * r;  // guards phi only (Q18)

@@ -15,6 +15,33 @@ import sys
 import tempfile
 
 
+FUNC_RE = re.compile(r"^(?:SD|static __device__ __noinline__|__global__|DM_FN|static __device__)\b[^(;]*?(\w+)\s*\(")
+
+
+def function_index(src_dir):
+    idx = {}
+    for f in os.listdir(src_dir):
+        if not f.endswith((".cuh", ".h", ".cu")):
+            continue
+        starts = []
+        for i, l in enumerate(open(os.path.join(src_dir, f), errors="ignore"), 1):
+            m = FUNC_RE.match(l)
+            if m:
+                starts.append((i, m.group(1)))
+        idx[f] = starts
+    return idx
+
+
+def function_of(idx, fl):
+    name = "?"
+    for start, n in idx.get(fl[0], []):
+        if start <= fl[1]:
+            name = n
+        else:
+            break
+    return name
+
+
 def sass_with_lines(so, kernel):
     tmp = tempfile.mkdtemp()
     subprocess.check_call(["cuobjdump", "-xelf", "all", os.path.abspath(so)], cwd=tmp, stdout=subprocess.DEVNULL)
@@ -22,8 +49,8 @@ def sass_with_lines(so, kernel):
     for f in sorted(os.listdir(tmp)):
         if not f.endswith(".cubin"):
             continue
-        txt = subprocess.run(["nvdisasm", "--print-line-info", "-c", os.path.join(tmp, f)], capture_output=True, text=True).stdout
-        cur, line, take = None, ("?", 0), False
+        txt = subprocess.run(["nvdisasm", "--print-line-info-inline", "-c", os.path.join(tmp, f)], capture_output=True, text=True).stdout
+        cur, line, take, chain, fresh = None, ("?", 0), False, [], True
         for l in txt.splitlines():
             m = re.match(r"\s*\.text\.(\S+):", l)
             if m:
@@ -33,11 +60,15 @@ def sass_with_lines(so, kernel):
                 continue
             m = re.search(r'//## File "([^"]+)", line (\d+)', l)
             if m:
-                line = (os.path.basename(m.group(1)), int(m.group(2)))
+                if fresh:
+                    chain, fresh = [], False
+                chain.append((os.path.basename(m.group(1)), int(m.group(2))))
+                line = chain[0]
                 continue
             m = re.match(r"\s+/\*([0-9a-f]{4,})\*/\s+(.*?);", l)
             if m:
-                out.append((int(m.group(1), 16), m.group(2).strip(), line))
+                fresh = True
+                out.append((int(m.group(1), 16), m.group(2).strip(), line, tuple(chain)))
         if out:
             break
     return out
@@ -60,6 +91,20 @@ def main():
         a[0] += prof[i][0]; a[1] += prof[i][1]; a[2] += prof[i][2]
     tot = sum(a[0] for a in agg.values()) or 1
     tots = sum(a[1] for a in agg.values()) or 1
+    # ---- by function bucket: the outermost inlined frame that is not the kernel / bounce loop itself ----
+    idx = function_index(os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "sail_b200", "csrc"))
+    skip = {"sail_trace_megakernel", "__launch_bounds__", "tracePath", "intersectObjects", "?"}
+    fagg = collections.defaultdict(lambda: [0, 0, 0])
+    for i in range(n):
+        chain = sass[i][3] or (sass[i][2],)
+        names = [function_of(idx, fl) for fl in chain]
+        bucket = next((nm for nm in reversed(names) if nm not in skip), names[-1])
+        a = fagg[bucket]
+        a[0] += prof[i][0]; a[1] += prof[i][1]; a[2] += prof[i][2]
+    print("%-28s %8s %8s %8s" % ("function", "inst%", "stall%", "thr/inst"))
+    for k, a in sorted(fagg.items(), key=lambda kv: -kv[1][0])[:25]:
+        print("%-28s %7.2f%% %7.2f%% %8.1f" % (k, 100.0 * a[0] / tot, 100.0 * a[1] / tots, a[2] / max(a[0], 1)))
+    print()
     print("%-28s %8s %8s %8s" % ("file:line", "inst%", "stall%", "thr/inst"))
     for k, a in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
         print("%-28s %7.2f%% %7.2f%% %8.1f" % ("%s:%d" % k, 100.0 * a[0] / tot, 100.0 * a[1] / tots, a[2] / max(a[0], 1)))
