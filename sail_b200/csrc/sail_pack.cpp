@@ -136,10 +136,22 @@ int sail_pack_scene(const float* objects, int n, const float* texparams, int tn,
         // ---- geometry ----
         float* q = s.q;
         switch (cat) {
-            case SAIL_CUBE: case SAIL_CORNELLBOX:
+            case SAIL_CUBE: case SAIL_CORNELLBOX: {
                 fetch3(O, 1, kObjectsLen, row, s.lo);
                 fetch3(O, 4, kObjectsLen, row, s.hi);
+                // Per-face normal (cube.glsl:25-38 `c*vec3(..)`; cornellbox.glsl:39-51,83 `-vec3(..)`) and dpdu
+                // (cube.glsl:40-48): scene constants, evaluated here with the shader's own operations.
+                const float c = (cat == SAIL_CUBE) ? s.rev : 1.0f;
+                const float axis[6][3] = {{-1, 0, 0}, {1, 0, 0}, {0, -1, 0}, {0, 1, 0}, {0, 0, -1}, {0, 0, 1}};
+                for (int f = 0; f < 6; f++) {
+                    H3 nrm{c * axis[f][0], c * axis[f][1], c * axis[f][2]};
+                    if (cat == SAIL_CORNELLBOX) nrm = H3{-nrm.x, -nrm.y, -nrm.z};
+                    H3 dpdu = (dm_abs(nrm.x) < 0.5f) ? hcross(nrm, H3{1.0f, 0.0f, 0.0f}) : hcross(nrm, H3{0.0f, 1.0f, 0.0f});
+                    st3(q + SQ_BOX_FACE + f * SQ_BOX_FACE_STRIDE, nrm);
+                    st3(q + SQ_BOX_FACE + f * SQ_BOX_FACE_STRIDE + 3, dpdu);
+                }
                 break;
+            }
             case SAIL_SPHERE: {  // sphere.glsl:10-16,45-92
                 float c[3];
                 fetch3(O, 1, kObjectsLen, row, c);

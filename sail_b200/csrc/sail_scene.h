@@ -30,7 +30,7 @@ enum { SAIL_FEAT_QUADRICS = 1, SAIL_FEAT_GLOSSY = 2, SAIL_FEAT_TEXTURED = 4, SAI
 enum { SAIL_UNIFORM_COLOR = 0, SAIL_CHECKERBOARD = 5, SAIL_CHECKERBOARD2 = 7, SAIL_BILERP = 8, SAIL_MIXF = 9,
        SAIL_SCALE = 10, SAIL_UVF = 11 };
 
-// Geometry of one object: what the nearest-hit scan touches.  48 B header + 80 B parameters = 128 B.
+// Geometry of one object: what the nearest-hit scan touches.  48 B header + 160 B parameters = 208 B.
 struct __attribute__((aligned(16))) SailShape {
     int category;
     float rev;        // reverseNormal ? -1 : +1   (Cornell box: +1, cornellbox.glsl:18)
@@ -38,9 +38,11 @@ struct __attribute__((aligned(16))) SailShape {
     float hi[3];      // cube/cornellbox: max; quadrics: bounding box corner
     float emission[3];
     int matCategory;  // texParams[matRow][0]
-    float q[20];      // shape parameters, layout per category (SQ_* below)
+    float q[40];      // shape parameters, layout per category (SQ_* below)
 };
 // q[] layouts
+// cube / cornellbox: per face (x-, x+, y-, y+, z-, z+) the geometric normal intersectX() returns and its dpdu
+enum { SQ_BOX_FACE = 0, SQ_BOX_FACE_STRIDE = 6 };
 enum { SQ_SPH_C = 0, SQ_SPH_R = 3, SQ_SPH_RR = 4, SQ_SPH_INVR = 5, SQ_SPH_PDF = 6 };
 enum { SQ_RECT_DPDU = 0, SQ_RECT_N = 3, SQ_RECT_SS = 6, SQ_RECT_TS = 9, SQ_RECT_MAXX = 12, SQ_RECT_MAXY = 13,
        SQ_RECT_INVMAXX = 14, SQ_RECT_INVMAXY = 15, SQ_RECT_DPDV = 16, SQ_RECT_PDF = 19 };

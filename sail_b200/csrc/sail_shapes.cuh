@@ -306,31 +306,34 @@ SD void hitRecord(const SailSceneBlock& sc, int i, float t, const Ray& ray, Hit&
     h.index = i;
     h.unitDpdu = (s.category == SAIL_CUBE || s.category == SAIL_CORNELLBOX);
     switch (s.category) {
-        case SAIL_CUBE: {  // cube.glsl:79-85
+        case SAIL_CUBE:          // cube.glsl:25-48,79-85
+        case SAIL_CORNELLBOX: {  // cornellbox.glsl:23-51,81-88
+            // One branch-free path for both boxes: the face is picked with the shader's comparison chain
+            // (x-, x+, y-, y+, z-, z+), its normal and dpdu come from the per-face table built at upload.
             V3 mn = ld3(s.lo), mx = ld3(s.hi);
             h.p = ray.o + t * ray.d;
-            gn = boxFaceNormal(h.p, mn, mx, s.rev);
-            h.dpdu = boxDpdu(gn);
-            if (wantUV) {  // getCubeUV, cube.glsl:54-63 (compares the *shifted* hit, as written)
-                V3 tr = mx - mn, hs = h.p - mn;
-                if (hs.x < mn.x + 0.0001f || hs.x > mx.x - 0.0001f) uv = mk2(fdiv(hs.y, tr.y), fdiv(hs.z, tr.z));
-                else if (hs.y < mn.y + 0.0001f || hs.y > mx.y - 0.0001f) uv = mk2(fdiv(hs.x, tr.x), fdiv(hs.z, tr.z));
-                else uv = mk2(fdiv(hs.x, tr.x), fdiv(hs.y, tr.y));
+            int face = 5;
+            face = (h.p.z < mn.z + 0.0001f) ? 4 : face;
+            face = (h.p.y > mx.y - 0.0001f) ? 3 : face;
+            face = (h.p.y < mn.y + 0.0001f) ? 2 : face;
+            face = (h.p.x > mx.x - 0.0001f) ? 1 : face;
+            face = (h.p.x < mn.x + 0.0001f) ? 0 : face;
+            const float* ft = q + SQ_BOX_FACE + face * SQ_BOX_FACE_STRIDE;
+            gn = ld3(ft);
+            h.dpdu = ld3(ft + 3);
+            if (s.category == SAIL_CORNELLBOX) {  // getCornellboxColor, cornellbox.glsl:23-37
+                V3 wall = (face == 0) ? mk3(0.25f, 0.75f, 0.25f) : mk3(0.25f, 0.25f, 0.75f);  // GREEN : BLUE
+                float rest = (face <= 3 || h.p.z > mn.z + 0.0001f) ? 1.0f : 0.0f;               // WHITE : BLACK
+                h.sc = (face <= 1) ? wall : splat3(rest);
+            } else {
+                if (wantUV) {  // getCubeUV, cube.glsl:54-63 (compares the *shifted* hit, as written)
+                    V3 tr = mx - mn, hs = h.p - mn;
+                    if (hs.x < mn.x + 0.0001f || hs.x > mx.x - 0.0001f) uv = mk2(fdiv(hs.y, tr.y), fdiv(hs.z, tr.z));
+                    else if (hs.y < mn.y + 0.0001f || hs.y > mx.y - 0.0001f) uv = mk2(fdiv(hs.x, tr.x), fdiv(hs.z, tr.z));
+                    else uv = mk2(fdiv(hs.x, tr.x), fdiv(hs.y, tr.y));
+                }
+                h.sc = surfaceColor<F>(u, uv);
             }
-            h.sc = surfaceColor<F>(u, uv);
-            break;
-        }
-        case SAIL_CORNELLBOX: {  // cornellbox.glsl:23-37,81-88
-            V3 mn = ld3(s.lo), mx = ld3(s.hi);
-            h.p = ray.o + t * ray.d;
-            gn = -boxFaceNormal(h.p, mn, mx, 1.0f);
-            h.dpdu = boxDpdu(gn);
-            if (h.p.x < mn.x + 0.0001f) h.sc = mk3(0.25f, 0.75f, 0.25f);       // GREEN
-            else if (h.p.x > mx.x - 0.0001f) h.sc = mk3(0.25f, 0.25f, 0.75f);  // BLUE
-            else if (h.p.y < mn.y + 0.0001f) h.sc = splat3(1.0f);
-            else if (h.p.y > mx.y - 0.0001f) h.sc = splat3(1.0f);
-            else if (h.p.z > mn.z + 0.0001f) h.sc = splat3(1.0f);
-            else h.sc = splat3(0.0f);
             break;
         }
         case SAIL_SPHERE: {  // sphere.glsl:33-43,62-84
