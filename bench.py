@@ -45,8 +45,9 @@ def peaks():
 
 
 def ops_per_path():
+    key = {"cornell": "cornell_1080p", "config2": "config2_1080p", "config3": "config3_1080p", "config5": "config5_1080p"}[_workload]
     with open(os.path.join(ROOT, "baseline", "ops_per_path.json")) as f:
-        return float(json.load(f)["cornell_1080p"]["ops_per_path"])
+        return float(json.load(f)[key]["ops_per_path"])
 
 
 class ClockSampler:
@@ -91,9 +92,16 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+WORKLOADS = {"cornell": ("cornell_1080p", WORKLOAD),
+             "config2": ("config2", "materials demo (mirror/glass/metal/matte spheres, area light) 1920x1080, 5 bounces"),
+             "config3": ("config3", "quadrics + textures + area/point/spot lights 1920x1080, 5 bounces"),
+             "config5": ("config5", "glass + metal spheres 1920x1080, 16 bounces")}
+_workload = "cornell"
+
+
 def build_workload():
     from sail_b200 import configs, wire
-    scene, W, H, _, bounces = configs.cornell_1080p()
+    scene, W, H, _, bounces = getattr(configs, WORKLOADS[_workload][0])()
     o, t, l = wire.serialize_scene(scene)
     return scene, W, H, bounces, (o, t, l)
 
@@ -263,7 +271,7 @@ def run_ours(args, rank, world, local_rank):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warm,
             "ms_per_step": dev_ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": WORKLOAD, "spp_per_step": SPP_PER_STEP, "paths_per_step_per_gpu": paths_per_step,
+            "config": {"workload": WORKLOADS[_workload][1], "spp_per_step": SPP_PER_STEP, "paths_per_step_per_gpu": paths_per_step,
                        "kernel": args.kernel, "arithmetic": "strict (bit-exact vs oracle)", "sharding": "sample index mod N",
                        "l2": "flushed between steps (256 MiB memset outside the per-step events)"},
             "spp_per_s": value * 1e6 / (W * H),
@@ -295,7 +303,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--kernel", default="mega", choices=["mega", "wavefront"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--workload", default="cornell", choices=sorted(WORKLOADS), help="cornell = the headline; others are extra")
     args = ap.parse_args()
+    global _workload
+    _workload = args.workload
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -18,7 +18,6 @@
 #include "sail_diag.cuh"
 #include "sail_mega.cuh"
 #include "sail_present.cuh"
-#include "sail_wavefront.cuh"
 
 struct sail_ctx {
     int device = 0;
@@ -37,7 +36,6 @@ struct sail_ctx {
     int* hitId = nullptr;
     float* presentF32 = nullptr;
     unsigned char* presentU8 = nullptr;
-    SailWavefront wf;
     uint64_t launches = 0;
     char err[512];
     sail_ctx() { err[0] = 0; }
@@ -48,6 +46,10 @@ cudaError_t sail_launch_mega_g0(int F, const SailLaunch* L, dim3 grid, cudaStrea
 cudaError_t sail_launch_mega_g1(int F, const SailLaunch* L, dim3 grid, cudaStream_t stream);
 cudaError_t sail_launch_mega_g2(int F, const SailLaunch* L, dim3 grid, cudaStream_t stream);
 cudaError_t sail_launch_mega_g3(int F, const SailLaunch* L, dim3 grid, cudaStream_t stream);
+cudaError_t sail_launch_wave_g0(int F, const SailLaunch* L, dim3 grid, cudaStream_t stream);
+cudaError_t sail_launch_wave_g1(int F, const SailLaunch* L, dim3 grid, cudaStream_t stream);
+cudaError_t sail_launch_wave_g2(int F, const SailLaunch* L, dim3 grid, cudaStream_t stream);
+cudaError_t sail_launch_wave_g3(int F, const SailLaunch* L, dim3 grid, cudaStream_t stream);
 }
 
 namespace {
@@ -58,6 +60,16 @@ cudaError_t launchMega(int F, const SailLaunch& L, dim3 grid, cudaStream_t strea
         case 1: return sail_launch_mega_g1(F, &L, grid, stream);
         case 2: return sail_launch_mega_g2(F, &L, grid, stream);
         case 3: return sail_launch_mega_g3(F, &L, grid, stream);
+    }
+    return cudaErrorInvalidValue;
+}
+
+cudaError_t launchWave(int F, const SailLaunch& L, dim3 grid, cudaStream_t stream) {
+    switch (F >> 2) {
+        case 0: return sail_launch_wave_g0(F, &L, grid, stream);
+        case 1: return sail_launch_wave_g1(F, &L, grid, stream);
+        case 2: return sail_launch_wave_g2(F, &L, grid, stream);
+        case 3: return sail_launch_wave_g3(F, &L, grid, stream);
     }
     return cudaErrorInvalidValue;
 }
@@ -192,7 +204,6 @@ void sail_destroy(sail_ctx* ctx) {
         cudaSetDevice(ctx->device);
         cudaStreamSynchronize(ctx->stream);
     }
-    ctx->wf.release();
     cudaFree(ctx->dScene); cudaFree(ctx->accum); cudaFree(ctx->normal); cudaFree(ctx->position);
     cudaFree(ctx->depth); cudaFree(ctx->hitId); cudaFree(ctx->presentF32); cudaFree(ctx->presentU8);
     if (ctx->evStart) cudaEventDestroy(ctx->evStart);
@@ -296,19 +307,15 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
     L.rcpH = dm_rcp((float)ctx->H);
     L.accum = ctx->accum; L.normal = ctx->normal; L.position = ctx->position; L.hitId = ctx->hitId; L.depth = ctx->depth;
     L.scene = ctx->dScene;
+    L.sceneSmem = (unsigned)sailSceneSmemBytes(ctx->hostScene.n, ctx->hostScene.ln);
     for (int k = 0; k < count; k++) lowerFrame(frames[k], L.frames[k]);
     CU(cudaEventRecord(ctx->evStart, ctx->stream));
-    if (ctx->cfg.kernel == SAIL_KERNEL_WAVEFRONT) {
-        int launched = 0;
-        cudaError_t e = ctx->wf.render(L, ctx->stream, &launched);
-        ctx->launches += launched;
-        if (e != cudaSuccess) return setErr(ctx, SAIL_ERR_CUDA, "wavefront render failed: %s", cudaGetErrorString(e));
-    } else {
-        dim3 grid((ctx->W + SAIL_TILE_W - 1) / SAIL_TILE_W, tileRows);
-        // the variant follows the scene's content, never the caller's mask hints
-        CU(launchMega(ctx->hostScene.features & SAIL_F_ALL, L, grid, ctx->stream));
-        ctx->launches++;
-    }
+    // the variant follows the scene's content, never the caller's mask hints
+    dim3 grid((ctx->W + SAIL_TILE_W - 1) / SAIL_TILE_W, tileRows);
+    const int F = ctx->hostScene.features & SAIL_F_ALL;
+    if (ctx->cfg.kernel == SAIL_KERNEL_WAVEFRONT) CU(launchWave(F, L, grid, ctx->stream));
+    else CU(launchMega(F, L, grid, ctx->stream));
+    ctx->launches++;
     CU(cudaEventRecord(ctx->evStop, ctx->stream));
     ctx->timed = true;
     return SAIL_OK;
@@ -416,7 +423,7 @@ int sail_intersect_rays(sail_ctx* ctx, const float* rays, int32_t count, int32_t
     CU(cudaMalloc(&dI, c * sizeof(int)));
     CU(cudaMalloc(&dM, c * sizeof(int)));
     CU(cudaMemcpyAsync(dR, rays, c * 6 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-    sail_intersect_kernel<<<(unsigned)((c + SAIL_CTA_THREADS - 1) / SAIL_CTA_THREADS), SAIL_CTA_THREADS, 0, ctx->stream>>>(ctx->dScene, dR, count, dI, dT, dN, dM);
+    sail_intersect_kernel<<<(unsigned)((c + SAIL_CTA_THREADS - 1) / SAIL_CTA_THREADS), SAIL_CTA_THREADS, sailSceneSmemBytes(ctx->hostScene.n, ctx->hostScene.ln), ctx->stream>>>(ctx->dScene, dR, count, dI, dT, dN, dM);
     ctx->launches++;
     CU(cudaGetLastError());
     if (hit_id) CU(cudaMemcpyAsync(hit_id, dI, c * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
@@ -445,7 +452,7 @@ int sail_trace_dump(sail_ctx* ctx, const sail_frame* frame, int32_t* hit_id, flo
     if (rays) CU(cudaMalloc(&L.rays, n * B * 6 * sizeof(float)));
     if (radiance) CU(cudaMalloc(&L.radiance, n * 3 * sizeof(float)));
     dim3 grid((ctx->W + SAIL_TILE_W - 1) / SAIL_TILE_W, (ctx->H + SAIL_TILE_H - 1) / SAIL_TILE_H);
-    sail_trace_dump_kernel<<<grid, SAIL_CTA_THREADS, 0, ctx->stream>>>(L);
+    sail_trace_dump_kernel<<<grid, SAIL_CTA_THREADS, sailSceneSmemBytes(ctx->hostScene.n, ctx->hostScene.ln), ctx->stream>>>(L);
     ctx->launches++;
     CU(cudaGetLastError());
     if (hit_id) CU(cudaMemcpyAsync(hit_id, L.hitId, n * B * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));

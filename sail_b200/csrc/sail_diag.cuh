@@ -8,8 +8,7 @@
 __global__ void __launch_bounds__(SAIL_CTA_THREADS) sail_intersect_kernel(const SailSceneBlock* __restrict__ scene,
                                                                           const float* __restrict__ rays, int count, int* hitId,
                                                                           float* t, float* normal, int* matCategory) {
-    __shared__ SailSceneBlock sc;
-    stageScene(sc, scene);
+    const SceneView sc = stageScene(scene);
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= count) return;
     Ray r;
@@ -37,8 +36,7 @@ struct SailDumpLaunch {
 };
 // trace() with per-bounce records; the loop body is the one of tracePath().
 __global__ void __launch_bounds__(SAIL_CTA_THREADS) sail_trace_dump_kernel(const __grid_constant__ SailDumpLaunch L) {
-    __shared__ SailSceneBlock sc;
-    stageScene(sc, L.scene);
+    const SceneView sc = stageScene(L.scene);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int x = blockIdx.x * SAIL_TILE_W + (warp & 1) * 8 + (lane & 7);
     const int y = blockIdx.y * SAIL_TILE_H + (warp >> 1) * 4 + (lane >> 3);

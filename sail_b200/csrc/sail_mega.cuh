@@ -23,7 +23,10 @@
 #define SAIL_CTA_THREADS 128
 // Resident CTAs per SM the register allocation is capped for: 8 (64 registers, 32 warps/SM) for the small
 // variants, 4 for those carrying microfacet BSDFs or quadrics (measured: profiles/r01_notes.md).
-#define SAIL_MIN_CTAS(F) (((F) & (SAIL_F_GLOSSY | SAIL_F_QUADRICS)) ? 4 : 8)
+#ifndef SAIL_MIN_CTAS_SMALL
+#define SAIL_MIN_CTAS_SMALL 8
+#endif
+#define SAIL_MIN_CTAS(F) (((F) & (SAIL_F_GLOSSY | SAIL_F_QUADRICS)) ? 4 : SAIL_MIN_CTAS_SMALL)
 
 // Per-frame constants derived on the host from (matrix, eye): the four corner rays of vstrace.glsl:4-7
 // and the edge differences used by the rasteriser-style interpolation (DESIGN.md "Primary rays").
@@ -50,22 +53,31 @@ struct SailLaunch {
     int* hitId;          // W*H
     float* depth;        // W*H
     const SailSceneBlock* scene;
+    unsigned sceneSmem;  // dynamic shared memory bytes (sailSceneSmemBytes)
     SailFrameDev frames[SAIL_MAX_BATCH];
 };
 
-// Stage the used part of the scene block into shared memory (16-byte copies).
-SD void stageScene(SailSceneBlock& dst, const SailSceneBlock* __restrict__ src) {
+// Stage the used part of the scene block into dynamic shared memory (16-byte copies) and return the view.
+extern __shared__ uint4 sail_dyn_smem[];
+SD SceneView stageScene(const SailSceneBlock* __restrict__ src) {
     const int n = src->n, ln = src->ln;
     const uint4* s4 = reinterpret_cast<const uint4*>(src);
-    uint4* d4 = reinterpret_cast<uint4*>(&dst);
+    uint4* d4 = sail_dyn_smem;
     const int tid = threadIdx.x, nt = blockDim.x;
     const int shapeOff = (int)(offsetof(SailSceneBlock, shape) / 16), surfOff = (int)(offsetof(SailSceneBlock, surf) / 16);
     const int lightOff = (int)(offsetof(SailSceneBlock, light) / 16);
+    const int nShape = n * (int)(sizeof(SailShape) / 16), nSurf = n * (int)(sizeof(SailSurface) / 16);
+    const int nLight = (ln + 1) * (int)(sizeof(SailLight) / 16);
     if (tid == 0) d4[0] = s4[0];
-    for (int i = tid; i < n * (int)(sizeof(SailShape) / 16); i += nt) d4[shapeOff + i] = s4[shapeOff + i];
-    for (int i = tid; i < n * (int)(sizeof(SailSurface) / 16); i += nt) d4[surfOff + i] = s4[surfOff + i];
-    for (int i = tid; i < (ln + 1) * (int)(sizeof(SailLight) / 16); i += nt) d4[lightOff + i] = s4[lightOff + i];
+    for (int i = tid; i < nShape; i += nt) d4[1 + i] = s4[shapeOff + i];
+    for (int i = tid; i < nSurf; i += nt) d4[1 + nShape + i] = s4[surfOff + i];
+    for (int i = tid; i < nLight; i += nt) d4[1 + nShape + nSurf + i] = s4[lightOff + i];
     __syncthreads();
+    return sceneViewAt(reinterpret_cast<const unsigned char*>(sail_dyn_smem));
+}
+// Dynamic shared memory a launch needs for a scene with n objects and ln lights.
+static inline size_t sailSceneSmemBytes(int n, int ln) {
+    return 16 + (size_t)n * (sizeof(SailShape) + sizeof(SailSurface)) + (size_t)(ln + 1) * sizeof(SailLight);
 }
 
 // Interpolated primary ray direction at the centre of pixel (x, y): not renormalised.
@@ -77,8 +89,7 @@ SD float nanToZero(float v) { return (v == v) ? v : 0.0f; }
 
 template <int F>
 __global__ void __launch_bounds__(SAIL_CTA_THREADS, SAIL_MIN_CTAS(F)) sail_trace_megakernel(const __grid_constant__ SailLaunch L) {
-    __shared__ SailSceneBlock sc;
-    stageScene(sc, L.scene);
+    const SceneView sc = stageScene(L.scene);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int x = blockIdx.x * SAIL_TILE_W + (warp & 1) * 8 + (lane & 7);

@@ -357,7 +357,7 @@ static __device__ __noinline__ V3 stubShapeNormal(const SailShape& s) {
     return splat3(0.0f);
 }
 template <int F>
-SD V3 sampleGeometry(const SailSceneBlock& sc, V2 u, int i, V3& normal, float& pdf) {
+SD V3 sampleGeometry(const SceneView& sc, V2 u, int i, V3& normal, float& pdf) {
     normal = splat3(0.0f);
     pdf = 0.0f;
     if (sc.n <= 0) return splat3(0.0f);
@@ -391,7 +391,7 @@ SD V3 sampleGeometry(const SailSceneBlock& sc, V2 u, int i, V3& normal, float& p
 
 // ---- light_sample(), shader.light.js:12-22 + area/point/spot.glsl -----------------------------------
 template <int F>
-SD V3 light_sample(const SailSceneBlock& sc, V2 u, V3 hit, V3 insNormal) {
+SD V3 light_sample(const SceneView& sc, V2 u, V3 hit, V3 insNormal) {
     const int ln = sc.ln;
     if (ln == 0) return splat3(0.0f);
     int index = toInt(u.x * (float)ln);  // randomInt(seed, 0, ln): same hash value as u.x
@@ -436,7 +436,7 @@ SD V3 light_sample(const SailSceneBlock& sc, V2 u, V3 hit, V3 insNormal) {
 
 // ---- shade(), path.glsl:1-14 ----------------------------------------------------------------------------
 template <int F>
-SD V3 shade(const SailSceneBlock& sc, const Hit& h, V2 u, V3 wo, V3& wi, V3& fpdf) {
+SD V3 shade(const SceneView& sc, const Hit& h, V2 u, V3 wo, V3& wi, V3& fpdf) {
     V3 f;
     // box faces: |dpdu| is exactly 1 (components 0 / +-1), so normalize() multiplies by rcp(sqrt(1)) = 1
     V3 ss = h.unitDpdu ? h.dpdu : normalize3(h.dpdu), ts = cross3(h.n, ss);
@@ -458,7 +458,7 @@ struct FirstHit {
 // ---- trace(), path.glsl:16-38 -----------------------------------------------------------------------------
 // fx, fy, fz = gl_FragCoord.xyz.  Returns the radiance sample e.
 template <int F>
-SD V3 tracePath(const SailSceneBlock& sc, Ray ray, int maxBounces, float fx, float fy, float fz, float timeSinceStart,
+SD V3 tracePath(const SceneView& sc, Ray ray, int maxBounces, float fx, float fy, float fz, float timeSinceStart,
                 FirstHit& first) {
     V3 fpdf = splat3(1.0f), e = splat3(0.0f);
     first.n = splat3(0.0f);

@@ -31,6 +31,26 @@ struct Ray {
     V3 o, d;
 };
 
+// The scene as the kernels see it: the used part of the SailSceneBlock, packed back to back in dynamic
+// shared memory -- [16 B header][n shapes][n surfaces][ln+1 lights] -- so a CTA reserves only what the
+// scene needs (1.1 KB for the Cornell box) and 8 CTAs fit an SM next to the wavefront's path slots.
+struct SceneView {
+    const SailShape* shape;
+    const SailSurface* surf;
+    const SailLight* light;
+    int n, ln;
+};
+SD SceneView sceneViewAt(const unsigned char* base) {
+    SceneView v;
+    const int* hdr = reinterpret_cast<const int*>(base);
+    v.n = hdr[0];
+    v.ln = hdr[1];
+    v.shape = reinterpret_cast<const SailShape*>(base + 16);
+    v.surf = reinterpret_cast<const SailSurface*>(base + 16 + (size_t)v.n * sizeof(SailShape));
+    v.light = reinterpret_cast<const SailLight*>(base + 16 + (size_t)v.n * (sizeof(SailShape) + sizeof(SailSurface)));
+    return v;
+}
+
 // Kernel specialisation: the reference compiles only the plugins a scene uses into its trace program
 // (/root/reference/src/scene/scene.js:70-112, src/shader/generator.js:107-123).  The AOT equivalent is one
 // kernel instantiation per feature set F; code for absent features is not emitted (smaller I-cache
@@ -213,7 +233,7 @@ struct Nearest {
     int id;
 };
 template <int F>
-SD Nearest nearestObjectInline(const SailSceneBlock& sc, const Ray& ray) {
+SD Nearest nearestObjectInline(const SceneView& sc, const Ray& ray) {
     V3 rd = mk3(dm_rcp(ray.d.x), dm_rcp(ray.d.y), dm_rcp(ray.d.z));
     Nearest r;
     r.t = SAIL_MAX_DISTANCE;
@@ -227,7 +247,7 @@ SD Nearest nearestObjectInline(const SailSceneBlock& sc, const Ray& ray) {
 }
 template <int F>
 static __device__ __noinline__ Nearest nearestObjectRegs(unsigned scAddr, float ox, float oy, float oz, float dx, float dy, float dz) {
-    const SailSceneBlock& sc = *reinterpret_cast<const SailSceneBlock*>(__cvta_shared_to_generic(scAddr));
+    const SceneView sc = sceneViewAt(reinterpret_cast<const unsigned char*>(__cvta_shared_to_generic(scAddr)));
     Ray ray;
     ray.o = mk3(ox, oy, oz);
     ray.d = mk3(dx, dy, dz);
@@ -236,9 +256,9 @@ static __device__ __noinline__ Nearest nearestObjectRegs(unsigned scAddr, float 
 // Variants without next-event estimation have a single call site (the bounce ray): inline it.  With NEE the
 // shadow rays are a second site and one out-of-line copy serves both (I-cache footprint).
 template <int F>
-SD Nearest nearestObject(const SailSceneBlock& sc, const Ray& ray) {
+SD Nearest nearestObject(const SceneView& sc, const Ray& ray) {
     if (!(F & SAIL_F_NEE)) return nearestObjectInline<F>(sc, ray);
-    return nearestObjectRegs<F>((unsigned)__cvta_generic_to_shared(&sc), ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z);
+    return nearestObjectRegs<F>((unsigned)__cvta_generic_to_shared(reinterpret_cast<const unsigned char*>(sc.shape) - 16), ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z);
 }
 
 // ---- procedural textures (texture/shader.texture.js:22-29) -------------------------------------
@@ -295,7 +315,7 @@ SD V3 boxDpdu(V3 normal) {  // cube.glsl:40-48
 // Phase 2: the full hit record of object `i` at distance `t` (the body of intersectX() after the hit
 // test, the per-arm emission mask of shader.shape.js:47-49 and the tail of :38-40).
 template <int F>
-SD void hitRecord(const SailSceneBlock& sc, int i, float t, const Ray& ray, Hit& h) {
+SD void hitRecord(const SceneView& sc, int i, float t, const Ray& ray, Hit& h) {
     const SailShape& s = sc.shape[i];
     const SailSurface& u = sc.surf[i];
     const float* q = s.q;
@@ -469,7 +489,7 @@ SD void hitRecord(const SailSceneBlock& sc, int i, float t, const Ray& ray, Hit&
 
 // intersectObjects() as one call (shader.shape.js:28-51).  Returns false on a miss.
 template <int F>
-SD bool intersectObjects(const SailSceneBlock& sc, const Ray& ray, Hit& h) {
+SD bool intersectObjects(const SceneView& sc, const Ray& ray, Hit& h) {
     Nearest nr = nearestObject<F>(sc, ray);
     h.d = nr.t;
     h.index = nr.id;
@@ -480,7 +500,7 @@ SD bool intersectObjects(const SailSceneBlock& sc, const Ray& ray, Hit& h) {
 
 // testShadow(), shader.light.js:24-31: distance only.
 template <int F>
-SD bool testShadow(const SailSceneBlock& sc, V3 origin, V3 toLight) {
+SD bool testShadow(const SceneView& sc, V3 origin, V3 toLight) {
     Ray r;
     r.o = origin;
     r.d = toLight;

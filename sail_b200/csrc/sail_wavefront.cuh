@@ -1,10 +1,138 @@
-// sail_wavefront.cuh -- wavefront (per-bounce kernels over compacted ray queues) variant.  Placeholder
-// until the queue kernels land: selecting SAIL_KERNEL_WAVEFRONT fails loudly.
+// sail_wavefront.cuh -- the wavefront variant, with its ray queues in SHARED memory.
+//
+// north_star sketches a wavefront tracer: per-bounce stages over ray queues compacted per material.  With
+// queues in HBM these scenes (a few hundred bytes of geometry, all path state in registers) would become
+// bandwidth bound: ~60 B of state written and re-read per path per bounce is 4-5 TB/s at the megakernel's
+// rate.  On B200 a CTA has up to 227 KB of shared memory, so the queue lives there instead:
+// each CTA is a persistent 128-path wavefront that, every bounce,
+//   1. runs the nearest-hit scan for its paths (uniform code, no divergence),
+//   2. counting-sorts the 128 paths by the object they hit (shared-memory histogram + prefix),
+//   3. exchanges path state through shared memory so that consecutive lanes hold paths that hit the same
+//      object -- hence the same shape code, material and texture,
+//   4. evaluates the hit record and the BSDF / light sampling on the regrouped paths.
+// A path is an independent computation, so regrouping changes which lane computes it but not one bit of its
+// value: the output equals the megakernel's exactly (tests/test_gpu_parity.py).  Paths carry their home lane
+// and return their radiance sample to it at the end of each frame; the home lane owns the accumulator.
 #ifndef SAIL_WAVEFRONT_CUH
 #define SAIL_WAVEFRONT_CUH
 #include "sail_mega.cuh"
-struct SailWavefront {
-    cudaError_t render(const SailLaunch&, cudaStream_t, int* launched) { *launched = 0; return cudaErrorNotSupported; }
-    void release() {}
-};
+
+#define SAIL_WF_STATE 16  // words of path state exchanged per bounce
+
+template <int F>
+__global__ void __launch_bounds__(SAIL_CTA_THREADS, SAIL_MIN_CTAS(F)) sail_trace_wavefront(const __grid_constant__ SailLaunch L) {
+    __shared__ float slot[SAIL_WF_STATE][SAIL_CTA_THREADS];  // SoA: lane-consecutive words, conflict free
+    __shared__ float firstHit[6][SAIL_CTA_THREADS];          // n, p of the primary hit, indexed by home lane
+    __shared__ int hist[SAIL_MAX_OBJECTS + 2];
+    const SceneView sc = stageScene(L.scene);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int x = blockIdx.x * SAIL_TILE_W + (warp & 1) * 8 + (lane & 7);
+    int tileY = L.y0 + blockIdx.y * SAIL_TILE_H;
+    if (L.bandStride > 1) {
+        const int tpb = L.bandRows / SAIL_TILE_H;
+        tileY = (L.bandFirst + ((int)blockIdx.y / tpb) * L.bandStride) * L.bandRows + ((int)blockIdx.y % tpb) * SAIL_TILE_H;
+    }
+    const int y = tileY + (warp >> 1) * 4 + (lane >> 3);
+    const bool inside = x < L.W && y < L.y1;  // no early exit: every lane takes part in the barriers
+    const size_t pix = inside ? (size_t)y * L.W + x : 0;
+    const float hx = (float)x + 0.5f, hy = (float)y + 0.5f;  // gl_FragCoord of the home pixel
+    const float a = hx * L.rcpW, b = hy * L.rcpH;
+    const int n = sc.n;
+
+    V3 c = inside ? mk3(L.accum[3 * pix], L.accum[3 * pix + 1], L.accum[3 * pix + 2]) : splat3(0.0f);
+    int firstId = -1;
+    float firstT = SAIL_MAX_DISTANCE;
+
+    for (int k = 0; k < L.nframes; k++) {
+        const SailFrameDev& f = L.frames[k];
+        // path state (travels between lanes)
+        Ray ray;
+        ray.o = ld3(f.eye);
+        ray.d = primaryDir(f, a, b);
+        V3 fpdf = splat3(1.0f), e = splat3(0.0f);
+        float fx = hx, fy = hy;  // RNG key of the path's pixel
+        int home = tid;
+        bool alive = inside;
+        firstHit[0][tid] = 0.0f; firstHit[1][tid] = 0.0f; firstHit[2][tid] = 0.0f;
+        firstHit[3][tid] = 0.0f; firstHit[4][tid] = 0.0f; firstHit[5][tid] = 0.0f;
+
+        for (int deepth = 1; deepth <= L.maxBounces; deepth++) {
+            // ---- stage 1: nearest-hit scan (uniform) ----
+            Nearest nr;
+            nr.t = SAIL_MAX_DISTANCE;
+            nr.id = -1;
+            if (alive) nr = nearestObject<F>(sc, ray);
+            if (deepth == 1) { firstId = nr.id; firstT = nr.t; }  // still on the home lane
+            if (nr.id < 0) alive = false;                          // path.glsl:22 `break`
+            // ---- stage 2: counting sort by hit object ----
+            const int key = alive ? nr.id : n;
+            if (tid <= n) hist[tid] = 0;
+            __syncthreads();
+            const int rank = atomicAdd(&hist[key], 1);
+            __syncthreads();
+            int pos = rank;
+            for (int j = 0; j < key; j++) pos += hist[j];
+            // ---- stage 3: exchange ----
+            slot[0][pos] = ray.o.x; slot[1][pos] = ray.o.y; slot[2][pos] = ray.o.z;
+            slot[3][pos] = ray.d.x; slot[4][pos] = ray.d.y; slot[5][pos] = ray.d.z;
+            slot[6][pos] = fpdf.x; slot[7][pos] = fpdf.y; slot[8][pos] = fpdf.z;
+            slot[9][pos] = e.x; slot[10][pos] = e.y; slot[11][pos] = e.z;
+            slot[12][pos] = fx; slot[13][pos] = fy;
+            slot[14][pos] = nr.t;
+            slot[15][pos] = __int_as_float((home << 8) | (alive ? (nr.id + 1) : 0));
+            __syncthreads();
+            ray.o = mk3(slot[0][tid], slot[1][tid], slot[2][tid]);
+            ray.d = mk3(slot[3][tid], slot[4][tid], slot[5][tid]);
+            fpdf = mk3(slot[6][tid], slot[7][tid], slot[8][tid]);
+            e = mk3(slot[9][tid], slot[10][tid], slot[11][tid]);
+            fx = slot[12][tid]; fy = slot[13][tid];
+            const float t = slot[14][tid];
+            const int tag = __float_as_int(slot[15][tid]);
+            home = tag >> 8;
+            const int id = (tag & 0xff) - 1;
+            alive = id >= 0;
+            // ---- stage 4: hit record + shading on regrouped paths (path.glsl:21-36) ----
+            if (alive) {
+                Hit h;
+                hitRecord<F>(sc, id, t, ray, h);
+                if (deepth == 1) {
+                    firstHit[0][home] = h.n.x; firstHit[1][home] = h.n.y; firstHit[2][home] = h.n.z;
+                    firstHit[3][home] = h.p.x; firstHit[4][home] = h.p.y; firstHit[5][home] = h.p.z;
+                }
+                const float seed = f.timeSinceStart + (float)deepth;
+                V2 u = random2(fx, fy, 0.5f, seed);
+                V3 wi, _fpdf;
+                e = e + shade<F>(sc, h, u, -ray.d, wi, _fpdf) * fpdf;
+                fpdf = fpdf * _fpdf;
+                const float outdot = dot3(h.n, wi);
+                ray.o = h.p + h.n * (outdot > SAIL_EPSILON ? 0.0001f : -0.0001f);
+                ray.d = wi;
+            }
+        }
+        // ---- return the sample to its home lane ----
+        __syncthreads();
+        slot[0][home] = e.x; slot[1][home] = e.y; slot[2][home] = e.z;
+        __syncthreads();
+        V3 es = mk3(nanToZero(slot[0][tid]), nanToZero(slot[1][tid]), nanToZero(slot[2][tid]));
+        if (L.accumMode == 0) c = mix3(es, c, f.textureWeight);  // fstrace.glsl:14
+        else c = c + es;
+        if (k + 1 < L.nframes) __syncthreads();  // slot[] / firstHit[] are rewritten by the next frame
+    }
+    if (!inside) return;
+    L.accum[3 * pix] = c.x;
+    L.accum[3 * pix + 1] = c.y;
+    L.accum[3 * pix + 2] = c.z;
+    if (L.writeAov) {
+        V3 fn = mk3(firstHit[0][tid], firstHit[1][tid], firstHit[2][tid]);
+        V3 fp = mk3(firstHit[3][tid], firstHit[4][tid], firstHit[5][tid]);
+        V3 on = vdivs(fn, 2.0f) + 0.5f;
+        V3 op = normalize3(fp);
+        L.normal[3 * pix] = on.x; L.normal[3 * pix + 1] = on.y; L.normal[3 * pix + 2] = on.z;
+        L.position[3 * pix] = op.x; L.position[3 * pix + 1] = op.y; L.position[3 * pix + 2] = op.z;
+        L.hitId[pix] = firstId;
+        L.depth[pix] = firstT;
+    }
+}
+
 #endif

@@ -44,9 +44,10 @@ def _render_both(capi, oracle, cfg, nframes, kernel=0, batch=False):
     return out, ref
 
 
+@pytest.mark.parametrize("kernel", [0, 1], ids=["mega", "wavefront"])
 @pytest.mark.parametrize("cfg", [1, 2, 3, 5])
-def test_frames_bit_exact(capi, oracle, cfg):
-    out, ref = _render_both(capi, oracle, cfg, 4)
+def test_frames_bit_exact(capi, oracle, cfg, kernel):
+    out, ref = _render_both(capi, oracle, cfg, 4, kernel=kernel, batch=(kernel == 1))
     assert np.array_equal(out["hit_id"], ref["hit_id"]), "primary hit ids differ"
     for name in ("depth", "normal", "position", "color"):
         assert bits_equal(out[name], ref[name]), mismatch_report(out[name], ref[name], "cfg%d %s" % (cfg, name))
