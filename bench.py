@@ -190,7 +190,7 @@ def run_ours(args, rank, world, local_rank):
     r = Renderer((W, H), device=local_rank)
     ctx = r.ctx
     ctx.configure(max_bounces=bounces, accum_mode=capi.ACCUM_SUM if world > 1 else capi.ACCUM_MEAN,
-                  kernel=capi.KERNEL_WAVEFRONT if args.kernel == "wavefront" else capi.KERNEL_MEGA)
+                  kernel={"wavefront": capi.KERNEL_WAVEFRONT, "mega": capi.KERNEL_MEGA, "auto": capi.KERNEL_AUTO}[args.kernel])
     r.update(scene)
     total_steps = warm + steps
     # rank g owns frame indices k = g (mod world)
@@ -301,7 +301,7 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--kernel", default="mega", choices=["mega", "wavefront"])
+    ap.add_argument("--kernel", default="auto", choices=["auto", "mega", "wavefront"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--workload", default="cornell", choices=sorted(WORKLOADS), help="cornell = the headline; others are extra")
     args = ap.parse_args()

@@ -151,7 +151,7 @@ void sail_default_config(sail_config* cfg) {
     cfg->trace_id = 0;
     cfg->max_bounces = 5;  // const/define.glsl:6
     cfg->accum_mode = SAIL_ACCUM_MEAN;
-    cfg->kernel = SAIL_KERNEL_MEGA;
+    cfg->kernel = SAIL_KERNEL_AUTO;
     cfg->filter_id = SAIL_FILTER_COLOR;
     cfg->filter_gamma_c = 2.2f;
 }
@@ -220,7 +220,7 @@ int sail_configure(sail_ctx* ctx, const sail_config* cfg) {
     if (cfg->max_bounces < 0 || cfg->max_bounces > 1024) return setErr(ctx, SAIL_ERR_INVALID, "max_bounces %d out of range", cfg->max_bounces);
     if (cfg->filter_id < 0 || cfg->filter_id > SAIL_FILTER_TONEMAPPING) return setErr(ctx, SAIL_ERR_INVALID, "unknown filter id %d", cfg->filter_id);
     if (cfg->accum_mode != SAIL_ACCUM_MEAN && cfg->accum_mode != SAIL_ACCUM_SUM) return setErr(ctx, SAIL_ERR_INVALID, "unknown accum_mode %d", cfg->accum_mode);
-    if (cfg->kernel != SAIL_KERNEL_MEGA && cfg->kernel != SAIL_KERNEL_WAVEFRONT) return setErr(ctx, SAIL_ERR_INVALID, "unknown kernel %d", cfg->kernel);
+    if (cfg->kernel < SAIL_KERNEL_MEGA || cfg->kernel > SAIL_KERNEL_AUTO) return setErr(ctx, SAIL_ERR_INVALID, "unknown kernel %d", cfg->kernel);
     ctx->cfg = *cfg;
     return SAIL_OK;
 }
@@ -313,7 +313,8 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
     // the variant follows the scene's content, never the caller's mask hints
     dim3 grid((ctx->W + SAIL_TILE_W - 1) / SAIL_TILE_W, tileRows);
     const int F = ctx->hostScene.features & SAIL_F_ALL;
-    if (ctx->cfg.kernel == SAIL_KERNEL_WAVEFRONT) CU(launchWave(F, L, grid, ctx->stream));
+    const bool wave = ctx->cfg.kernel == SAIL_KERNEL_WAVEFRONT || (ctx->cfg.kernel == SAIL_KERNEL_AUTO && (F & SAIL_F_QUADRICS));
+    if (wave) CU(launchWave(F, L, grid, ctx->stream));
     else CU(launchMega(F, L, grid, ctx->stream));
     ctx->launches++;
     CU(cudaEventRecord(ctx->evStop, ctx->stream));

@@ -65,33 +65,38 @@ __global__ void __launch_bounds__(SAIL_CTA_THREADS, SAIL_MIN_CTAS(F)) sail_trace
             if (alive) nr = nearestObject<F>(sc, ray);
             if (deepth == 1) { firstId = nr.id; firstT = nr.t; }  // still on the home lane
             if (nr.id < 0) alive = false;                          // path.glsl:22 `break`
-            // ---- stage 2: counting sort by hit object ----
-            const int key = alive ? nr.id : n;
-            if (tid <= n) hist[tid] = 0;
-            __syncthreads();
-            const int rank = atomicAdd(&hist[key], 1);
-            __syncthreads();
-            int pos = rank;
-            for (int j = 0; j < key; j++) pos += hist[j];
-            // ---- stage 3: exchange ----
-            slot[0][pos] = ray.o.x; slot[1][pos] = ray.o.y; slot[2][pos] = ray.o.z;
-            slot[3][pos] = ray.d.x; slot[4][pos] = ray.d.y; slot[5][pos] = ray.d.z;
-            slot[6][pos] = fpdf.x; slot[7][pos] = fpdf.y; slot[8][pos] = fpdf.z;
-            slot[9][pos] = e.x; slot[10][pos] = e.y; slot[11][pos] = e.z;
-            slot[12][pos] = fx; slot[13][pos] = fy;
-            slot[14][pos] = nr.t;
-            slot[15][pos] = __int_as_float((home << 8) | (alive ? (nr.id + 1) : 0));
-            __syncthreads();
-            ray.o = mk3(slot[0][tid], slot[1][tid], slot[2][tid]);
-            ray.d = mk3(slot[3][tid], slot[4][tid], slot[5][tid]);
-            fpdf = mk3(slot[6][tid], slot[7][tid], slot[8][tid]);
-            e = mk3(slot[9][tid], slot[10][tid], slot[11][tid]);
-            fx = slot[12][tid]; fy = slot[13][tid];
-            const float t = slot[14][tid];
-            const int tag = __float_as_int(slot[15][tid]);
-            home = tag >> 8;
-            const int id = (tag & 0xff) - 1;
-            alive = id >= 0;
+            float t = nr.t;
+            int id = alive ? nr.id : -1;
+            // Primary rays of a tile are coherent already; regroup from the second bounce on.
+            if (deepth > 1) {
+                // ---- stage 2: counting sort by hit object ----
+                const int key = alive ? nr.id : n;
+                if (tid <= n) hist[tid] = 0;
+                __syncthreads();
+                const int rank = atomicAdd(&hist[key], 1);
+                __syncthreads();
+                int pos = rank;
+                for (int j = 0; j < key; j++) pos += hist[j];
+                // ---- stage 3: exchange ----
+                slot[0][pos] = ray.o.x; slot[1][pos] = ray.o.y; slot[2][pos] = ray.o.z;
+                slot[3][pos] = ray.d.x; slot[4][pos] = ray.d.y; slot[5][pos] = ray.d.z;
+                slot[6][pos] = fpdf.x; slot[7][pos] = fpdf.y; slot[8][pos] = fpdf.z;
+                slot[9][pos] = e.x; slot[10][pos] = e.y; slot[11][pos] = e.z;
+                slot[12][pos] = fx; slot[13][pos] = fy;
+                slot[14][pos] = nr.t;
+                slot[15][pos] = __int_as_float((home << 8) | (alive ? (nr.id + 1) : 0));
+                __syncthreads();
+                ray.o = mk3(slot[0][tid], slot[1][tid], slot[2][tid]);
+                ray.d = mk3(slot[3][tid], slot[4][tid], slot[5][tid]);
+                fpdf = mk3(slot[6][tid], slot[7][tid], slot[8][tid]);
+                e = mk3(slot[9][tid], slot[10][tid], slot[11][tid]);
+                fx = slot[12][tid]; fy = slot[13][tid];
+                t = slot[14][tid];
+                const int tag = __float_as_int(slot[15][tid]);
+                home = tag >> 8;
+                id = (tag & 0xff) - 1;
+                alive = id >= 0;
+            }
             // ---- stage 4: hit record + shading on regrouped paths (path.glsl:21-36) ----
             if (alive) {
                 Hit h;

@@ -52,7 +52,7 @@ def test_version_and_defaults(capi):
     cfg = capi.Config()
     lib.sail_default_config(ctypes.byref(cfg))
     assert cfg.max_bounces == 5 and cfg.trace_id == 0 and cfg.accum_mode == capi.ACCUM_MEAN
-    assert cfg.filter_id == 0 and cfg.kernel == capi.KERNEL_MEGA
+    assert cfg.filter_id == 0 and cfg.kernel == capi.KERNEL_AUTO
 
 
 def test_no_cpu_fallback(capi):
