@@ -8,7 +8,7 @@ A "step" = SPP_PER_STEP progressive samples per pixel of the 1920x1080 README Co
 every rank = one sail_render_n() launch per rank.  Multi-GPU is sample sharding: rank g
 traces frame indices k = g (mod N) into a local FP32 sum; nothing is exchanged per step, so scaling is
 "weak" (per-GPU work fixed).  After the timed region the partial sums are combined once with an NCCL
-reduce and checked against rank 0's own re-render of the same frame set.
+reduce (its time is reported as `reduce_ms`) and the result sanity-checked on rank 0.
 
 value  : paths/s with everything resident in HBM, CUDA events on the context's stream, max over ranks.
 e2e    : same metric through sail_b200.Renderer (the user-facing call): every step builds the frame
@@ -201,14 +201,14 @@ def run_ours(args, rank, world, local_rank):
     stream = torch.cuda.ExternalStream(ctx.stream(), device=local_rank)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    sampler = ClockSampler(local_rank)
+    sampler.start()  # runs through the warm-up (same kernel, same load) and the timed region
     for s in range(warm):
         ctx.render_n(batches[s])
     ctx.synchronize()
     torch.cuda.synchronize()
     if dist:
         dist.barrier()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
     launches0 = ctx.launch_count()
     with torch.cuda.stream(stream):
         for s in range(steps):
@@ -298,7 +298,7 @@ def run_ours(args, rank, world, local_rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--kernel", default="auto", choices=["auto", "mega", "wavefront"])
