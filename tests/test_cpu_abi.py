@@ -97,3 +97,12 @@ def test_upload_validation_without_device(capi):
     z18, z16 = np.zeros((0, 18), np.float32), np.zeros((0, 16), np.float32)
     assert capi.scene_features(z18, z16, z18) == 0
     assert capi.scene_features(o[:1], t[:2], l[:1]) >= 0
+
+
+def test_napi_addon_source_compiles_against_the_header():
+    """napi/sail_napi.cc cannot be built here (no Node.js); check at least that it is valid C++ against
+    include/sail_b200.h and the N-API signatures it uses (tests/napi_stub/node_api.h)."""
+    import subprocess
+    r = subprocess.run(["g++", "-std=c++17", "-fsyntax-only", "-Wall", "-I", os.path.join(ROOT, "tests", "napi_stub"), "-I",
+                        os.path.join(ROOT, "include"), os.path.join(ROOT, "napi", "sail_napi.cc")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
