@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(SAIL_CTA_THREADS) sail_trace_dump_kernel(const
         }
         if (!ok) break;
         float seed = L.frame.timeSinceStart + (float)deepth;
-        V2 u = random2(fx, fy, fz, seed);
+        V2 u = random2<SAIL_F_ALL>(fx, fy, fz, seed);
         V3 wi, _fpdf;
         e = e + shade<SAIL_F_ALL>(sc, h, u, -ray.d, wi, _fpdf) * fpdf;
         fpdf = fpdf * _fpdf;

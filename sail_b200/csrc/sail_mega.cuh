@@ -82,8 +82,12 @@ static inline size_t sailSceneSmemBytes(int n, int ln) {
 
 // Interpolated primary ray direction at the centre of pixel (x, y): not renormalised.
 SD V3 primaryDir(const SailFrameDev& f, float a, float b) {
-    if (a + b < 1.0f) return ld3(f.d0) + a * ld3(f.e20) + b * ld3(f.e10);
-    return ld3(f.d3) + (1.0f - a) * ld3(f.e13) + (1.0f - b) * ld3(f.e23);
+    // Both triangles evaluate base + s*e1 + t*e2: pick the operands, not the result (d0,e20,e10 and d3,e13,e23
+    // are laid out back to back in SailFrameDev).
+    const bool lower = a + b < 1.0f;
+    const int o = lower ? 0 : 9;  // floats from d0 to d3
+    const float s = lower ? a : 1.0f - a, t = lower ? b : 1.0f - b;
+    return ld3(f.d0 + o) + s * ld3(f.d0 + o + 3) + t * ld3(f.d0 + o + 6);
 }
 SD float nanToZero(float v) { return (v == v) ? v : 0.0f; }
 
@@ -107,13 +111,16 @@ __global__ void __launch_bounds__(SAIL_CTA_THREADS, SAIL_MIN_CTAS(F)) sail_trace
     const float a = fx * L.rcpW, b = fy * L.rcpH;
 
     V3 c = mk3(L.accum[3 * pix], L.accum[3 * pix + 1], L.accum[3 * pix + 2]);
-    FirstHit first;
+    AovSink aov;
+    aov.normal = L.normal; aov.position = L.position; aov.hitId = L.hitId; aov.depth = L.depth;
+    aov.pix = pix;
     for (int k = 0; k < L.nframes; k++) {
         const SailFrameDev& f = L.frames[k];
         Ray ray;
         ray.o = ld3(f.eye);
         ray.d = primaryDir(f, a, b);
-        V3 e = tracePath<F>(sc, ray, L.maxBounces, fx, fy, fz, f.timeSinceStart, first);
+        aov.on = L.writeAov && k == L.nframes - 1;  // the AOVs of a launch are those of its last frame
+        V3 e = tracePath<F>(sc, ray, L.maxBounces, fx, fy, fz, f.timeSinceStart, aov);
         e = mk3(nanToZero(e.x), nanToZero(e.y), nanToZero(e.z));
         if (L.accumMode == 0) c = mix3(e, c, f.textureWeight);  // fstrace.glsl:14
         else c = c + e;
@@ -121,15 +128,6 @@ __global__ void __launch_bounds__(SAIL_CTA_THREADS, SAIL_MIN_CTAS(F)) sail_trace
     L.accum[3 * pix] = c.x;
     L.accum[3 * pix + 1] = c.y;
     L.accum[3 * pix + 2] = c.z;
-    if (L.writeAov) {
-        // fstrace.glsl:15-16: out_normal = n/2+0.5, out_position = normalize(p)
-        V3 on = vdivs(first.n, 2.0f) + 0.5f;
-        V3 op = normalize3(first.p);
-        L.normal[3 * pix] = on.x; L.normal[3 * pix + 1] = on.y; L.normal[3 * pix + 2] = on.z;
-        L.position[3 * pix] = op.x; L.position[3 * pix + 1] = op.y; L.position[3 * pix + 2] = op.z;
-        L.hitId[pix] = first.id;
-        L.depth[pix] = first.t;
-    }
 }
 
 #endif

@@ -14,11 +14,16 @@
 #include "sail_shapes.cuh"
 
 // ---- util/random.glsl:5-10 ---------------------------------------------------------------------
+// The two sines of one call go through ONE out-of-line function (one call, two independent dependency chains
+// interleaved by the scheduler); the small variants inline them.
+static __device__ __noinline__ float2 sail_sin2(float a, float b) { return make_float2(dm_sin(a), dm_sin(b)); }
+template <int F>
 SD V2 random2(float fx, float fy, float fz, float seed) {
     float ax = fx + seed, ay = fy + seed, az = fz + seed;
     float d1 = ax * 12.9898f + ay * 78.233f + az * 151.7182f;
     float d2 = ax * 63.7264f + ay * 10.873f + az * 623.6736f;
-    return mk2(ffract(sail_sin(d1) * 43758.5453f + seed), ffract(sail_sin(d2) * 43758.5453f + seed));
+    float2 s2 = SAIL_SMALL(F) ? make_float2(dm_sin(d1), dm_sin(d2)) : sail_sin2(d1, d2);
+    return mk2(ffract(s2.x * 43758.5453f + seed), ffract(s2.y * 43758.5453f + seed));
 }
 
 // ---- util/sampler.glsl ---------------------------------------------------------------------------
@@ -448,32 +453,45 @@ SD V3 shade(const SceneView& sc, const Hit& h, V2 u, V3 wo, V3& wi, V3& fpdf) {
     return h.emission + direct;
 }
 
-// First-hit AOVs of one path (fstrace.glsl:8,15-16 plus the hit id / depth this library adds).
-struct FirstHit {
-    V3 n, p;
-    int id;
-    float t;
+// First-hit AOVs of one path (fstrace.glsl:8,15-16 plus the hit id / depth this library adds).  They are
+// written straight to memory from inside the bounce loop of the frame that wants them (the last of a launch)
+// instead of being carried in eight registers through every frame.
+struct AovSink {
+    float* normal;
+    float* position;
+    int* hitId;
+    float* depth;
+    size_t pix;
+    bool on;
 };
+SD void writeAov(const AovSink& a, V3 n, V3 p, int id, float t) {
+    // fstrace.glsl:15-16: out_normal = n/2+0.5, out_position = normalize(p)
+    V3 on = vdivs(n, 2.0f) + 0.5f;
+    V3 op = normalize3(p);
+    a.normal[3 * a.pix] = on.x; a.normal[3 * a.pix + 1] = on.y; a.normal[3 * a.pix + 2] = on.z;
+    a.position[3 * a.pix] = op.x; a.position[3 * a.pix + 1] = op.y; a.position[3 * a.pix + 2] = op.z;
+    a.hitId[a.pix] = id;
+    a.depth[a.pix] = t;
+}
 
 // ---- trace(), path.glsl:16-38 -----------------------------------------------------------------------------
 // fx, fy, fz = gl_FragCoord.xyz.  Returns the radiance sample e.
 template <int F>
 SD V3 tracePath(const SceneView& sc, Ray ray, int maxBounces, float fx, float fy, float fz, float timeSinceStart,
-                FirstHit& first) {
+                const AovSink& aov) {
     V3 fpdf = splat3(1.0f), e = splat3(0.0f);
-    first.n = splat3(0.0f);
-    first.p = splat3(0.0f);
-    first.id = -1;
-    first.t = SAIL_MAX_DISTANCE;
     int deepth = 0;
+    if (aov.on && maxBounces < 1) writeAov(aov, splat3(0.0f), splat3(0.0f), -1, SAIL_MAX_DISTANCE);
     while (deepth++ < maxBounces) {
         Hit h;
         bool ok = intersectObjects<F>(sc, ray, h);
-        if (deepth == 1) { first.id = h.index; first.t = h.d; }
-        if (!ok) break;
-        if (deepth == 1) { first.n = h.n; first.p = h.p; }
+        if (!ok) {
+            if (deepth == 1 && aov.on) writeAov(aov, splat3(0.0f), splat3(0.0f), h.index, h.d);
+            break;
+        }
+        if (deepth == 1 && aov.on) writeAov(aov, h.n, h.p, h.index, h.d);
         float seed = timeSinceStart + (float)deepth;
-        V2 u = random2(fx, fy, fz, seed);
+        V2 u = random2<F>(fx, fy, fz, seed);
         V3 wi, _fpdf;
         e = e + shade<F>(sc, h, u, -ray.d, wi, _fpdf) * fpdf;
         fpdf = fpdf * _fpdf;

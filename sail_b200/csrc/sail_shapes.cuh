@@ -136,19 +136,28 @@ SD float quadricRoot(float a, float b, float c, V3 ol, V3 dl, float zLo, float z
     return t;
 }
 
+SD int opaqueInt(int v) {
+    asm("" : "+r"(v));
+    return v;
+}
 // Phase 1: the value intersectX() would leave in `result.d` (MAX_DISTANCE = no hit).
 template <int F>
 SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd) {
     const float* q = s.q;
-    switch (s.category) {
-        case SAIL_CUBE:          // cube.glsl:65-79: the near slab hit if it is in front, else the far one
-        case SAIL_CORNELLBOX: {  // cornellbox.glsl:67-81: always the far slab hit
-            float tNear, tFar;
-            slab(ld3(s.lo), ld3(s.hi), ray.o, rd, tNear, tFar);
-            float t = -1.0f;
-            if (tNear < tFar) t = (s.category == SAIL_CUBE && tNear > SAIL_EPSILON) ? tNear : tFar;
-            return (t > SAIL_EPSILON) ? t : SAIL_MAX_DISTANCE;
-        }
+    // The three common shapes are tested by a compare chain (2-3 instructions each); a `switch` over all
+    // categories compiles to a bounds check + jump-table load + indirect branch, 11 instructions per object.
+    // opaqueInt() keeps the compiler from folding the chain back into that switch.
+    const int cat = s.category;
+    if (cat == SAIL_CUBE || cat == SAIL_CORNELLBOX) {
+        // cube.glsl:65-79: the near slab hit if it is in front, else the far one
+        // cornellbox.glsl:67-81: always the far slab hit
+        float tNear, tFar;
+        slab(ld3(s.lo), ld3(s.hi), ray.o, rd, tNear, tFar);
+        float t = -1.0f;
+        if (tNear < tFar) t = (cat == SAIL_CUBE && tNear > SAIL_EPSILON) ? tNear : tFar;
+        return (t > SAIL_EPSILON) ? t : SAIL_MAX_DISTANCE;
+    }
+    switch (opaqueInt(cat) == SAIL_SPHERE ? SAIL_SPHERE : (opaqueInt(cat) == SAIL_RECTANGLE ? SAIL_RECTANGLE : ((F & SAIL_F_QUADRICS) ? cat : 0))) {
         case SAIL_SPHERE: {  // sphere.glsl:10-16,45-62
             if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_SPH_C));

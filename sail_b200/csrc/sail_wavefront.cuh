@@ -106,7 +106,7 @@ __global__ void __launch_bounds__(SAIL_CTA_THREADS, SAIL_MIN_CTAS(F)) sail_trace
                     firstHit[3][home] = h.p.x; firstHit[4][home] = h.p.y; firstHit[5][home] = h.p.z;
                 }
                 const float seed = f.timeSinceStart + (float)deepth;
-                V2 u = random2(fx, fy, 0.5f, seed);
+                V2 u = random2<F>(fx, fy, 0.5f, seed);
                 V3 wi, _fpdf;
                 e = e + shade<F>(sc, h, u, -ray.d, wi, _fpdf) * fpdf;
                 fpdf = fpdf * _fpdf;

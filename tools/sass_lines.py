@@ -97,10 +97,16 @@ def main():
     fagg = collections.defaultdict(lambda: [0, 0, 0])
     for i in range(n):
         chain = sass[i][3] or (sass[i][2],)
+        # nvdisasm names the kernel's file for the outermost frame of an out-of-line device function (sail_sin ...),
+        # which live in sail_shapes.cuh above the kernel's first line: look those up there.
+        if chain[-1][0] == "sail_mega.cuh" and chain[-1][1] < 90:
+            chain = tuple(chain[:-1]) + (("sail_shapes.cuh", chain[-1][1]),)
         names = [function_of(idx, fl) for fl in chain]
         bucket = next((nm for nm in reversed(names) if nm not in skip), names[-1])
         a = fagg[bucket]
         a[0] += prof[i][0]; a[1] += prof[i][1]; a[2] += prof[i][2]
+        if os.environ.get("SASS_BUCKET") == bucket:
+            print("  %6.3f%% %-40s %s" % (100.0 * prof[i][0] / tot, sass[i][1][:40], " < ".join("%s:%d" % fl for fl in chain)))
     print("%-28s %8s %8s %8s" % ("function", "inst%", "stall%", "thr/inst"))
     for k, a in sorted(fagg.items(), key=lambda kv: -kv[1][0])[:25]:
         print("%-28s %7.2f%% %7.2f%% %8.1f" % (k, 100.0 * a[0] / tot, 100.0 * a[1] / tots, a[2] / max(a[0], 1)))
