@@ -241,16 +241,16 @@ def run_ours(args, rank, world, local_rank):
 
     # ---------------- end-to-end arm: Renderer API, host buffers in and out -----------------
     scene.sampleCount = 0
-    e2e_steps = max(1, min(steps, 4))
+    e2e_steps = max(1, min(steps, 20))
     for _ in range(2):
-        r.trace(scene, SPP_PER_STEP)
-        r.ctx.present(as_u8=True)
+        r.render(scene, frames=SPP_PER_STEP)
     if dist:
         dist.barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        r.trace(scene, SPP_PER_STEP)      # host: 32 x (jitter, inverse MVP) -> sail_frame[]; H2D as kernel parameters
-        img8 = r.ctx.present(as_u8=True)  # display filter + D2H of the RGBA8 image (synchronises)
+        # host: 32 x (jitter, inverse MVP) -> sail_frame[] -> H2D as kernel parameters; trace; display filter;
+        # D2H of the RGBA8 image into page-locked host memory (synchronises)
+        img8 = r.render(scene, frames=SPP_PER_STEP)
     e2e_s = time.perf_counter() - t0
     assert img8.shape == (H, W, 4)
 

@@ -188,6 +188,12 @@ uint64_t sail_launch_count(const sail_ctx* ctx);
 /* Device time of the most recent sail_render() / sail_render_n() call, from CUDA events recorded on the
  * context's stream around its kernels, in milliseconds (synchronises). */
 int sail_last_render_ms(sail_ctx* ctx, float* ms);
+/* Page-locked host memory for the caller's image / table buffers, so that sail_present / sail_read_* copy
+ * straight into it at full PCIe rate (the destination ArrayBuffer of the reference's gl.readPixels,
+ * src/core/webgl.js:88-92 usage in renderer.js; an N-API host wraps it as an external ArrayBuffer).  Returns NULL
+ * on failure.  Buffers from any other allocator are accepted everywhere too (staged by the driver, slower). */
+void* sail_alloc_host(uint64_t bytes);
+void sail_free_host(void* p);
 
 #ifdef __cplusplus
 }

@@ -16,4 +16,7 @@ def __getattr__(name):
     if name in ("Renderer", "Tracer"):
         from . import renderer
         return getattr(renderer, name)
+    if name in ("Pickup", "Ray"):  # index.js:19 exports the interaction layer too
+        from . import pickup
+        return getattr(pickup, name)
     raise AttributeError(name)

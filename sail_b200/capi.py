@@ -76,6 +76,8 @@ _SIGNATURES = {
     "sail_selftest_math": (ctypes.c_int, [_P, ctypes.POINTER(ctypes.c_uint64)]),
     "sail_launch_count": (ctypes.c_uint64, [_P]),
     "sail_last_render_ms": (ctypes.c_int, [_P, ctypes.POINTER(ctypes.c_float)]),
+    "sail_alloc_host": (ctypes.c_void_p, [ctypes.c_uint64]),
+    "sail_free_host": (None, [ctypes.c_void_p]),
 }
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)
 
@@ -132,6 +134,7 @@ class Context:
         if rows is not None:
             info.row_begin, info.row_end = int(rows[0]), int(rows[1])
         handle = _P()
+        self._pinned = {}
         rc = self.lib.sail_create(ctypes.byref(info), ctypes.byref(handle))
         self._h = handle
         if rc != 0:
@@ -145,6 +148,9 @@ class Context:
 
     def close(self):
         if getattr(self, "_h", None):
+            for p, _ in getattr(self, "_pinned", {}).values():
+                self.lib.sail_free_host(p)
+            self._pinned = {}
             self.lib.sail_destroy(self._h)
             self._h = None
 
@@ -249,10 +255,26 @@ class Context:
     def scale_accum(self, s):
         self._check(self.lib.sail_scale_accum(self._h, float(s)))
 
-    def present(self, as_u8=False, both=False):
+    def host_buffer(self, shape, dtype):
+        """A numpy array over page-locked memory from sail_alloc_host, cached per (shape, dtype) and freed with
+        the context: the reusable destination of ``present(..., pinned=True)`` (the canvas of renderer.js:63)."""
+        key = (tuple(shape), np.dtype(dtype).str)
+        if key not in self._pinned:
+            nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+            p = self.lib.sail_alloc_host(nbytes)
+            if not p:
+                raise SailError(ERR_NOMEM, "sail_alloc_host(%d) failed" % nbytes)
+            arr = np.frombuffer((ctypes.c_uint8 * nbytes).from_address(p), dtype=dtype).reshape(shape)
+            self._pinned[key] = (p, arr)
+        return self._pinned[key][1]
+
+    def present(self, as_u8=False, both=False, pinned=False):
+        """Display pass + read-back.  ``pinned=True`` returns views of context-owned page-locked buffers that the
+        next ``present`` overwrites (like the canvas); the default returns fresh arrays."""
         H, W = self.height, self.width
-        f32 = np.empty((H, W, 4), np.float32) if (both or not as_u8) else None
-        u8 = np.empty((H, W, 4), np.uint8) if (both or as_u8) else None
+        alloc = self.host_buffer if pinned else (lambda shape, dtype: np.empty(shape, dtype))
+        f32 = alloc((H, W, 4), np.float32) if (both or not as_u8) else None
+        u8 = alloc((H, W, 4), np.uint8) if (both or as_u8) else None
         self._check(self.lib.sail_present(self._h, _ptr(f32), _ptr(u8)))
         if both:
             return f32, u8
@@ -312,6 +334,21 @@ def scene_features(objects, texparams, lights):
 
 def frame_array(frames):
     return (Frame * len(frames))(*frames)
+
+
+def frames_from_arrays(matrices, eye, textureWeights, times):
+    """A ``sail_frame[n]`` from (n, 16) column-major matrices, one eye, (n,) weights and (n,) times, filled in one
+    numpy pass (a sail_frame is 21 consecutive floats: include/sail_b200.h)."""
+    m = np.asarray(matrices, dtype=np.float32).reshape(-1, 16)
+    n = m.shape[0]
+    rows = np.empty((n, 21), dtype=np.float32)
+    rows[:, :16] = m
+    rows[:, 16:19] = np.asarray(eye, dtype=np.float32).reshape(3)
+    rows[:, 19] = np.asarray(textureWeights, dtype=np.float32)
+    rows[:, 20] = np.asarray(times, dtype=np.float32)
+    out = (Frame * n)()
+    ctypes.memmove(out, rows.ctypes.data, rows.nbytes)
+    return out
 
 
 def device_count():

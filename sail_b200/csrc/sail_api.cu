@@ -515,4 +515,16 @@ int sail_last_render_ms(sail_ctx* ctx, float* ms) {
     return SAIL_OK;
 }
 
+void* sail_alloc_host(uint64_t bytes) {
+    void* p = nullptr;
+    if (bytes == 0 || cudaHostAlloc(&p, (size_t)bytes, cudaHostAllocPortable) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+void sail_free_host(void* p) {
+    if (p) cudaFreeHost(p);
+}
+
 }  // extern "C"

@@ -4,8 +4,10 @@
 parameters, then ``reverseNormal, matRow, texRow, emission.rgb`` appended by ``Object3D.gen``
 (geometry.js:82-90), zero padded to ``OBJECTS_LENGTH`` = 18 (webgl.js:137).
 ``genTexparams()`` returns material row ++ texture row (geometry.js:75-80).
-The CPU picking intersectors (``intersect``/``boundbox``) belong to the interaction layer
- and are not part of this module.
+``boundbox()`` is the picking bound of the interaction layer (pickup.js:41-62): ``{'min', 'max'}`` with any
+pending ``temporaryTranslation`` NOT applied (as in the reference), or ``False`` for shapes that cannot be
+picked (geometry.js:51-53: Object3D, hence Cornellbox).  The per-shape CPU ``intersect(ray)`` of the reference is
+replaced by the device query behind ``sail_b200.pickup.Pickup`` (sail_intersect_rays).
 """
 import math
 
@@ -32,6 +34,10 @@ class Object3D:
         self.texparamID = 0
         self.temporaryTranslation = [0.0, 0.0, 0.0]
         self.light = any(c != 0 for c in self.emission)
+
+    def boundbox(self):
+        """geometry.js:51-53."""
+        return False
 
     def temporaryTranslate(self, vector):
         self.temporaryTranslation = _vec(vector)
@@ -74,6 +80,10 @@ class Cube(Object3D):
         self.max = self._moved(self.max)
         super().translate()
 
+    def boundbox(self):
+        """geometry.js:103-108."""
+        return {'min': list(self.min), 'max': list(self.max)}
+
     def gen(self, texparamID=None):
         texparamID = self._begin_gen(texparamID)
         self.translate()
@@ -93,6 +103,10 @@ class Sphere(Object3D):
     def translate(self):
         self.c = self._moved(self.c)
         super().translate()
+
+    def boundbox(self):
+        """geometry.js:152-158."""
+        return {'min': [c - self.r for c in self.c], 'max': [c + self.r for c in self.c]}
 
     def gen(self, texparamID=None):
         texparamID = self._begin_gen(texparamID)
@@ -114,6 +128,15 @@ class Rectangle(Object3D):
         self.min = self._moved(self.min)
         self.max = self._moved(self.max)
         super().translate()
+
+    def boundbox(self):
+        """geometry.js:202-222: a flat axis is padded by 0.05 on both sides."""
+        mn, mx = list(self.min), list(self.max)
+        for a in range(3):
+            if self.max[a] == self.min[a]:
+                mx[a] += 0.05
+                mn[a] -= 0.05
+        return {'min': mn, 'max': mx}
 
     def gen(self, texparamID=None):
         texparamID = self._begin_gen(texparamID)
@@ -138,6 +161,12 @@ class Cone(_Positioned):
         self.height = float(height)
         self.radius = float(radius)
 
+    def boundbox(self):
+        """geometry.js:279-284."""
+        p = self.position
+        return {'min': [p[0] - self.radius, p[1], p[2] - self.radius],
+                'max': [p[0] + self.radius, p[1] + self.height, p[2] + self.radius]}
+
     def gen(self, texparamID=None):
         texparamID = self._begin_gen(texparamID)
         self.translate()
@@ -155,6 +184,12 @@ class Cylinder(_Positioned):
         self.height = float(height)
         self.radius = float(radius)
 
+    def boundbox(self):
+        """geometry.js:345-350."""
+        p = self.position
+        return {'min': [p[0] - self.radius, p[1], p[2] - self.radius],
+                'max': [p[0] + self.radius, p[1] + self.height, p[2] + self.radius]}
+
     def gen(self, texparamID=None):
         texparamID = self._begin_gen(texparamID)
         self.translate()
@@ -171,6 +206,12 @@ class Disk(_Positioned):
         self.position = _vec(position)
         self.radius = float(radius)
         self.innerRadius = float(innerRadius)
+
+    def boundbox(self):
+        """geometry.js:410-415."""
+        p = self.position
+        return {'min': [p[0] - self.radius, p[1] - 0.05, p[2] - self.radius],
+                'max': [p[0] + self.radius, p[1] + 0.05, p[2] + self.radius]}
 
     def gen(self, texparamID=None):
         texparamID = self._begin_gen(texparamID)
@@ -219,6 +260,12 @@ class Hyperboloid(_Positioned):
         if not math.isfinite(self.ah):
             raise ValueError("the p1,p2 of hyperboloid is illegal")
 
+    def boundbox(self):
+        """geometry.js:489-494."""
+        p = self.position
+        return {'min': [p[0] - self.rMax, p[1] + self.zMin, p[2] - self.rMax],
+                'max': [p[0] + self.rMax, p[1] + self.zMax, p[2] + self.rMax]}
+
     def gen(self, texparamID=None):
         texparamID = self._begin_gen(texparamID)
         self.translate()
@@ -236,6 +283,13 @@ class Paraboloid(_Positioned):
         self.z0 = float(z0)
         self.z1 = float(z1)
         self.radius = float(radius)
+
+    def boundbox(self):
+        """geometry.js:557-562 (its zMin/zMax are z0/z1 sorted, geometry.js:549-550)."""
+        p = self.position
+        zMin, zMax = min(self.z0, self.z1), max(self.z0, self.z1)
+        return {'min': [p[0] - self.radius, p[1] + zMin, p[2] - self.radius],
+                'max': [p[0] + self.radius, p[1] + zMax, p[2] + self.radius]}
 
     def gen(self, texparamID=None):
         texparamID = self._begin_gen(texparamID)

@@ -13,7 +13,7 @@ import numpy as np
 from . import capi
 from .filters import lower_filter
 from .scene import plugin_masks
-from .schedule import FrameSchedule, frame_matrix
+from .schedule import FrameSchedule, frame_matrices, frame_matrix
 from .wire import serialize_objects, serialize_scene
 
 
@@ -44,6 +44,13 @@ class Tracer:
         k = int(sampleCount)
         m = frame_matrix(modelviewProjection, self.schedule.jitter_unit(k), self.ctx.width, self.ctx.height)
         return capi.make_frame(m, eye, k / (k + 1.0), self.schedule.time(k))
+
+    def frames(self, modelviewProjection, eye, sampleCount, count):
+        """``count`` consecutive frames starting at ``sampleCount`` as one sail_frame[] (same values as ``frame``)."""
+        k0 = int(sampleCount)
+        m = frame_matrices(modelviewProjection, self.schedule.jitter_units(k0, count), self.ctx.width, self.ctx.height)
+        k = np.arange(k0, k0 + count, dtype=np.float64)
+        return capi.frames_from_arrays(m, eye, k / (k + 1.0), self.schedule.times(k0, count))
 
     def render(self, modelviewProjection, eye, sampleCount):
         """tracer.js:92-101."""
@@ -86,15 +93,24 @@ class Renderer:
             self.updateObjects(scene)
         if scene.sampleCount == 0:
             self.ctx.reset()
-        fr = [self.tracer.frame(scene.mat, scene.eye, scene.sampleCount + i) for i in range(frames)]
+        fr = self.tracer.frames(scene.mat, scene.eye, scene.sampleCount, frames)
         scene.sampleCount += frames
         self.ctx.render_n(fr)
 
-    def render(self, scene, as_u8=True):
-        """renderer.js:54-72: one progressive sample, then the display pass; returns the displayed image
-        (H x W x 4, row 0 = bottom).  The selection wireframe (renderer.js:65-71) is editor UI, out of scope."""
-        self.trace(scene, 1)
-        return self.ctx.present(as_u8=as_u8)
+    def render(self, scene, as_u8=True, frames=1):
+        """renderer.js:54-72: one progressive sample (or ``frames`` of them), then the display pass; returns the
+        displayed image (H x W x 4, row 0 = bottom) in the renderer's page-locked "canvas" buffer, which the next
+        ``render`` overwrites.  The selection wireframe (renderer.js:65-71) is editor UI, out of scope."""
+        self.trace(scene, frames)
+        return self.ctx.present(as_u8=as_u8, pinned=True)
+
+    def save(self, path, img=None):
+        """Write the displayed image (``img`` or a fresh display pass of the current accumulation) as .png or .ppm --
+        the headless stand-in for the canvas of renderer.js:63."""
+        from . import image
+        if img is None:
+            img = self.ctx.present(as_u8=True, pinned=True)
+        (image.write_ppm if str(path).lower().endswith(".ppm") else image.write_png)(path, img)
 
     def readPixels(self, which=capi.AOV_COLOR):
         return self.ctx.read_aov(which)

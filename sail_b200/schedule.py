@@ -45,12 +45,29 @@ class FrameSchedule:
     def time(self, k):
         return float(np.float32((k + 1) / 60.0))
 
+    def jitter_units(self, k0, count):
+        """(count, 2) array of jitter_unit(k0) .. jitter_unit(k0 + count - 1)."""
+        self._ensure(2 * (k0 + count))
+        return np.asarray(self._u[2 * k0:2 * (k0 + count)], dtype=np.float64).reshape(count, 2) * 2 - 1
+
+    def times(self, k0, count):
+        return ((np.arange(k0, k0 + count, dtype=np.float64) + 1) / 60.0).astype(np.float32)
+
+
+def frame_matrices(mvp, jitter_units, width, height):
+    """tracer.js:94-96 for a batch of frames: inverse(Translation((jx, jy, 0)) * MVP) in double precision, each
+    returned as the column-major float32[16] that ``gl.uniformMatrix4fv`` receives (matrix.js:612-622).
+    ``jitter_units``: (n, 2) values in [-1, 1).  Translation * MVP only adds jx (jy) times the last row of MVP to
+    its first (second) row, which is written out so that one frame and a batch give the same bits."""
+    mvp = np.asarray(mvp, dtype=np.float64)
+    j = np.asarray(jitter_units, dtype=np.float64).reshape(-1, 2)
+    m = np.broadcast_to(mvp, (j.shape[0], 4, 4)).copy()
+    m[:, 0, :] += (j[:, 0] / width)[:, None] * mvp[3, :]
+    m[:, 1, :] += (j[:, 1] / height)[:, None] * mvp[3, :]
+    inv = np.linalg.inv(m)
+    return np.ascontiguousarray(inv.transpose(0, 2, 1).reshape(-1, 16).astype(np.float32))
+
 
 def frame_matrix(mvp, jitter_unit, width, height):
-    """tracer.js:94-96: inverse(Translation((jx, jy, 0)) * MVP), double precision, returned as the
-    column-major float32[16] that ``gl.uniformMatrix4fv`` receives (matrix.js:612-622)."""
-    t = np.eye(4, dtype=np.float64)
-    t[0, 3] = jitter_unit[0] / width
-    t[1, 3] = jitter_unit[1] / height
-    inv = np.linalg.inv(t @ np.asarray(mvp, dtype=np.float64))
-    return np.ascontiguousarray(inv.T.reshape(16).astype(np.float32))
+    """One frame of ``frame_matrices``."""
+    return frame_matrices(mvp, [jitter_unit], width, height)[0]

@@ -117,3 +117,60 @@ def test_frame_schedule_and_matrix():
     assert np.allclose(m @ mvp, np.eye(4), atol=1e-5)
     # camera.js:38-41: X axis negated (mirror image, Q14): a standard lookAt down +z gives x = (-1,0,0)
     assert cam.modelview[0, 0] == pytest.approx(1.0)
+
+
+def test_batched_frames_equal_single_frames():
+    """Tracer.frames (one numpy pass, used by Renderer.trace) must give the very bytes of Tracer.frame per sample."""
+    from sail_b200 import capi
+    from sail_b200.renderer import Tracer
+    from sail_b200.schedule import FrameSchedule
+
+    class Size:
+        width, height = 320, 200
+
+    from conftest import scene_tables
+    scene, *_ = scene_tables(2, 320, 200)
+    tr = Tracer(Size(), FrameSchedule())
+    one = capi.frame_array([tr.frame(scene.mat, scene.eye, k) for k in range(7, 7 + 40)])
+    many = tr.frames(scene.mat, scene.eye, 7, 40)
+    assert bytes(one) == bytes(many)
+
+
+def test_image_writers_round_trip(tmp_path):
+    """PNG/PPM writers of the display output: bottom-up device rows come out top-down."""
+    from sail_b200 import image
+    rng = np.random.default_rng(3)
+    img = rng.integers(0, 256, size=(37, 53, 4), dtype=np.uint8)
+    image.write_png(tmp_path / "a.png", img)
+    assert np.array_equal(image.read_png(tmp_path / "a.png"), img[::-1, :, :3])
+    image.write_png(tmp_path / "b.png", img, alpha=True)
+    assert np.array_equal(image.read_png(tmp_path / "b.png"), img[::-1])
+    image.write_ppm(tmp_path / "a.ppm", img)
+    raw = open(tmp_path / "a.ppm", "rb").read()
+    assert raw.startswith(b"P6\n53 37\n255\n") and raw[len(b"P6\n53 37\n255\n"):] == img[::-1, :, :3].tobytes()
+    # float display output: clamp + round to nearest like an RGBA8 target
+    f = np.array([[[0.0, 0.5, 1.0, 1.0], [-1.0, 2.0, float("nan"), 1.0]]], np.float32)
+    image.write_png(tmp_path / "c.png", f)
+    assert image.read_png(tmp_path / "c.png").tolist() == [[[0, 128, 255], [0, 255, 0]]]
+
+
+def test_pickup_ray_and_boundboxes():
+    """pickup.js:9-38 and the boundbox() of every shape (geometry.js), host-side arithmetic only."""
+    from sail_b200.pickup import MAXVALUE, Ray
+    box = {'min': [-1, -1, 4], 'max': [1, 1, 6]}
+    r = Ray([0, 0, 0], [0, 0, 2])
+    assert r.testBoundBox(box) and r.intersectBoundBox(box) == 2.0      # un-normalised dir: t in units of |dir|
+    assert Ray([0, 0, 5], [0, 0, 1]).intersectBoundBox(box) == 1.0       # inside: far face
+    assert not Ray([0, 0, 0], [0, 0, -1]).testBoundBox(box)
+    assert Ray([0, 5, 0], [0, 0, 1]).intersectBoundBox(box) == MAXVALUE
+    m, w = Sail.Matte(0.7), Sail.Color.WHITE
+    assert Sail.Cornellbox().boundbox() is False                         # geometry.js:51-53: walls are not pickable
+    assert Sail.Sphere([1, 2, 3], 0.5, m, w).boundbox() == {'min': [0.5, 1.5, 2.5], 'max': [1.5, 2.5, 3.5]}
+    bb = Sail.Rectangle([0, 1, 0], [2, 1, 3], m, w).boundbox()
+    assert bb['min'] == [0, 0.95, 0] and bb['max'] == [2, 1.05, 3]
+    assert Sail.Cone([0, 0, 0], 2, 1, m, w).boundbox() == {'min': [-1, 0, -1], 'max': [1, 2, 1]}
+    assert Sail.Disk([0, 1, 0], 2, 0.5, m, w).boundbox() == {'min': [-2, 0.95, -2], 'max': [2, 1.05, 2]}
+    hb = Sail.Hyperboloid([0, 1, 0], [0.4, -0.3, -0.6], [0.4, 0.3, 0.6], m, w).boundbox()
+    assert hb['min'][1] == pytest.approx(0.4) and hb['max'][1] == pytest.approx(1.6) and hb['max'][0] == pytest.approx(0.5)
+    pb = Sail.Paraboloid([0, 0, 0], 0, 1, 0.6, m, w).boundbox()
+    assert pb == {'min': [-0.6, 0, -0.6], 'max': [0.6, 1, 0.6]}

@@ -281,3 +281,54 @@ def test_renderer_api_matches_reference_call_order(capi, oracle):
     r.render(scene)
     assert scene.sampleCount == 1
     r.close()
+
+
+def test_pickup_selects_what_is_drawn_and_drag_reuploads_objects(capi, tmp_path):
+    """Pickup.pick asks the device for the first hit of the pixel's ray (what is picked is what
+    the HIT_ID AOV shows), the Cornell box stays unpickable, and a drag ends in updateObjects (renderer.js:57-60)."""
+    import sail_b200 as Sail
+    from sail_b200.renderer import Renderer
+    W, H = 128, 128
+    scene, o, t, l, bounces = scene_tables(1, W, H)
+    r = Renderer((W, H))
+    r.update(scene)
+    r.render(scene)
+    hit = r.readPixels(capi.AOV_HIT_ID)          # row 0 = bottom
+    pick = Sail.Pickup(scene, r)
+    seen = {}
+    for y in range(4, H, 8):                      # canvas pixels, y down; sample pixel centres
+        for x in range(4, W, 8):
+            i = int(hit[H - 1 - y, x])
+            if (hit[H - 3 - y:H + 2 - y, x - 2:x + 3] != i).any():
+                continue                          # silhouette: the AOV's ray is jittered by up to a pixel, the pick ray is not
+            ok = pick.pick(x + 0.5, y + 0.5)
+            obj = scene.objects[i] if i >= 0 else None
+            if obj is not None and obj.boundbox():
+                assert ok and scene.select is obj, (x, y, i)
+            else:
+                assert not ok and scene.select is None, (x, y, i)
+            seen[i] = seen.get(i, 0) + 1
+    assert set(seen) >= {1, 2}, seen              # walls and the sphere were both probed
+    # drag the sphere: pick it, begin, move, end -> temporaryTranslate, moving flag, re-upload on render
+    ys, xs = np.nonzero(hit == 2)
+    cy, cx = int(np.median(ys)), int(np.median(xs))
+    px, py = cx + 0.5, (H - 1 - cy) + 0.5
+    assert pick.pick(px, py) and isinstance(scene.select, Sail.Sphere)
+    before = list(scene.select.c)
+    assert pick.movingBegin(px, py) and scene.moving
+    pick.moving(px + 6, py)
+    assert scene.select.temporaryTranslation != [0.0, 0.0, 0.0]
+    for _ in range(2):
+        r.render(scene)                           # moving: sampleCount reset + updateObjects each frame
+    assert scene.sampleCount == 1 and scene.select.c != before
+    pick.movingEnd(px + 6, py)
+    assert not scene.moving
+    moved = r.readPixels(capi.AOV_HIT_ID)
+    assert (moved == 2).any() and not np.array_equal(moved == 2, hit == 2)
+    # the displayed image goes to a file instead of a canvas (8(f) rank 3)
+    from sail_b200 import image
+    img8 = r.render(scene)
+    r.save(tmp_path / "cornell.png", img8)
+    back = image.read_png(tmp_path / "cornell.png")
+    assert np.array_equal(back, np.asarray(img8)[::-1, :, :3])
+    r.close()
