@@ -52,12 +52,16 @@ def gather_rows(image, my_rows, all_rows, dst=0, group=None):
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
         return image
     rank, world = dist.get_rank(group), dist.get_world_size(group)
-    mine = torch.cat([image[a:b] for a, b in my_rows], dim=0).contiguous() if my_rows else image[:0].contiguous()
+    counts = [sum(b - a for a, b in all_rows[r]) for r in range(world)]
+    most = max(counts)
+    # NCCL's gather wants one size for every rank: ranks with fewer rows pad up to the largest share
+    mine = torch.zeros((most,) + tuple(image.shape[1:]), dtype=image.dtype, device=image.device)
+    off = 0
+    for a, b in my_rows:
+        mine[off:off + (b - a)] = image[a:b]
+        off += b - a
     if rank == dst:
-        bufs = []
-        for r in range(world):
-            n = sum(b - a for a, b in all_rows[r])
-            bufs.append(torch.empty((n,) + tuple(image.shape[1:]), dtype=image.dtype, device=image.device))
+        bufs = [torch.empty_like(mine) for _ in range(world)]
         dist.gather(mine, bufs, dst=dst, group=group)
         full = torch.empty_like(image)
         for r in range(world):
