@@ -43,6 +43,7 @@ class Oracle:
                                           _f32p, _f32p, ctypes.c_void_p]
         lib.oracle_intersect_rays.argtypes = [ctypes.c_int, _f32p, _i32p, _f32p, ctypes.c_void_p, ctypes.c_void_p]
         lib.oracle_intersect_detail.argtypes = [_f32p, _f32p]
+        lib.oracle_unit.argtypes = [ctypes.c_int, _f32p, _f32p]
         lib.oracle_random2.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_float, _f32p]
         lib.oracle_detmath.argtypes = [ctypes.c_int, ctypes.c_int, _f32p, ctypes.c_void_p, _f32p]
         lib.oracle_present.argtypes = [ctypes.c_int, ctypes.c_int, _f32p, _f32p, _f32p, ctypes.c_int, ctypes.c_float,
@@ -116,6 +117,20 @@ class Oracle:
         bb = None if b is None else np.ascontiguousarray(b, dtype=np.float32).reshape(-1)
         self.lib.oracle_detmath(names[which], a.size, a, _opt(bb), out)
         return out
+
+    UNITS = {"frDielectric": (0, 1), "frConductor": (1, 3), "trowbridgeReitz_d": (2, 1), "trowbridgeReitz_sample_wh": (3, 3),
+             "trowbridgeReitz_pdf": (4, 1), "getSurfaceColor": (5, 3), "cosineSampleHemisphere": (6, 3),
+             "uniformSampleSphere": (7, 3), "concentricSampleDisk": (8, 2), "quadratic": (9, 3), "light_arm": (10, 3)}
+
+    def unit(self, name, *args):
+        """One shader function on scalar/vector arguments (flattened in order); see oracle_unit in oracle.cpp."""
+        which, nout = self.UNITS[name]
+        a = np.concatenate([np.asarray(x, np.float32).reshape(-1) for x in args]).astype(np.float32)
+        a = np.concatenate([a, np.zeros(16, np.float32)])
+        out = np.zeros(4, np.float32)
+        if self.lib.oracle_unit(which, a, out) != 0:
+            raise ValueError("oracle_unit(%s) rejected its arguments" % name)
+        return out[:nout].copy() if nout > 1 else out[0]
 
     def present(self, color, normal, position, filt, as_u8=False):
         """Display pass.  ``filt`` = dict(filter_id, gamma_c, radius, weights) from sail_b200.filters.lower_filter."""

@@ -167,6 +167,47 @@ void oracle_detmath(int which, int N, const float* a, const float* b, float* out
     }
 }
 
+// Single shader functions for known-answer tests.  `in`/`out` are small float arrays:
+//   0 frDielectric(cosThetaI, etaI, etaT) -> 1          fresnel.glsl:31-46
+//   1 frConductor(cosThetaI, etaI[3], etaT[3], k[3]) -> 3  fresnel.glsl:48-70
+//   2 trowbridgeReitz_d(ax, ay, wh[3]) -> 1             microfacet.glsl:61-67
+//   3 trowbridgeReitz_sample_wh(u[2], ax, ay, wo[3]) -> 3   microfacet.glsl:41-59
+//   4 trowbridgeReitz_pdf(ax, ay, wo[3], wh[3]) -> 1    microfacet.glsl:69-71
+//   5 getSurfaceColor(hit[3], uv[2], texparams row) -> 3 (scene set)  shader.texture.js:22-29
+//   6 cosineSampleHemisphere(u[2]) -> 3, 7 uniformSampleSphere(u[2]) -> 3, 8 concentricSampleDisk(u[2]) -> 2   sampler.glsl
+//   9 quadratic(A, B, C) -> ok, t0, t1                  utility.glsl:37-51
+//  10 light arm of row `index`: in = pixel x, y, seed, hit[3], normal[3], index -> 3 (scene set)  area/point/spot.glsl
+int oracle_unit(int which, const float* in, float* out) {
+    auto v3 = [&](int o) { return vec3(in[o], in[o + 1], in[o + 2]); };
+    auto put3 = [&](vec3 v) { out[0] = v.x.v; out[1] = v.y.v; out[2] = v.z.v; };
+    switch (which) {
+        case 0: out[0] = frDielectric(real(in[0]), real(in[1]), real(in[2])).v; return 0;
+        case 1: put3(frConductor(real(in[0]), v3(1), v3(4), v3(7))); return 0;
+        case 2: out[0] = trowbridgeReitz_d(real(in[0]), real(in[1]), v3(2)).v; return 0;
+        case 3: put3(trowbridgeReitz_sample_wh(vec2(in[0], in[1]), real(in[2]), real(in[3]), v3(4))); return 0;
+        case 4: out[0] = trowbridgeReitz_pdf(real(in[0]), real(in[1]), v3(2), v3(5)).v; return 0;
+        case 5: put3(getSurfaceColor(v3(0), vec2(in[3], in[4]), rowCoord((int)in[5], tn_))); return 0;
+        case 6: put3(cosineSampleHemisphere(vec2(in[0], in[1]))); return 0;
+        case 7: put3(uniformSampleSphere(vec2(in[0], in[1]))); return 0;
+        case 8: { vec2 d = concentricSampleDisk(vec2(in[0], in[1])); out[0] = d.x.v; out[1] = d.y.v; return 0; }
+        case 9: { real t0 = 0.0f, t1 = 0.0f; bool ok = quadratic(real(in[0]), real(in[1]), real(in[2]), t0, t1);
+                  out[0] = ok ? 1.0f : 0.0f; out[1] = t0.v; out[2] = t1.v; return 0; }
+        case 10: {
+            gl_FragCoord = vec3(in[0] + 0.5f, in[1] + 0.5f, 0.5f);
+            int index = (int)in[9];
+            if (index < 0 || index >= ln_) return -1;
+            real row = rowCoord(index, ln_);
+            int cat = readInt(lights, vec2(0.0f, row), LIGHTS_LENGTH);
+            if (cat == AREA) put3(area_sample(parseArea(row), real(in[2]), v3(3), v3(6)));
+            else if (cat == POINT) put3(point_sample(parsePoint(row), real(in[2]), v3(3), v3(6)));
+            else if (cat == SPOT) put3(spot_sample(parseSpot(row), real(in[2]), v3(3), v3(6)));
+            else return -1;
+            return 0;
+        }
+    }
+    return -1;
+}
+
 int oracle_counts_ops(void) {
 #ifdef SAIL_COUNT_OPS
     return 1;

@@ -165,3 +165,120 @@ def _params(name, **kw):
     for k, v in kw.items():
         pp.addParam(k, v)
     return pp
+
+
+def test_fresnel_known_answers(oracle):
+    """fresnel.glsl:31-70 against float64 closed forms."""
+    assert oracle.unit("frDielectric", 1.0, 1.0, 1.5) == pytest.approx(0.04, rel=1e-6)           # ((n-1)/(n+1))^2
+    assert oracle.unit("frDielectric", 1.0, 1.0, 1.0) == pytest.approx(0.0, abs=1e-12)
+    assert oracle.unit("frDielectric", 0.2, 1.5, 1.0) == 1.0                                     # total internal reflection
+    c = math.cos(math.radians(56.30993247))                                                      # Brewster angle of n = 1.5
+    ct = math.sqrt(1 - (math.sin(math.radians(56.30993247)) / 1.5) ** 2)
+    rs = (c - 1.5 * ct) / (c + 1.5 * ct)
+    assert oracle.unit("frDielectric", c, 1.0, 1.5) == pytest.approx(0.5 * rs * rs, rel=1e-4)    # r_parallel vanishes
+    # conductor at normal incidence: ((n-1)^2 + k^2) / ((n+1)^2 + k^2), per channel
+    eta, k = np.array([0.2, 0.92, 1.1]), np.array([3.9, 2.45, 2.14])
+    want = ((eta - 1) ** 2 + k ** 2) / ((eta + 1) ** 2 + k ** 2)
+    got = oracle.unit("frConductor", 1.0, [1, 1, 1], eta, k)
+    assert np.allclose(got, want, rtol=2e-6)
+    # grazing incidence reflects everything
+    assert np.allclose(oracle.unit("frConductor", 1e-4, [1, 1, 1], eta, k), 1.0, atol=2e-3)
+
+
+def test_trowbridge_reitz_known_answers(oracle):
+    """microfacet.glsl:41-71: D(n) = 1/(pi ax ay); D integrates to 1 against cos; sample_wh uses u.x only (Q11)."""
+    assert oracle.unit("trowbridgeReitz_d", 0.3, 0.3, [0, 0, 1]) == pytest.approx(1 / (math.pi * 0.09), rel=1e-6)
+    assert oracle.unit("trowbridgeReitz_d", 0.2, 0.5, [0, 0, 1]) == pytest.approx(1 / (math.pi * 0.1), rel=1e-6)
+    assert oracle.unit("trowbridgeReitz_d", 0.3, 0.3, [1, 0, 0]) == pytest.approx(0.001)          # tan2Theta = inf sentinel
+    # midpoint quadrature of D(wh) cos(theta) over the hemisphere = 1
+    ax, ay, n = 0.4, 0.25, 96
+    th = (np.arange(n) + 0.5) * (math.pi / 2 / n)
+    ph = (np.arange(2 * n) + 0.5) * (math.pi / n)
+    total = 0.0
+    for t in th:
+        for p in ph[::4]:
+            wh = [math.sin(t) * math.cos(p), math.sin(t) * math.sin(p), math.cos(t)]
+            total += float(oracle.unit("trowbridgeReitz_d", ax, ay, wh)) * math.cos(t) * math.sin(t)
+    total *= (math.pi / 2 / n) * (4 * math.pi / n)
+    assert total == pytest.approx(1.0, abs=0.02)
+    wo = [0.3, 0.1, 0.9]
+    a = oracle.unit("trowbridgeReitz_sample_wh", [0.37, 0.11], 0.3, 0.3, wo)
+    b = oracle.unit("trowbridgeReitz_sample_wh", [0.37, 0.93], 0.3, 0.3, wo)
+    assert np.array_equal(a, b) and a[2] > 0 and np.linalg.norm(a) == pytest.approx(1.0, abs=1e-6)   # u.y unused
+    # isotropic: cos(theta) = 1/sqrt(1 + a^2 u/(1-u)), phi = 2 pi u
+    ct = 1 / math.sqrt(1 + 0.09 * 0.37 / 0.63)
+    assert a[2] == pytest.approx(ct, rel=1e-6) and math.atan2(a[1], a[0]) == pytest.approx(2 * math.pi * 0.37, abs=1e-5)
+    assert oracle.unit("trowbridgeReitz_pdf", 0.3, 0.3, wo, a) == pytest.approx(
+        float(oracle.unit("trowbridgeReitz_d", 0.3, 0.3, a)) * abs(float(a[2])), rel=1e-6)
+
+
+def test_samplers_and_quadratic_known_answers(oracle):
+    """sampler.glsl and utility.glsl:37-51."""
+    for u in ([0.25, 0.6], [0.9, 0.05], [0.0, 0.0]):
+        w = oracle.unit("cosineSampleHemisphere", u)
+        assert w[2] == pytest.approx(math.sqrt(1 - u[0]), abs=1e-6) and np.linalg.norm(w) == pytest.approx(1.0, abs=1e-6)
+        assert math.atan2(w[1], w[0]) % (2 * math.pi) == pytest.approx((2 * math.pi * u[1]) % (2 * math.pi), abs=1e-5)
+        s = oracle.unit("uniformSampleSphere", u)
+        assert s[2] == pytest.approx(1 - 2 * u[0], abs=1e-6) and np.linalg.norm(s) == pytest.approx(1.0, abs=1e-6)
+    assert np.array_equal(oracle.unit("concentricSampleDisk", [0.5, 0.5]), [0, 0])
+    d = oracle.unit("concentricSampleDisk", [1.0, 0.5])
+    assert d[0] == pytest.approx(1.0) and d[1] == pytest.approx(0.0, abs=1e-7)
+    ok, t0, t1 = oracle.unit("quadratic", 1.0, -3.0, 2.0)
+    assert ok == 1 and (t0, t1) == (1.0, 2.0)
+    assert oracle.unit("quadratic", 1.0, 0.0, 1.0)[0] == 0                                        # negative discriminant
+    ok, t0, t1 = oracle.unit("quadratic", 1.0, -1e4, 1.0)                                         # stable small root: C/q
+    assert ok == 1 and t0 == pytest.approx(1e-4, rel=1e-6) and t1 == pytest.approx(1e4, rel=1e-6)
+
+
+def test_textures_known_answers(oracle):
+    """texture/*.glsl through getSurfaceColor on a hand-built texParams table."""
+    import sail_b200 as Sail
+    tex = [Sail.UniformColor([0.1, 0.2, 0.3]), Sail.Checkerboard(0.25, 0.05), Sail.Checkerboard2([1, 0, 0], [0, 0, 1], 0.5),
+           Sail.Mix([1, 0, 0], [0, 0, 1], 0.25), Sail.Scale([0.5, 0.5, 1.0], [0.5, 1.0, 0.2]), Sail.UV()]
+    rows = np.array([t.gen() for t in tex], np.float32)
+    oracle.set_scene(np.zeros((0, 18), np.float32), rows, np.zeros((0, 18), np.float32))
+    hit = [0, 0, 0]
+    assert np.allclose(oracle.unit("getSurfaceColor", hit, [0.3, 0.7], 0), [0.1, 0.2, 0.3])
+    # checkerboard.glsl:6-20: WHITE inside a cell, GREY (0.5) on a grid line of width lineWidth every `size`
+    assert np.allclose(oracle.unit("getSurfaceColor", hit, [0.125, 0.125], 1), 1.0)
+    assert np.allclose(oracle.unit("getSurfaceColor", hit, [0.251, 0.125], 1), 0.5)
+    # checkerboard2.glsl:7-16: parity of floor(u/s) + floor(v/s)
+    c00, c10 = oracle.unit("getSurfaceColor", hit, [0.2, 0.2], 2), oracle.unit("getSurfaceColor", hit, [0.7, 0.2], 2)
+    assert not np.array_equal(c00, c10) and {tuple(c00), tuple(c10)} == {(1.0, 0.0, 0.0), (0.0, 0.0, 1.0)}
+    assert np.array_equal(oracle.unit("getSurfaceColor", hit, [0.7, 0.7], 2), c00)
+    # mixf.glsl:7-13 / scale.glsl:6-11 / uvf.glsl:1-3
+    m = oracle.unit("getSurfaceColor", hit, [0.3, 0.3], 3)
+    assert np.allclose(m, [0.75, 0.0, 0.25], atol=1e-6) or np.allclose(m, [0.25, 0.0, 0.75], atol=1e-6)
+    assert np.allclose(oracle.unit("getSurfaceColor", hit, [0.3, 0.3], 4), [0.25, 0.5, 0.2])
+    assert np.allclose(oracle.unit("getSurfaceColor", hit, [1.25, -0.25], 5), [0.25, 0.75, 0.0])
+
+
+def test_light_arms_known_answers(oracle):
+    """point.glsl / spot.glsl / area.glsl on an empty scene (nothing to occlude): closed forms of SURVEY 8(a)."""
+    import sail_b200 as Sail
+    matte = Sail.Matte(0.7)
+    scene = Sail.Scene()
+    scene.add(Sail.PointLight([0, 4, 0], [0.6, 0.5, 0.4]))
+    scene.add(Sail.SpotLight([0, 5, 0], 35, 10, [30, 30, 30]))
+    scene.add(Sail.Camera([0, 1, -5], [0, 1, 0]))
+    from sail_b200.wire import serialize_scene
+    o, t, l = serialize_scene(scene)
+    oracle.set_scene(o, t, l)
+    hit, n = [0.0, 0.0, 0.0], [0.0, 1.0, 0.0]
+    # point light: E * max(0, w.n), no falloff; the sampled point lies within 0.1 of `from`
+    p = oracle.unit("light_arm", 10, 20, 0.5, hit, n, 0)
+    assert np.all(p <= np.float32([0.6, 0.5, 0.4]) * 1.0000001) and np.allclose(p, [0.6, 0.5, 0.4], rtol=2e-3)
+    assert np.array_equal(oracle.unit("light_arm", 10, 20, 0.5, hit, [0, -1, 0], 0), [0, 0, 0])   # facing away
+    # spot light straight above: falloff 1 inside the inner cone, E / d^2
+    s = oracle.unit("light_arm", 10, 20, 0.5, hit, n, 1)
+    assert np.allclose(s, 30.0 / 25.0, rtol=1e-6)
+    # outside the cone (35 deg total): tan(40 deg) * 5 away on the floor
+    far = [5 * math.tan(math.radians(40)), 0.0, 0.0]
+    assert np.array_equal(oracle.unit("light_arm", 10, 20, 0.5, far, n, 1), [0, 0, 0])
+    # in the falloff band (between 25 and 35 deg): delta^4 smooth step, strictly between 0 and the full value
+    mid = [5 * math.tan(math.radians(30)), 0.0, 0.0]
+    v = oracle.unit("light_arm", 10, 20, 0.5, mid, n, 1)
+    d2 = 25 + mid[0] ** 2
+    cosw = 5 / math.sqrt(d2)
+    delta = (cosw - math.cos(math.radians(35))) / (math.cos(math.radians(25)) - math.cos(math.radians(35)))
+    assert np.allclose(v, 30.0 * delta ** 4 * cosw / d2, rtol=5e-5)
