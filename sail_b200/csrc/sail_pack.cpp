@@ -135,10 +135,11 @@ int sail_pack_scene(const float* objects, int n, const float* texparams, int tn,
         }
         // ---- geometry ----
         float* q = s.q;
+        float lo[3] = {0.0f, 0.0f, 0.0f}, hi[3] = {0.0f, 0.0f, 0.0f};
         switch (cat) {
             case SAIL_CUBE: case SAIL_CORNELLBOX: {
-                fetch3(O, 1, kObjectsLen, row, s.lo);
-                fetch3(O, 4, kObjectsLen, row, s.hi);
+                fetch3(O, 1, kObjectsLen, row, lo);
+                fetch3(O, 4, kObjectsLen, row, hi);
                 // Per-face normal (cube.glsl:25-38 `c*vec3(..)`; cornellbox.glsl:39-51,83 `-vec3(..)`) and dpdu
                 // (cube.glsl:40-48): scene constants, evaluated here with the shader's own operations.
                 const float c = (cat == SAIL_CUBE) ? s.rev : 1.0f;
@@ -156,7 +157,7 @@ int sail_pack_scene(const float* objects, int n, const float* texparams, int tn,
                 float c[3];
                 fetch3(O, 1, kObjectsLen, row, c);
                 float r = fetch(O, 4, 0, kObjectsLen, row);
-                for (int k = 0; k < 3; k++) { s.lo[k] = c[k] - r; s.hi[k] = c[k] + r; q[SQ_SPH_C + k] = c[k]; }
+                for (int k = 0; k < 3; k++) { lo[k] = c[k] - r; hi[k] = c[k] + r; q[SQ_SPH_C + k] = c[k]; }
                 q[SQ_SPH_R] = r;
                 q[SQ_SPH_RR] = r * r;
                 q[SQ_SPH_INVR] = dm_rcp(r);
@@ -167,8 +168,8 @@ int sail_pack_scene(const float* objects, int n, const float* texparams, int tn,
                 float mn[3], mx[3];
                 fetch3(O, 1, kObjectsLen, row, mn);
                 fetch3(O, 4, kObjectsLen, row, mx);
-                memcpy(s.lo, mn, sizeof(mn));
-                memcpy(s.hi, mx, sizeof(mx));
+                memcpy(lo, mn, sizeof(mn));
+                memcpy(hi, mx, sizeof(mx));
                 H3 dpdu{mx[0] - mn[0], 0.0f, 0.0f}, dpdv{0.0f, mx[1] - mn[1], mx[2] - mn[2]};
                 H3 nrm = hnormalize(hcross(dpdu, dpdv));
                 float maxX = hlength(dpdu), maxY = hlength(dpdv);
@@ -185,8 +186,8 @@ int sail_pack_scene(const float* objects, int n, const float* texparams, int tn,
                 float p[3];
                 fetch3(O, 1, kObjectsLen, row, p);
                 float h = fetch(O, 4, 0, kObjectsLen, row), r = fetch(O, 5, 0, kObjectsLen, row);
-                s.lo[0] = p[0] - r; s.lo[1] = p[1] - 0.0f; s.lo[2] = p[2] - r;
-                s.hi[0] = p[0] + r; s.hi[1] = p[1] + h; s.hi[2] = p[2] + r;
+                lo[0] = p[0] - r; lo[1] = p[1] - 0.0f; lo[2] = p[2] - r;
+                hi[0] = p[0] + r; hi[1] = p[1] + h; hi[2] = p[2] + r;
                 for (int k = 0; k < 3; k++) q[k] = p[k];
                 q[3] = h;
                 if (cat == SAIL_CONE) {
@@ -220,8 +221,8 @@ int sail_pack_scene(const float* objects, int n, const float* texparams, int tn,
                 fetch3(O, 7, kObjectsLen, row, p2);
                 float r1 = dm_sqrt(p1[0] * p1[0] + p1[1] * p1[1]), r2 = dm_sqrt(p2[0] * p2[0] + p2[1] * p2[1]);
                 float rMax = dm_max(r1, r2), zMin = dm_min(p1[2], p2[2]), zMax = dm_max(p1[2], p2[2]);
-                s.lo[0] = p[0] - rMax; s.lo[1] = p[1] - (-zMin); s.lo[2] = p[2] - rMax;
-                s.hi[0] = p[0] + rMax; s.hi[1] = p[1] + zMax; s.hi[2] = p[2] + rMax;
+                lo[0] = p[0] - rMax; lo[1] = p[1] - (-zMin); lo[2] = p[2] - rMax;
+                hi[0] = p[0] + rMax; hi[1] = p[1] + zMax; hi[2] = p[2] + rMax;
                 for (int k = 0; k < 3; k++) { q[SQ_HYP_P + k] = p[k]; q[SQ_HYP_P1 + k] = p1[k]; q[SQ_HYP_P2 + k] = p2[k]; }
                 q[SQ_HYP_AH] = fetch(O, 10, 0, kObjectsLen, row);
                 q[SQ_HYP_CH] = fetch(O, 11, 0, kObjectsLen, row);
@@ -235,8 +236,8 @@ int sail_pack_scene(const float* objects, int n, const float* texparams, int tn,
                 float z0 = fetch(O, 4, 0, kObjectsLen, row), z1 = fetch(O, 5, 0, kObjectsLen, row);
                 float r = fetch(O, 6, 0, kObjectsLen, row);
                 float zMin = dm_min(z0, z1), zMax = dm_max(z0, z1);
-                s.lo[0] = p[0] - r; s.lo[1] = p[1] - (-zMin); s.lo[2] = p[2] - r;
-                s.hi[0] = p[0] + r; s.hi[1] = p[1] + zMax; s.hi[2] = p[2] + r;
+                lo[0] = p[0] - r; lo[1] = p[1] - (-zMin); lo[2] = p[2] - r;
+                hi[0] = p[0] + r; hi[1] = p[1] + zMax; hi[2] = p[2] + r;
                 for (int k = 0; k < 3; k++) q[SQ_PAR_P + k] = p[k];
                 q[SQ_PAR_ZMIN] = zMin; q[SQ_PAR_ZMAX] = zMax;
                 q[SQ_PAR_K] = dm_div(zMax, r * r);
@@ -245,6 +246,7 @@ int sail_pack_scene(const float* objects, int n, const float* texparams, int tn,
                 break;
             }
         }
+        for (int k = 0; k < 3; k++) { s.lohi[2 * k] = lo[k]; s.lohi[2 * k + 1] = hi[k]; }
     }
 
     // ---- kernel features actually needed by this scene ----

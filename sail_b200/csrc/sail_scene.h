@@ -15,6 +15,7 @@
 // object scan reads it with warp-uniform (broadcast) addresses.
 #ifndef SAIL_SCENE_H
 #define SAIL_SCENE_H
+#include <stddef.h>
 #include <stdint.h>
 
 #define SAIL_MAX_OBJECTS 64
@@ -34,12 +35,15 @@ enum { SAIL_UNIFORM_COLOR = 0, SAIL_CHECKERBOARD = 5, SAIL_CHECKERBOARD2 = 7, SA
 struct __attribute__((aligned(16))) SailShape {
     int category;
     float rev;        // reverseNormal ? -1 : +1   (Cornell box: +1, cornellbox.glsl:18)
-    float lo[3];      // cube/cornellbox: min; quadrics: bounding box corner; rectangle: min
-    float hi[3];      // cube/cornellbox: max; quadrics: bounding box corner
+    // The two corners, interleaved per axis {lo.x, hi.x, lo.y, hi.y, lo.z, hi.z} at an 8-byte aligned offset: the
+    // slab test loads each axis as one 64-bit register pair for the packed FP32 pipe (FADD2 / FMUL2).
+    // lo = cube/cornellbox/rectangle min or a bounding-box corner of the quadrics; hi = the max corner.
+    float lohi[6];
     float emission[3];
     int matCategory;  // texParams[matRow][0]
     float q[40];      // shape parameters, layout per category (SQ_* below)
 };
+static_assert(sizeof(SailShape) == 208 && offsetof(SailShape, lohi) == 8, "SailShape layout");
 // q[] layouts
 // cube / cornellbox: per face (x-, x+, y-, y+, z-, z+) the geometric normal intersectX() returns and its dpdu
 enum { SQ_BOX_FACE = 0, SQ_BOX_FACE_STRIDE = 6 };

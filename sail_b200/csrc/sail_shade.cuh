@@ -328,8 +328,8 @@ static __device__ __noinline__ V3 stubShapeNormal(const SailShape& s) {
     const float* q = s.q;
     const V3 hit = splat3(0.0f);
     switch (s.category) {
-        case SAIL_CUBE: return boxFaceNormal(hit, ld3(s.lo), ld3(s.hi), s.rev);       // cube.glsl:25-38
-        case SAIL_CORNELLBOX: return boxFaceNormal(hit, ld3(s.lo), ld3(s.hi), 1.0f);  // cornellbox.glsl:39-51
+        case SAIL_CUBE: return boxFaceNormal(hit, loOf(s), hiOf(s), s.rev);       // cube.glsl:25-38
+        case SAIL_CORNELLBOX: return boxFaceNormal(hit, loOf(s), hiOf(s), 1.0f);  // cornellbox.glsl:39-51
         case SAIL_CONE: if (F & SAIL_F_QUADRICS) {  // cone.glsl:38-46
             V3 hh = hit - ld3(q + SQ_CONE_P);
             float d = dm_sqrt(hh.x * hh.x + hh.y * hh.y);
@@ -377,7 +377,7 @@ SD V3 sampleGeometry(const SceneView& sc, V2 u, int i, V3& normal, float& pdf) {
             return p;
         }
         case SAIL_RECTANGLE: {  // rectangle.glsl:25-30,65-70
-            V3 p = ld3(s.lo) + ld3(q + SQ_RECT_DPDU) * u.x + ld3(q + SQ_RECT_DPDV) * u.y;
+            V3 p = loOf(s) + ld3(q + SQ_RECT_DPDU) * u.x + ld3(q + SQ_RECT_DPDV) * u.y;
             pdf = q[SQ_RECT_PDF];
             normal = s.rev * ld3(q + SQ_RECT_N);
             return p;

@@ -100,19 +100,24 @@ SD bool quadratic(float A, float B, float C, float& t0, float& t1) {
 }
 
 // ---- shape/boundbox.glsl:6-17 and the slab core of cube.glsl:65-74 / cornellbox.glsl:67-76 ----
-// `first`/`second` are box.min/box.max in the order the shader's min()/max() sees them.
-SD void slab(V3 first, V3 second, V3 o, V3 rd, float& tNear, float& tFar) {
-    V3 tMin = (first - o) * rd;
-    V3 tMax = (second - o) * rd;
-    V3 t1 = mk3(fmin2(tMin.x, tMax.x), fmin2(tMin.y, tMax.y), fmin2(tMin.z, tMax.z));
-    V3 t2 = mk3(fmax2(tMin.x, tMax.x), fmax2(tMin.y, tMax.y), fmax2(tMin.z, tMax.z));
-    tNear = fmax2(fmax2(t1.x, t1.y), t1.z);
-    tFar = fmin2(fmin2(t2.x, t2.y), t2.z);
+// tMin = (box.min - o) / d, tMax = (box.max - o) / d per axis, then the component-wise min / max.  Which corner the
+// shader calls min or max does not matter (min/max are symmetric), so each axis is evaluated as ONE packed pair
+// {lo, hi}: one FADD2 (subtract the origin) and one FMUL2 (times 1/d) instead of two FADDs and two FMULs.
+SD void slab(const SailShape& s, V3 o, V3 rd, float& tNear, float& tFar) {
+    F2 tx = mul2(sub2(ld2(s.lohi), pk2(o.x, o.x)), pk2(rd.x, rd.x));
+    F2 ty = mul2(sub2(ld2(s.lohi + 2), pk2(o.y, o.y)), pk2(rd.y, rd.y));
+    F2 tz = mul2(sub2(ld2(s.lohi + 4), pk2(o.z, o.z)), pk2(rd.z, rd.z));
+    float ax, bx, ay, by, az, bz;
+    upk2(tx, ax, bx); upk2(ty, ay, by); upk2(tz, az, bz);
+    tNear = fmax2(fmax2(fmin2(ax, bx), fmin2(ay, by)), fmin2(az, bz));
+    tFar = fmin2(fmin2(fmax2(ax, bx), fmax2(ay, by)), fmax2(az, bz));
 }
-// testBoundbox with Boundbox(lo, hi): the constructor order is (max, min), so box.min = hi.
+SD V3 loOf(const SailShape& s) { return mk3(s.lohi[0], s.lohi[2], s.lohi[4]); }
+SD V3 hiOf(const SailShape& s) { return mk3(s.lohi[1], s.lohi[3], s.lohi[5]); }
+// testBoundbox with Boundbox(lo, hi) (the constructor order (max, min) is immaterial, see above).
 SD bool boundsHit(const SailShape& s, V3 o, V3 rd) {
     float tNear, tFar;
-    slab(ld3(s.hi), ld3(s.lo), o, rd, tNear, tFar);
+    slab(s, o, rd, tNear, tFar);
     if (tNear < 0.0f && tFar < 0.0f) return false;
     return tNear < tFar;
 }
@@ -152,7 +157,7 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd) {
         // cube.glsl:65-79: the near slab hit if it is in front, else the far one
         // cornellbox.glsl:67-81: always the far slab hit
         float tNear, tFar;
-        slab(ld3(s.lo), ld3(s.hi), ray.o, rd, tNear, tFar);
+        slab(s, ray.o, rd, tNear, tFar);
         float t = -1.0f;
         if (tNear < tFar) t = (cat == SAIL_CUBE && tNear > SAIL_EPSILON) ? tNear : tFar;
         return (t > SAIL_EPSILON) ? t : SAIL_MAX_DISTANCE;
@@ -175,7 +180,7 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd) {
         case SAIL_RECTANGLE: {  // rectangle.glsl:32-55
             V3 nn = ld3(q + SQ_RECT_N), ss = ld3(q + SQ_RECT_SS), ts = ld3(q + SQ_RECT_TS);
             V3 dl = worldToLocal(ray.d, nn, ss, ts);
-            V3 ol = worldToLocal(ray.o - ld3(s.lo), nn, ss, ts);
+            V3 ol = worldToLocal(ray.o - loOf(s), nn, ss, ts);
             if (dl.z == 0.0f) return SAIL_MAX_DISTANCE;
             float t = fdiv(-ol.z, dl.z);
             if (t < SAIL_EPSILON) return SAIL_MAX_DISTANCE;
@@ -339,7 +344,7 @@ SD void hitRecord(const SceneView& sc, int i, float t, const Ray& ray, Hit& h) {
         case SAIL_CORNELLBOX: {  // cornellbox.glsl:23-51,81-88
             // One branch-free path for both boxes: the face is picked with the shader's comparison chain
             // (x-, x+, y-, y+, z-, z+), its normal and dpdu come from the per-face table built at upload.
-            V3 mn = ld3(s.lo), mx = ld3(s.hi);
+            V3 mn = loOf(s), mx = hiOf(s);
             h.p = ray.o + t * ray.d;
             int face = 5;
             face = (h.p.z < mn.z + 0.0001f) ? 4 : face;
@@ -389,7 +394,7 @@ SD void hitRecord(const SceneView& sc, int i, float t, const Ray& ray, Hit& h) {
             break;
         }
         case SAIL_RECTANGLE: {  // rectangle.glsl:36-62
-            V3 nn = ld3(q + SQ_RECT_N), ss = ld3(q + SQ_RECT_SS), ts = ld3(q + SQ_RECT_TS), mn = ld3(s.lo);
+            V3 nn = ld3(q + SQ_RECT_N), ss = ld3(q + SQ_RECT_SS), ts = ld3(q + SQ_RECT_TS), mn = loOf(s);
             V3 dl = worldToLocal(ray.d, nn, ss, ts);
             V3 ol = worldToLocal(ray.o - mn, nn, ss, ts);
             V3 hl = ol + t * dl;
