@@ -14,15 +14,49 @@
 #include "sail_shapes.cuh"
 
 // ---- util/random.glsl:5-10 ---------------------------------------------------------------------
-// The two sines of one call go through ONE out-of-line function (one call, two independent dependency chains
-// interleaved by the scheduler); the small variants inline them.
-static __device__ __noinline__ float2 sail_sin2(float a, float b) { return make_float2(dm_sin(a), dm_sin(b)); }
+// dm_sin (detmath.h) of two arguments at once: the same operations in the same order, with every FP32 step that
+// both lanes share issued as one packed instruction (FMUL2 / FFMA2).  Each half rounds exactly like the scalar code,
+// so sinPair(a, b) == (dm_sin(a), dm_sin(b)) bit for bit (tests/test_gpu_parity.py::test_device_math_matches_host
+// checks the scalar path against the host, the frame tests check this one against the oracle).
+SD V2 sinPair(float a, float b) {
+    const F2 x = pk2(a, b);
+    float ta, tb;
+    upk2(mul2(x, splat2(DM_TWO_OVER_PI)), ta, tb);
+    const float na = rintf(ta), nb = rintf(tb);
+    const F2 nn = pk2(-na, -nb);
+    F2 r = fma2(nn, splat2(DM_PIO2_HI), x);
+    r = fma2(nn, splat2(DM_PIO2_MID), r);
+    r = fma2(nn, splat2(DM_PIO2_LO), r);
+    const F2 z = mul2(r, r);
+    // dm_sin_kernel
+    F2 ps = fma2(splat2(-1.9515295891e-4f), z, splat2(8.3321608736e-3f));
+    ps = fma2(ps, z, splat2(-1.6666654611e-1f));
+    const F2 sn = fma2(mul2(ps, z), r, r);
+    // dm_cos_kernel
+    F2 pc = fma2(splat2(2.443315711809948e-5f), z, splat2(-1.388731625493765e-3f));
+    pc = fma2(pc, z, splat2(4.166664568298827e-2f));
+    pc = mul2(mul2(pc, z), z);
+    const F2 cs = add2(fma2(splat2(-0.5f), z, splat2(1.0f)), pc);
+    float sa, sb, ca, cb;
+    upk2(sn, sa, sb);
+    upk2(cs, ca, cb);
+    const int qa = (int)na, qb = (int)nb;
+    float va = (qa & 1) ? ca : sa, vb = (qb & 1) ? cb : sb;
+    va = (qa & 2) ? -va : va;
+    vb = (qb & 2) ? -vb : vb;
+    if (!(dm_abs(a) < 4194304.0f)) va = dm_sub(a, a);
+    if (!(dm_abs(b) < 4194304.0f)) vb = dm_sub(b, b);
+    return mk2(va, vb);
+}
+static __device__ __noinline__ float2 sail_sin2(float a, float b) { V2 v = sinPair(a, b); return make_float2(v.x, v.y); }
 template <int F>
 SD V2 random2(float fx, float fy, float fz, float seed) {
     float ax = fx + seed, ay = fy + seed, az = fz + seed;
     float d1 = ax * 12.9898f + ay * 78.233f + az * 151.7182f;
     float d2 = ax * 63.7264f + ay * 10.873f + az * 623.6736f;
-    float2 s2 = SAIL_SMALL(F) ? make_float2(dm_sin(d1), dm_sin(d2)) : sail_sin2(d1, d2);
+    V2 s2;
+    if (SAIL_SMALL(F)) s2 = sinPair(d1, d2);
+    else { float2 t = sail_sin2(d1, d2); s2 = mk2(t.x, t.y); }
     return mk2(ffract(s2.x * 43758.5453f + seed), ffract(s2.y * 43758.5453f + seed));
 }
 

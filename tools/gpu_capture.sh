@@ -1,7 +1,7 @@
 set -x
-python bench.py > gpurun_out/bench_r1e.json 2> gpurun_out/bench_r1e.err || exit 1
-cat gpurun_out/bench_r1e.json
-python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/plain_r1e.log 2>&1 || exit 1
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_r1e.csv python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_l.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:megakernel -s 3 -c 1 -f -o gpurun_out/prof_r1e python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_f.log 2>&1
+python bench.py > gpurun_out/bench_${TAG:-r1x}.json 2> gpurun_out/bench_${TAG:-r1x}.err || exit 1
+cat gpurun_out/bench_${TAG:-r1x}.json
+python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/plain_${TAG:-r1x}.log 2>&1 || exit 1
+ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_${TAG:-r1x}.csv python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_l.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:megakernel -s 3 -c 1 -f -o gpurun_out/prof_${TAG:-r1x} python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_f.log 2>&1
 ls -la gpurun_out
