@@ -239,6 +239,21 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd) {
     return SAIL_MAX_DISTANCE;
 }
 
+// dm_rcp (detmath.h) of the three components of a direction: the two Newton FMAs of x and y issue as one packed
+// pair; every lane computes exactly what dm_rcp computes.
+SD V3 rcp3(V3 d) {
+    float yx, yy;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(yx) : "f"(d.x));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(yy) : "f"(d.y));
+    const F2 y0 = pk2(yx, yy);
+    const F2 e = fma2(pk2(-d.x, -d.y), y0, splat2(1.0f));
+    F2 y1;
+    asm("fma.rn.ftz.f32x2 %0, %1, %2, %1;" : "=l"(y1) : "l"(y0), "l"(e));
+    float rx, ry;
+    upk2(y1, rx, ry);
+    return mk3((rx != rx) ? yx : rx, (ry != ry) ? yy : ry, dm_rcp(d.z));
+}
+
 // shader.shape.js:28-37: nearest object by strict `<` in ascending index.  Returns (ins.d, object index
 // or -1).  Out of line (one copy serves primary/bounce rays and shadow rays); everything travels in
 // registers -- the scene block is addressed by its shared-memory window offset.
@@ -248,7 +263,7 @@ struct Nearest {
 };
 template <int F>
 SD Nearest nearestObjectInline(const SceneView& sc, const Ray& ray) {
-    V3 rd = mk3(dm_rcp(ray.d.x), dm_rcp(ray.d.y), dm_rcp(ray.d.z));
+    V3 rd = rcp3(ray.d);
     Nearest r;
     r.t = SAIL_MAX_DISTANCE;
     r.id = -1;
