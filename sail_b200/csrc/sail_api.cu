@@ -313,7 +313,7 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
     // the variant follows the scene's content, never the caller's mask hints
     dim3 grid((ctx->W + SAIL_TILE_W - 1) / SAIL_TILE_W, tileRows);
     const int F = ctx->hostScene.features & SAIL_F_ALL;
-    const bool wave = ctx->cfg.kernel == SAIL_KERNEL_WAVEFRONT || (ctx->cfg.kernel == SAIL_KERNEL_AUTO && (F & SAIL_F_QUADRICS));
+    const bool wave = ctx->cfg.kernel == SAIL_KERNEL_WAVEFRONT || (ctx->cfg.kernel == SAIL_KERNEL_AUTO && (F & (SAIL_F_QUADRICS | SAIL_F_GLOSSY)));
     if (wave) CU(launchWave(F, L, grid, ctx->stream));
     else CU(launchMega(F, L, grid, ctx->stream));
     ctx->launches++;

@@ -26,7 +26,10 @@
 #ifndef SAIL_MIN_CTAS_SMALL
 #define SAIL_MIN_CTAS_SMALL 8
 #endif
-#define SAIL_MIN_CTAS(F) (((F) & (SAIL_F_GLOSSY | SAIL_F_QUADRICS)) ? 4 : SAIL_MIN_CTAS_SMALL)
+#ifndef SAIL_MIN_CTAS_BIG
+#define SAIL_MIN_CTAS_BIG 8
+#endif
+#define SAIL_MIN_CTAS(F) (((F) & (SAIL_F_GLOSSY | SAIL_F_QUADRICS)) ? SAIL_MIN_CTAS_BIG : SAIL_MIN_CTAS_SMALL)
 
 // Per-frame constants derived on the host from (matrix, eye): the four corner rays of vstrace.glsl:4-7
 // and the edge differences used by the rasteriser-style interpolation (DESIGN.md "Primary rays").
