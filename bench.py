@@ -106,8 +106,62 @@ def build_workload():
     return scene, W, H, bounces, (o, t, l)
 
 
-def cpu_baseline(nframes=2, threads=0):
-    """The CPU oracle (a port: the reference has no CPU implementation) on a bounded sample of the workload."""
+def other_workload(name, local_rank, peak_tops, steps=8, warm=3):
+    """Device-resident throughput of one of the other BASELINE.json configs (same timing rules, fewer steps):
+    context for the headline, not a bench line of its own."""
+    global _workload
+    import torch
+    from sail_b200 import capi
+    from sail_b200.renderer import Renderer
+    keep, _workload = _workload, name
+    try:
+        scene, W, H, bounces, _ = build_workload()
+        ops = ops_per_path()
+    finally:
+        _workload = keep
+    r = Renderer((W, H), device=local_rank)
+    r.ctx.configure(max_bounces=bounces)
+    r.update(scene)
+    batches = [r.tracer.frames(scene.mat, scene.eye, s * SPP_PER_STEP, SPP_PER_STEP) for s in range(warm + steps)]
+    stream = torch.cuda.ExternalStream(r.ctx.stream(), device=local_rank)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for s in range(warm):
+        r.ctx.render_n(batches[s])
+    r.ctx.synchronize()
+    with torch.cuda.stream(stream):
+        for s in range(steps):
+            flush.zero_()
+            ev[s][0].record(stream)
+            r.ctx.render_n(batches[warm + s])
+            ev[s][1].record(stream)
+    r.ctx.synchronize()
+    torch.cuda.synchronize()
+    ms = sum(a.elapsed_time(b) for a, b in ev) / steps
+    feats = capi.scene_features(*_tables(scene))
+    r.close()
+    paths_s = W * H * SPP_PER_STEP / (ms * 1e-3)
+    return {"workload": WORKLOADS[name][1], "value": paths_s / 1e6, "unit": UNIT, "ms_per_step": ms, "steps": steps,
+            "kernel_variant_F": int(feats), "roofline_frac": paths_s * ops / 1e12 / peak_tops, "ops_per_path": ops}
+
+
+def _tables(scene):
+    from sail_b200 import wire
+    return wire.serialize_scene(scene)
+
+
+def measured_traffic():
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/traffic.json), or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(_workload, {}).get("dram_bytes_per_launch")
+    except (OSError, ValueError):
+        return None
+
+
+def cpu_baseline(seconds=12.0, min_frames=8, threads=0):
+    """The CPU oracle (a port: the reference has no CPU implementation) on a bounded sample of the workload: whole
+    1080p frames of 1 spp until about ``seconds`` of CPU work are done, all host cores (OpenMP over rows)."""
     import oracle as oracle_pkg
     from sail_b200 import schedule
     scene, W, H, bounces, (o, t, l) = build_workload()
@@ -116,16 +170,20 @@ def cpu_baseline(nframes=2, threads=0):
     sch = schedule.FrameSchedule()
     acc = np.zeros((H, W, 3), np.float32)
     cores = threads or (os.cpu_count() or 1)
-    best = None
-    for k in range(nframes + 1):  # first frame = warm-up
+    total, frames, k = 0.0, 0, 0
+    while frames < min_frames or total < seconds:
         m = schedule.frame_matrix(scene.mat, sch.jitter_unit(k), W, H)
         t0 = time.perf_counter()
         orc.render_frame(W, H, m, scene.eye, k / (k + 1.0), sch.time(k), acc, max_bounces=bounces, nthreads=cores)
         dt = time.perf_counter() - t0
-        if k > 0:
-            best = dt if best is None else min(best, dt)
-    return {"value": W * H / best / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": "%d full 1080p frames (1 spp each, %d paths), best frame, OpenMP over rows" % (nframes, W * H)}
+        if k > 0:  # first frame = warm-up
+            total += dt
+            frames += 1
+        k += 1
+        if frames >= 400:
+            break
+    return {"value": frames * W * H / total / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "%d full 1080p frames of 1 spp (%d paths) in %.1f s, OpenMP over rows" % (frames, frames * W * H, total)}
 
 
 def run_reference(args, rank, world):
@@ -276,7 +334,7 @@ def run_ours(args, rank, world, local_rank):
                        "l2": "flushed between steps (256 MiB memset outside the per-step events)"},
             "spp_per_s": value * 1e6 / (W * H),
             "roofline": {"bound": "fp32_issue", "achieved": achieved, "peak": peak, "unit": "Tops/s (FP32 lane-ops)",
-                         "frac": achieved / peak, "traffic": None, "ops_per_path": ops,
+                         "frac": achieved / peak, "traffic": measured_traffic(), "ops_per_path": ops,
                          "peak_def": "%d SMs x 128 lanes x %.0f MHz (%s sm_max_mhz)" % (n_sm, pk["sm_max_mhz"], pk["source"]),
                          "hbm": {"achieved": hbm_gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": hbm_gbs / pk["hbm_gbs"],
                                  "bytes_per_launch": W * H * 24}},
@@ -289,6 +347,8 @@ def run_ours(args, rank, world, local_rank):
             line["reduce_ms"] = reduce_ms
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline()
+        if world == 1 and not args.no_cpu and _workload == "cornell":
+            line["other_workloads"] = [other_workload(w, local_rank, peak) for w in ("config2", "config3", "config5")]
         print(json.dumps(line))
     r.close()
     if dist:
