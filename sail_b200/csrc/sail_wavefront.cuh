@@ -23,7 +23,7 @@ template <int F>
 __global__ void __launch_bounds__(SAIL_CTA_THREADS, SAIL_MIN_CTAS(F)) sail_trace_wavefront(const __grid_constant__ SailLaunch L) {
     __shared__ float slot[SAIL_WF_STATE][SAIL_CTA_THREADS];  // SoA: lane-consecutive words, conflict free
     __shared__ float firstHit[6][SAIL_CTA_THREADS];          // n, p of the primary hit, indexed by home lane
-    __shared__ int hist[SAIL_MAX_OBJECTS + 2];
+    __shared__ int hist[2][SAIL_MAX_OBJECTS + 2];  // double buffered: the next bounce's counters are cleared while this one scatters
     const SceneView sc = stageScene(L.scene);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -39,6 +39,9 @@ __global__ void __launch_bounds__(SAIL_CTA_THREADS, SAIL_MIN_CTAS(F)) sail_trace
     const float hx = (float)x + 0.5f, hy = (float)y + 0.5f;  // gl_FragCoord of the home pixel
     const float a = hx * L.rcpW, b = hy * L.rcpH;
     const int n = sc.n;
+    if (tid <= n) { hist[0][tid] = 0; hist[1][tid] = 0; }
+    int hsel = 0;  // which histogram the next regroup uses (uniform across the CTA); stageScene's barrier is behind us,
+    __syncthreads();  // this one publishes the cleared counters
 
     V3 c = inside ? mk3(L.accum[3 * pix], L.accum[3 * pix + 1], L.accum[3 * pix + 2]) : splat3(0.0f);
     int firstId = -1;
@@ -71,12 +74,13 @@ __global__ void __launch_bounds__(SAIL_CTA_THREADS, SAIL_MIN_CTAS(F)) sail_trace
             if (deepth > 1) {
                 // ---- stage 2: counting sort by hit object ----
                 const int key = alive ? nr.id : n;
-                if (tid <= n) hist[tid] = 0;
-                __syncthreads();
-                const int rank = atomicAdd(&hist[key], 1);
+                int* hcur = hist[hsel];
+                const int rank = atomicAdd(&hcur[key], 1);
                 __syncthreads();
                 int pos = rank;
-                for (int j = 0; j < key; j++) pos += hist[j];
+                for (int j = 0; j < key; j++) pos += hcur[j];
+                if (tid <= n) hist[hsel ^ 1][tid] = 0;  // nobody reads or counts in the other buffer before the next barrier
+                hsel ^= 1;
                 // ---- stage 3: exchange ----
                 slot[0][pos] = ray.o.x; slot[1][pos] = ray.o.y; slot[2][pos] = ray.o.z;
                 slot[3][pos] = ray.d.x; slot[4][pos] = ray.d.y; slot[5][pos] = ray.d.z;
