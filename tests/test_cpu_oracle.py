@@ -282,3 +282,19 @@ def test_light_arms_known_answers(oracle):
     cosw = 5 / math.sqrt(d2)
     delta = (cosw - math.cos(math.radians(35))) / (math.cos(math.radians(25)) - math.cos(math.radians(35)))
     assert np.allclose(v, 30.0 * delta ** 4 * cosw / d2, rtol=5e-5)
+
+
+def test_oracle_matches_golden_v2_bounce_dump(oracle):
+    """tests/golden/oracle_v2.npz: per-bounce rays / hits of frame 0 of config 2 (the converged images of the same file
+    take ~10 s of CPU and are regenerated by tests/golden/make_golden_v2.py; the GPU suite checks them)."""
+    gold = np.load(os.path.join(ROOT, "tests", "golden", "oracle_v2.npz"))
+    W, H = 48, 27
+    scene, o, t, l, bounces = scene_tables(2, W, H)
+    oracle.set_scene(o, t, l)
+    m, eye, w, tm = frame_uniforms(scene, 0, W, H)
+    d = oracle.trace_dump(W, H, m, eye, tm, max_bounces=bounces)
+    assert np.array_equal(d["hit_id"], gold["c2_bounce_hit_id"])
+    for k in ("t", "rays", "radiance"):
+        assert bits_equal(d[k], gold["c2_bounce_" + k]), k
+    assert gold["c1_converged"].shape == (64, 64, 3) and np.isfinite(gold["c1_converged"]).all()
+    assert 0.05 < float(gold["c1_converged"].mean()) < 1.0
