@@ -139,10 +139,11 @@ def other_workload(name, local_rank, peak_tops, steps=8, warm=3):
     torch.cuda.synchronize()
     ms = sum(a.elapsed_time(b) for a, b in ev) / steps
     feats = capi.scene_features(*_tables(scene))
+    used = r.ctx.kernel_info()
     r.close()
     paths_s = W * H * SPP_PER_STEP / (ms * 1e-3)
     return {"workload": WORKLOADS[name][1], "value": paths_s / 1e6, "unit": UNIT, "ms_per_step": ms, "steps": steps,
-            "kernel_variant_F": int(feats), "roofline_frac": paths_s * ops / 1e12 / peak_tops, "ops_per_path": ops}
+            "kernel_variant_F": int(feats), "kernel_used": used, "roofline_frac": paths_s * ops / 1e12 / peak_tops, "ops_per_path": ops}
 
 
 def _tables(scene):
@@ -248,7 +249,8 @@ def run_ours(args, rank, world, local_rank):
     r = Renderer((W, H), device=local_rank)
     ctx = r.ctx
     ctx.configure(max_bounces=bounces, accum_mode=capi.ACCUM_SUM if world > 1 else capi.ACCUM_MEAN,
-                  kernel={"wavefront": capi.KERNEL_WAVEFRONT, "mega": capi.KERNEL_MEGA, "auto": capi.KERNEL_AUTO}[args.kernel])
+                  kernel={"wavefront": capi.KERNEL_WAVEFRONT, "mega": capi.KERNEL_MEGA, "auto": capi.KERNEL_AUTO}[args.kernel],
+                  specialise=capi.SPECIALISE_OFF if args.no_jit else capi.SPECIALISE_AUTO)
     r.update(scene)
     total_steps = warm + steps
     # rank g owns frame indices k = g (mod world)
@@ -277,6 +279,7 @@ def run_ours(args, rank, world, local_rank):
     ctx.synchronize()
     torch.cuda.synchronize()
     launches = ctx.launch_count() - launches0
+    kernel_used = ctx.kernel_info()
     clocks = sampler.stop()
     if dist:
         dist.barrier()
@@ -330,7 +333,7 @@ def run_ours(args, rank, world, local_rank):
             "ms_per_step": dev_ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": WORKLOADS[_workload][1], "spp_per_step": SPP_PER_STEP, "paths_per_step_per_gpu": paths_per_step,
-                       "kernel": args.kernel, "arithmetic": "strict (bit-exact vs oracle)", "sharding": "sample index mod N",
+                       "kernel": args.kernel, "kernel_used": kernel_used, "arithmetic": "strict (bit-exact vs oracle)", "sharding": "sample index mod N",
                        "l2": "flushed between steps (256 MiB memset outside the per-step events)"},
             "spp_per_s": value * 1e6 / (W * H),
             "roofline": {"bound": "fp32_issue", "achieved": achieved, "peak": peak, "unit": "Tops/s (FP32 lane-ops)",
@@ -363,6 +366,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--kernel", default="auto", choices=["auto", "mega", "wavefront"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-jit", action="store_true", help="ahead-of-time kernel variants only (no per-scene NVRTC build)")
     ap.add_argument("--workload", default="cornell", choices=sorted(WORKLOADS), help="cornell = the headline; others are extra")
     args = ap.parse_args()
     global _workload

@@ -70,6 +70,14 @@ enum {
     SAIL_KERNEL_AUTO = 2        /* default: wavefront for scenes with quadric shapes or metal/glass, megakernel otherwise */
 };
 
+enum {
+    SAIL_SPECIALISE_AUTO = 0,    /* default: compile the kernel for the scene's structure at first use (NVRTC; object count
+                                    and per-slot shape categories become constants -- the per-scene shader generation of
+                                    src/shader/generator.js:107-123); use the ahead-of-time variant when that is not possible */
+    SAIL_SPECIALISE_OFF = 1,     /* ahead-of-time variants only */
+    SAIL_SPECIALISE_REQUIRE = 2  /* fail sail_render* with SAIL_ERR_STATE if the scene-specialised kernel cannot be built */
+};
+
 typedef struct sail_ctx sail_ctx;
 
 /* new Sail.Renderer(canvas): src/core/renderer.js:9-39 + WebglHelper.initWebgl (src/core/webgl.js:215-227)
@@ -95,7 +103,8 @@ typedef struct sail_config {
     float filter_gamma_c;     /* FILTER_GAMMA_C (filter/gamma.glsl:1-8) */
     float filter_radius[2];   /* FILTER_WINDOW_RADIUS / FILTER_WAVELET_R */
     float filter_weights[16]; /* windowWeightTable built by filter/{box,gaussian,mitchell,sinc,triangle}.js */
-    int32_t reserved[4];
+    int32_t specialise;       /* SAIL_SPECIALISE_* (was reserved: 0 keeps the default) */
+    int32_t reserved[3];
 } sail_config;
 
 /* One frame's uniforms: Tracer.render(), src/core/tracer.js:92-101 / src/core/shader.js:41-49. */
@@ -188,6 +197,10 @@ uint64_t sail_launch_count(const sail_ctx* ctx);
 /* Device time of the most recent sail_render() / sail_render_n() call, from CUDA events recorded on the
  * context's stream around its kernels, in milliseconds (synchronises). */
 int sail_last_render_ms(sail_ctx* ctx, float* ms);
+/* One line describing the trace kernel the most recent sail_render* used, e.g.
+ * "jit mega<F=0> n=3 cats=1,9,2 (nvrtc 12.9, 0.8 s)" or "aot wavefront<F=10> (jit: NVRTC not found ...)".
+ * Returns the length written (excluding the terminator), or a negative error code. */
+int sail_kernel_info(sail_ctx* ctx, char* buf, int32_t len);
 /* Page-locked host memory for the caller's image / table buffers, so that sail_present / sail_read_* copy
  * straight into it at full PCIe rate (the destination ArrayBuffer of the reference's gl.readPixels,
  * src/core/webgl.js:88-92 usage in renderer.js; an N-API host wraps it as an external ArrayBuffer).  Returns NULL

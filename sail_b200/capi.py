@@ -17,6 +17,7 @@ MAX_FRAMES_PER_CALL = 32
 AOV_COLOR, AOV_NORMAL, AOV_POSITION, AOV_HIT_ID, AOV_DEPTH = range(5)
 ACCUM_MEAN, ACCUM_SUM = 0, 1
 KERNEL_MEGA, KERNEL_WAVEFRONT, KERNEL_AUTO = 0, 1, 2
+SPECIALISE_AUTO, SPECIALISE_OFF, SPECIALISE_REQUIRE = 0, 1, 2
 ERR_CUDA, ERR_INVALID, ERR_STATE, ERR_NOMEM = -1, -2, -3, -4
 
 
@@ -36,7 +37,7 @@ class Config(ctypes.Structure):
                 ("light_mask", ctypes.c_uint32), ("trace_id", ctypes.c_int32), ("max_bounces", ctypes.c_int32),
                 ("accum_mode", ctypes.c_int32), ("kernel", ctypes.c_int32), ("filter_id", ctypes.c_int32),
                 ("filter_gamma_c", ctypes.c_float), ("filter_radius", ctypes.c_float * 2),
-                ("filter_weights", ctypes.c_float * 16), ("reserved", ctypes.c_int32 * 4)]
+                ("filter_weights", ctypes.c_float * 16), ("specialise", ctypes.c_int32), ("reserved", ctypes.c_int32 * 3)]
 
 
 class Frame(ctypes.Structure):
@@ -76,6 +77,7 @@ _SIGNATURES = {
     "sail_selftest_math": (ctypes.c_int, [_P, ctypes.POINTER(ctypes.c_uint64)]),
     "sail_launch_count": (ctypes.c_uint64, [_P]),
     "sail_last_render_ms": (ctypes.c_int, [_P, ctypes.POINTER(ctypes.c_float)]),
+    "sail_kernel_info": (ctypes.c_int, [_P, ctypes.c_char_p, ctypes.c_int32]),
     "sail_alloc_host": (ctypes.c_void_p, [ctypes.c_uint64]),
     "sail_free_host": (None, [ctypes.c_void_p]),
 }
@@ -224,6 +226,12 @@ class Context:
         ms = ctypes.c_float()
         self._check(self.lib.sail_last_render_ms(self._h, ctypes.byref(ms)))
         return ms.value
+
+    def kernel_info(self):
+        """Which trace kernel the last render used (scene-specialised at run time, or an ahead-of-time variant and why)."""
+        buf = ctypes.create_string_buffer(400)
+        self._check(min(0, self.lib.sail_kernel_info(self._h, buf, 400)))
+        return buf.value.decode()
 
     def launch_count(self):
         return int(self.lib.sail_launch_count(self._h))

@@ -16,6 +16,7 @@
 
 #include "../../include/sail_b200.h"
 #include "sail_diag.cuh"
+#include "sail_jit.h"
 #include "sail_mega.cuh"
 #include "sail_present.cuh"
 
@@ -37,8 +38,13 @@ struct sail_ctx {
     float* presentF32 = nullptr;
     unsigned char* presentU8 = nullptr;
     uint64_t launches = 0;
+    // scene-specialised kernels (sail_jit.cpp): resolved lazily per kernel kind, dropped when the scene changes
+    void* jitFn[2] = {nullptr, nullptr};
+    bool jitTried[2] = {false, false};
+    char jitNote[2][320];
+    char kernelInfo[400];
     char err[512];
-    sail_ctx() { err[0] = 0; }
+    sail_ctx() { err[0] = 0; kernelInfo[0] = 0; jitNote[0][0] = jitNote[1][0] = 0; }
 };
 
 extern "C" {
@@ -123,6 +129,8 @@ int uploadBlock(sail_ctx* ctx) {
     CU(cudaMemcpyAsync(ctx->dScene, &ctx->hostScene, sizeof(SailSceneBlock), cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));  // hostScene may be rewritten by the next upload
     ctx->sceneLoaded = true;
+    ctx->jitTried[0] = ctx->jitTried[1] = false;  // the structure may have changed: look the specialised kernels up again
+    ctx->jitFn[0] = ctx->jitFn[1] = nullptr;
     return SAIL_OK;
 }
 
@@ -221,6 +229,7 @@ int sail_configure(sail_ctx* ctx, const sail_config* cfg) {
     if (cfg->filter_id < 0 || cfg->filter_id > SAIL_FILTER_TONEMAPPING) return setErr(ctx, SAIL_ERR_INVALID, "unknown filter id %d", cfg->filter_id);
     if (cfg->accum_mode != SAIL_ACCUM_MEAN && cfg->accum_mode != SAIL_ACCUM_SUM) return setErr(ctx, SAIL_ERR_INVALID, "unknown accum_mode %d", cfg->accum_mode);
     if (cfg->kernel < SAIL_KERNEL_MEGA || cfg->kernel > SAIL_KERNEL_AUTO) return setErr(ctx, SAIL_ERR_INVALID, "unknown kernel %d", cfg->kernel);
+    if (cfg->specialise < SAIL_SPECIALISE_AUTO || cfg->specialise > SAIL_SPECIALISE_REQUIRE) return setErr(ctx, SAIL_ERR_INVALID, "unknown specialise mode %d", cfg->specialise);
     ctx->cfg = *cfg;
     return SAIL_OK;
 }
@@ -314,7 +323,34 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
     dim3 grid((ctx->W + SAIL_TILE_W - 1) / SAIL_TILE_W, tileRows);
     const int F = ctx->hostScene.features & SAIL_F_ALL;
     const bool wave = ctx->cfg.kernel == SAIL_KERNEL_WAVEFRONT || (ctx->cfg.kernel == SAIL_KERNEL_AUTO && (F & (SAIL_F_QUADRICS | SAIL_F_GLOSSY)));
-    if (wave) CU(launchWave(F, L, grid, ctx->stream));
+    const int kind = wave ? 1 : 0;
+    void* jit = nullptr;
+    if (ctx->cfg.specialise != SAIL_SPECIALISE_OFF) {
+        if (!ctx->jitTried[kind]) {
+            ctx->jitTried[kind] = true;
+            SailJitKernel k;
+            char why[300];
+            why[0] = 0;
+            if (sail_jit_get(ctx->device, kind, F, SAIL_MIN_CTAS(F), &ctx->hostScene, &k, why, sizeof(why)) == 0) {
+                ctx->jitFn[kind] = k.fn;
+                snprintf(ctx->jitNote[kind], sizeof(ctx->jitNote[kind]), "%s", k.info);
+            } else {
+                ctx->jitFn[kind] = nullptr;
+                snprintf(ctx->jitNote[kind], sizeof(ctx->jitNote[kind]), "aot %s<F=%d> (jit: %s)", wave ? "wavefront" : "mega", F, why);
+            }
+        }
+        jit = ctx->jitFn[kind];
+        if (!jit && ctx->cfg.specialise == SAIL_SPECIALISE_REQUIRE)
+            return setErr(ctx, SAIL_ERR_STATE, "scene-specialised kernel unavailable: %s", ctx->jitNote[kind]);
+        snprintf(ctx->kernelInfo, sizeof(ctx->kernelInfo), "%s", ctx->jitNote[kind]);
+    } else {
+        snprintf(ctx->kernelInfo, sizeof(ctx->kernelInfo), "aot %s<F=%d> (specialise = off)", wave ? "wavefront" : "mega", F);
+    }
+    if (jit) {
+        char why[200];
+        if (sail_jit_launch(jit, &L, grid.x, grid.y, SAIL_CTA_THREADS, L.sceneSmem, ctx->stream, why, sizeof(why)) != 0)
+            return setErr(ctx, SAIL_ERR_CUDA, "%s", why);
+    } else if (wave) CU(launchWave(F, L, grid, ctx->stream));
     else CU(launchMega(F, L, grid, ctx->stream));
     ctx->launches++;
     CU(cudaEventRecord(ctx->evStop, ctx->stream));
@@ -513,6 +549,11 @@ int sail_last_render_ms(sail_ctx* ctx, float* ms) {
     CU(cudaEventSynchronize(ctx->evStop));
     CU(cudaEventElapsedTime(ms, ctx->evStart, ctx->evStop));
     return SAIL_OK;
+}
+
+int sail_kernel_info(sail_ctx* ctx, char* buf, int32_t len) {
+    if (!ctx || !buf || len < 1) return SAIL_ERR_INVALID;
+    return snprintf(buf, (size_t)len, "%s", ctx->kernelInfo[0] ? ctx->kernelInfo : "no trace kernel launched yet");
 }
 
 void* sail_alloc_host(uint64_t bytes) {

@@ -1,0 +1,188 @@
+// sail_jit.cpp -- per-scene kernel specialisation at run time.
+//
+// The reference assembles its fragment shader per scene: only the plugins the scene uses, with the scene's object
+// count baked in (/root/reference/src/shader/generator.js:107-123, src/scene/scene.js:70-112, src/core/tracer.js:43).
+// The 16 ahead-of-time variants (sail_mega_variants.cu) reproduce the "only what is used" half.  This file adds the
+// other half: NVRTC compiles the same kernel body with the object count and the shape category of every object slot
+// as compile-time constants, so the nearest-hit scan becomes straight-line code (sail_shapes.cuh, SAIL_JIT_NRUNS).
+// Scene *values* (positions, sizes, materials) stay in the shared-memory scene block, so dragging an object
+// (Renderer.updateObjects) never recompiles; only a change of structure does, and kernels are cached per process.
+//
+// NVRTC and the CUDA driver library are opened with dlopen: the library links against neither, and when one of them is
+// missing sail_jit_get() reports it and the caller runs the ahead-of-time variant (still a CUDA kernel -- there is no
+// CPU path anywhere).
+#include "sail_jit.h"
+
+#include <dlfcn.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <chrono>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "sail_jit_sources.inc"
+
+namespace {
+
+typedef int (*nvrtcCreateProgram_t)(void**, const char*, const char*, int, const char* const*, const char* const*);
+typedef int (*nvrtcCompileProgram_t)(void*, int, const char* const*);
+typedef int (*nvrtcGetSize_t)(void*, size_t*);
+typedef int (*nvrtcGetData_t)(void*, char*);
+typedef int (*nvrtcDestroyProgram_t)(void**);
+typedef int (*nvrtcVersion_t)(int*, int*);
+typedef int (*cuModuleLoadData_t)(void**, const void*);
+typedef int (*cuModuleGetFunction_t)(void**, void*, const char*);
+typedef int (*cuLaunchKernel_t)(void*, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, void*, void**, void**);
+typedef int (*cuGetErrorString_t)(int, const char**);
+
+struct Api {
+    bool tried = false, ok = false;
+    std::string why;
+    int nvrtcMajor = 0, nvrtcMinor = 0;
+    nvrtcCreateProgram_t createProgram = nullptr;
+    nvrtcCompileProgram_t compileProgram = nullptr;
+    nvrtcGetSize_t logSize = nullptr, cubinSize = nullptr;
+    nvrtcGetData_t log = nullptr, cubin = nullptr;
+    nvrtcDestroyProgram_t destroyProgram = nullptr;
+    cuModuleLoadData_t moduleLoadData = nullptr;
+    cuModuleGetFunction_t moduleGetFunction = nullptr;
+    cuLaunchKernel_t launchKernel = nullptr;
+    cuGetErrorString_t errorString = nullptr;
+};
+Api g_api;
+std::mutex g_mutex;
+std::map<std::string, void*> g_cache;  // key (device, kind, F, minCtas, cats) -> CUfunction; modules live for the process
+
+void* openFirst(const std::vector<std::string>& names, std::string* tried) {
+    for (const std::string& n : names) {
+        if (n.empty()) continue;
+        if (void* h = dlopen(n.c_str(), RTLD_NOW | RTLD_LOCAL)) return h;
+        *tried += n + " ";
+    }
+    return nullptr;
+}
+
+bool loadApi() {
+    if (g_api.tried) return g_api.ok;
+    g_api.tried = true;
+    const char* off = getenv("SAIL_B200_JIT");
+    if (off && off[0] == '0') { g_api.why = "disabled by SAIL_B200_JIT=0"; return false; }
+    std::string tried;
+    const char* envPath = getenv("SAIL_B200_NVRTC");
+    void* nv = openFirst({envPath ? envPath : "", "/usr/local/cuda/lib64/libnvrtc.so.12", "libnvrtc.so.12", "libnvrtc.so"}, &tried);
+    if (!nv) { g_api.why = "NVRTC not found (tried " + tried + ")"; return false; }
+    void* cu = openFirst({"libcuda.so.1", "libcuda.so"}, &tried);
+    if (!cu) { g_api.why = "CUDA driver library not found"; return false; }
+#define SYM(lib, field, name, type) g_api.field = (type)dlsym(lib, name); if (!g_api.field) { g_api.why = std::string("missing symbol ") + name; return false; }
+    SYM(nv, createProgram, "nvrtcCreateProgram", nvrtcCreateProgram_t)
+    SYM(nv, compileProgram, "nvrtcCompileProgram", nvrtcCompileProgram_t)
+    SYM(nv, logSize, "nvrtcGetProgramLogSize", nvrtcGetSize_t)
+    SYM(nv, log, "nvrtcGetProgramLog", nvrtcGetData_t)
+    SYM(nv, cubinSize, "nvrtcGetCUBINSize", nvrtcGetSize_t)
+    SYM(nv, cubin, "nvrtcGetCUBIN", nvrtcGetData_t)
+    SYM(nv, destroyProgram, "nvrtcDestroyProgram", nvrtcDestroyProgram_t)
+    SYM(cu, moduleLoadData, "cuModuleLoadData", cuModuleLoadData_t)
+    SYM(cu, moduleGetFunction, "cuModuleGetFunction", cuModuleGetFunction_t)
+    SYM(cu, launchKernel, "cuLaunchKernel", cuLaunchKernel_t)
+    SYM(cu, errorString, "cuGetErrorString", cuGetErrorString_t)
+#undef SYM
+    if (nvrtcVersion_t ver = (nvrtcVersion_t)dlsym(nv, "nvrtcVersion")) ver(&g_api.nvrtcMajor, &g_api.nvrtcMinor);
+    g_api.ok = true;
+    return true;
+}
+
+void setErr(char* err, int errlen, const std::string& s) {
+    if (err && errlen > 0) snprintf(err, (size_t)errlen, "%s", s.c_str());
+}
+
+}  // namespace
+
+int sail_jit_get(int device, int kind, int F, int minCtas, const SailSceneBlock* scene, SailJitKernel* out, char* err, int errlen) {
+    std::lock_guard<std::mutex> lock(g_mutex);
+    if (!loadApi()) { setErr(err, errlen, g_api.why); return 1; }
+    const int n = scene->n;
+    if (n < 1) { setErr(err, errlen, "empty scene"); return 2; }
+    // runs of equal shape category in slot order
+    std::string cats, runCat, runStart, runLen;
+    int nruns = 0;
+    for (int i = 0; i < n;) {
+        int j = i;
+        while (j < n && scene->shape[j].category == scene->shape[i].category) j++;
+        const char* sep = nruns ? "," : "";
+        runCat += sep + std::to_string(scene->shape[i].category);
+        runStart += sep + std::to_string(i);
+        runLen += sep + std::to_string(j - i);
+        cats += sep + std::to_string(scene->shape[i].category) + (j - i > 1 ? "x" + std::to_string(j - i) : "");
+        nruns++;
+        i = j;
+    }
+    if (nruns > SAIL_JIT_MAX_RUNS) { setErr(err, errlen, "more than 16 runs of distinct shapes"); return 2; }
+    char head[96];
+    snprintf(head, sizeof(head), "jit %s<F=%d> n=%d shapes=", kind ? "wavefront" : "mega", F, n);
+    const std::string key = "dev" + std::to_string(device) + " m" + std::to_string(minCtas) + " " + head + cats;
+    auto it = g_cache.find(key);
+    if (it != g_cache.end()) {
+        out->fn = it->second;
+        snprintf(out->info, sizeof(out->info), "%s%s (cached)", head, cats.c_str());
+        return 0;
+    }
+    char src[2048];
+    snprintf(src, sizeof(src),
+             "#define SAIL_JIT_NRUNS %d\n#define SAIL_JIT_RUN_CATS %s\n#define SAIL_JIT_RUN_STARTS %s\n#define SAIL_JIT_RUN_LENS %s\n"
+             "#include \"sail_mega.cuh\"\n#include \"sail_wavefront.cuh\"\n"
+             "extern \"C\" __global__ void __launch_bounds__(SAIL_CTA_THREADS, %d) sail_jit_kernel(const __grid_constant__ SailLaunch L) "
+             "{ %s<%d>(L); }\n",
+             nruns, runCat.c_str(), runStart.c_str(), runLen.c_str(), minCtas, kind ? "sailWaveBody" : "sailMegaBody", F);
+    void* prog = nullptr;
+    if (g_api.createProgram(&prog, src, "sail_jit.cu", kSailJitCount, kSailJitTexts, kSailJitNames) != 0) {
+        setErr(err, errlen, "nvrtcCreateProgram failed");
+        return 3;
+    }
+    const char* opts[] = {"--gpu-architecture=sm_100a", "--fmad=false", "-std=c++17", "-lineinfo"};
+    const auto t0 = std::chrono::steady_clock::now();
+    const int rc = g_api.compileProgram(prog, 4, opts);
+    const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (rc != 0) {
+        size_t ls = 0;
+        g_api.logSize(prog, &ls);
+        std::string log(ls ? ls : 1, '\0');
+        if (ls) g_api.log(prog, &log[0]);
+        g_api.destroyProgram(&prog);
+        setErr(err, errlen, "nvrtcCompileProgram failed: " + log.substr(0, 400));
+        return 4;
+    }
+    size_t cs = 0;
+    g_api.cubinSize(prog, &cs);
+    std::vector<char> cubin(cs);
+    g_api.cubin(prog, cubin.data());
+    g_api.destroyProgram(&prog);
+    void *mod = nullptr, *fn = nullptr;
+    int cr = g_api.moduleLoadData(&mod, cubin.data());
+    if (cr == 0) cr = g_api.moduleGetFunction(&fn, mod, "sail_jit_kernel");
+    if (cr != 0) {
+        const char* es = nullptr;
+        g_api.errorString(cr, &es);
+        setErr(err, errlen, std::string("loading the compiled kernel failed: ") + (es ? es : "?"));
+        return 5;
+    }
+    g_cache[key] = fn;
+    out->fn = fn;
+    snprintf(out->info, sizeof(out->info), "%s%s (nvrtc %d.%d, %.2f s)", head, cats.c_str(), g_api.nvrtcMajor, g_api.nvrtcMinor, secs);
+    return 0;
+}
+
+int sail_jit_launch(void* fn, const void* launch, unsigned gridX, unsigned gridY, unsigned block, unsigned smemBytes, void* stream,
+                    char* err, int errlen) {
+    void* params[1] = {const_cast<void*>(launch)};
+    const int cr = g_api.launchKernel(fn, gridX, gridY, 1, block, 1, 1, smemBytes, stream, params, nullptr);
+    if (cr != 0) {
+        const char* es = nullptr;
+        g_api.errorString(cr, &es);
+        setErr(err, errlen, std::string("cuLaunchKernel: ") + (es ? es : "?"));
+    }
+    return cr;
+}

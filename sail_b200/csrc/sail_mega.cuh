@@ -67,8 +67,7 @@ SD SceneView stageScene(const SailSceneBlock* __restrict__ src) {
     const uint4* s4 = reinterpret_cast<const uint4*>(src);
     uint4* d4 = sail_dyn_smem;
     const int tid = threadIdx.x, nt = blockDim.x;
-    const int shapeOff = (int)(offsetof(SailSceneBlock, shape) / 16), surfOff = (int)(offsetof(SailSceneBlock, surf) / 16);
-    const int lightOff = (int)(offsetof(SailSceneBlock, light) / 16);
+    const int shapeOff = SAIL_SCENE_SHAPE_OFF / 16, surfOff = SAIL_SCENE_SURF_OFF / 16, lightOff = SAIL_SCENE_LIGHT_OFF / 16;
     const int nShape = n * (int)(sizeof(SailShape) / 16), nSurf = n * (int)(sizeof(SailSurface) / 16);
     const int nLight = (ln + 1) * (int)(sizeof(SailLight) / 16);
     if (tid == 0) d4[0] = s4[0];
@@ -78,10 +77,12 @@ SD SceneView stageScene(const SailSceneBlock* __restrict__ src) {
     __syncthreads();
     return sceneViewAt(reinterpret_cast<const unsigned char*>(sail_dyn_smem));
 }
+#ifndef __CUDACC_RTC__
 // Dynamic shared memory a launch needs for a scene with n objects and ln lights.
 static inline size_t sailSceneSmemBytes(int n, int ln) {
     return 16 + (size_t)n * (sizeof(SailShape) + sizeof(SailSurface)) + (size_t)(ln + 1) * sizeof(SailLight);
 }
+#endif
 
 // Interpolated primary ray direction at the centre of pixel (x, y): not renormalised.
 SD V3 primaryDir(const SailFrameDev& f, float a, float b) {
@@ -94,8 +95,10 @@ SD V3 primaryDir(const SailFrameDev& f, float a, float b) {
 }
 SD float nanToZero(float v) { return (v == v) ? v : 0.0f; }
 
+// The kernel body is a device function so that the ahead-of-time variants below and the scene-specialised kernels
+// compiled at run time (sail_jit.cpp) share it; L is the kernel's __grid_constant__ parameter (constant bank).
 template <int F>
-__global__ void __launch_bounds__(SAIL_CTA_THREADS, SAIL_MIN_CTAS(F)) sail_trace_megakernel(const __grid_constant__ SailLaunch L) {
+SD void sailMegaBody(const SailLaunch& L) {
     const SceneView sc = stageScene(L.scene);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -131,6 +134,11 @@ __global__ void __launch_bounds__(SAIL_CTA_THREADS, SAIL_MIN_CTAS(F)) sail_trace
     L.accum[3 * pix] = c.x;
     L.accum[3 * pix + 1] = c.y;
     L.accum[3 * pix + 2] = c.z;
+}
+
+template <int F>
+__global__ void __launch_bounds__(SAIL_CTA_THREADS, SAIL_MIN_CTAS(F)) sail_trace_megakernel(const __grid_constant__ SailLaunch L) {
+    sailMegaBody<F>(L);
 }
 
 #endif

@@ -15,8 +15,10 @@
 // object scan reads it with warp-uniform (broadcast) addresses.
 #ifndef SAIL_SCENE_H
 #define SAIL_SCENE_H
+#ifndef __CUDACC_RTC__  // (run-time compilation, sail_jit.cpp: no host headers)
 #include <stddef.h>
 #include <stdint.h>
+#endif
 
 #define SAIL_MAX_OBJECTS 64
 #define SAIL_MAX_LIGHTS 32
@@ -43,7 +45,9 @@ struct __attribute__((aligned(16))) SailShape {
     int matCategory;  // texParams[matRow][0]
     float q[40];      // shape parameters, layout per category (SQ_* below)
 };
+#ifndef __CUDACC_RTC__
 static_assert(sizeof(SailShape) == 208 && offsetof(SailShape, lohi) == 8, "SailShape layout");
+#endif
 // q[] layouts
 // cube / cornellbox: per face (x-, x+, y-, y+, z-, z+) the geometric normal intersectX() returns and its dpdu
 enum { SQ_BOX_FACE = 0, SQ_BOX_FACE_STRIDE = 6 };
@@ -92,8 +96,17 @@ struct __attribute__((aligned(16))) SailSceneBlock {
     SailLight light[SAIL_MAX_LIGHTS + 1];
 };
 
+// Byte offsets of the three arrays inside the block (the staging copy works in 16-byte units).
+#define SAIL_SCENE_SHAPE_OFF 16
+#define SAIL_SCENE_SURF_OFF (SAIL_SCENE_SHAPE_OFF + SAIL_MAX_OBJECTS * (int)sizeof(SailShape))
+#define SAIL_SCENE_LIGHT_OFF (SAIL_SCENE_SURF_OFF + SAIL_MAX_OBJECTS * (int)sizeof(SailSurface))
+
+#ifndef __CUDACC_RTC__
+static_assert(offsetof(SailSceneBlock, shape) == SAIL_SCENE_SHAPE_OFF && offsetof(SailSceneBlock, surf) == SAIL_SCENE_SURF_OFF &&
+              offsetof(SailSceneBlock, light) == SAIL_SCENE_LIGHT_OFF, "SailSceneBlock layout");
 // Host packer (sail_pack.cpp).  Returns 0 or a negative sail error code; `err` receives a message.
 int sail_pack_scene(const float* objects, int n, const float* texparams, int tn, const float* lights, int ln,
                     SailSceneBlock* out, char* err, int errlen);
+#endif
 
 #endif

@@ -147,12 +147,13 @@ SD int opaqueInt(int v) {
 }
 // Phase 1: the value intersectX() would leave in `result.d` (MAX_DISTANCE = no hit).
 template <int F>
-SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd) {
+SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd, const int fixedCat = -1) {
     const float* q = s.q;
     // The three common shapes are tested by a compare chain (2-3 instructions each); a `switch` over all
     // categories compiles to a bounds check + jump-table load + indirect branch, 11 instructions per object.
     // opaqueInt() keeps the compiler from folding the chain back into that switch.
-    const int cat = s.category;
+    // fixedCat >= 0: the category is a compile-time constant of a scene-specialised kernel (SAIL_JIT_NRUNS below)
+    const int cat = fixedCat >= 0 ? fixedCat : s.category;
     if (cat == SAIL_CUBE || cat == SAIL_CORNELLBOX) {
         // cube.glsl:65-79: the near slab hit if it is in front, else the far one
         // cornellbox.glsl:67-81: always the far slab hit
@@ -162,7 +163,8 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd) {
         if (tNear < tFar) t = (cat == SAIL_CUBE && tNear > SAIL_EPSILON) ? tNear : tFar;
         return (t > SAIL_EPSILON) ? t : SAIL_MAX_DISTANCE;
     }
-    switch (opaqueInt(cat) == SAIL_SPHERE ? SAIL_SPHERE : (opaqueInt(cat) == SAIL_RECTANGLE ? SAIL_RECTANGLE : ((F & SAIL_F_QUADRICS) ? cat : 0))) {
+    const int cat2 = fixedCat >= 0 ? cat : opaqueInt(cat);
+    switch (cat2 == SAIL_SPHERE ? SAIL_SPHERE : (cat2 == SAIL_RECTANGLE ? SAIL_RECTANGLE : ((F & SAIL_F_QUADRICS) ? cat : 0))) {
         case SAIL_SPHERE: {  // sphere.glsl:10-16,45-62
             if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_SPH_C));
@@ -267,11 +269,37 @@ SD Nearest nearestObjectInline(const SceneView& sc, const Ray& ray) {
     Nearest r;
     r.t = SAIL_MAX_DISTANCE;
     r.id = -1;
+#ifdef SAIL_JIT_NRUNS
+    // Scene-specialised kernel (sail_jit.cpp): the object list is known at compile time as runs of equal shape
+    // category -- what the reference gets from generating its shader per scene (generator.js:107-123).  Runs are
+    // unrolled (no dispatch, no loop control, tests of different objects interleave); a run of three or more equal
+    // shapes stays a loop over that one shape's code, so the kernel does not grow with the object count.
+    constexpr int kRunCat[SAIL_JIT_NRUNS] = {SAIL_JIT_RUN_CATS};
+    constexpr int kRunStart[SAIL_JIT_NRUNS] = {SAIL_JIT_RUN_STARTS};
+    constexpr int kRunLen[SAIL_JIT_NRUNS] = {SAIL_JIT_RUN_LENS};
+#pragma unroll
+    for (int k = 0; k < SAIL_JIT_NRUNS; k++) {
+        if (kRunLen[k] < 3) {
+#pragma unroll
+            for (int j = 0; j < kRunLen[k]; j++) {
+                float t = shapeDistance<F>(sc.shape[kRunStart[k] + j], ray, rd, kRunCat[k]);
+                if (t < r.t) { r.t = t; r.id = kRunStart[k] + j; }
+            }
+        } else {
+#pragma unroll 1
+            for (int i = kRunStart[k]; i < kRunStart[k] + kRunLen[k]; i++) {
+                float t = shapeDistance<F>(sc.shape[i], ray, rd, kRunCat[k]);
+                if (t < r.t) { r.t = t; r.id = i; }
+            }
+        }
+    }
+#else
     const int n = sc.n;
     for (int i = 0; i < n; i++) {
         float t = shapeDistance<F>(sc.shape[i], ray, rd);
         if (t < r.t) { r.t = t; r.id = i; }
     }
+#endif
     return r;
 }
 template <int F>

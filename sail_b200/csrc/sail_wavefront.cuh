@@ -20,7 +20,7 @@
 #define SAIL_WF_STATE 16  // words of path state exchanged per bounce
 
 template <int F>
-__global__ void __launch_bounds__(SAIL_CTA_THREADS, SAIL_MIN_CTAS(F)) sail_trace_wavefront(const __grid_constant__ SailLaunch L) {
+SD void sailWaveBody(const SailLaunch& L) {
     __shared__ float slot[SAIL_WF_STATE][SAIL_CTA_THREADS];  // SoA: lane-consecutive words, conflict free
     __shared__ float firstHit[6][SAIL_CTA_THREADS];          // n, p of the primary hit, indexed by home lane
     __shared__ int hist[2][SAIL_MAX_OBJECTS + 2];  // double buffered: the next bounce's counters are cleared while this one scatters
@@ -142,6 +142,11 @@ __global__ void __launch_bounds__(SAIL_CTA_THREADS, SAIL_MIN_CTAS(F)) sail_trace
         L.hitId[pix] = firstId;
         L.depth[pix] = firstT;
     }
+}
+
+template <int F>
+__global__ void __launch_bounds__(SAIL_CTA_THREADS, SAIL_MIN_CTAS(F)) sail_trace_wavefront(const __grid_constant__ SailLaunch L) {
+    sailWaveBody<F>(L);
 }
 
 #endif

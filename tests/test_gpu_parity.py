@@ -18,12 +18,12 @@ def capi():
     return c
 
 
-def _render_both(capi, oracle, cfg, nframes, kernel=0, batch=False):
+def _render_both(capi, oracle, cfg, nframes, kernel=0, batch=False, specialise=0):
     W, H = SIZES[cfg]
     scene, o, t, l, bounces = scene_tables(cfg, W, H)
     oracle.set_scene(o, t, l)
     ctx = capi.Context(W, H)
-    ctx.configure(max_bounces=bounces, kernel=kernel)
+    ctx.configure(max_bounces=bounces, kernel=kernel, specialise=specialise)
     ctx.upload_scene(o, t, l)
     acc = np.zeros((H, W, 3), np.float32)
     frames = []
@@ -38,16 +38,20 @@ def _render_both(capi, oracle, cfg, nframes, kernel=0, batch=False):
     if batch:
         ctx.render_n(frames)
     out = {"color": ctx.read_accum(), "normal": ctx.read_aov(capi.AOV_NORMAL), "position": ctx.read_aov(capi.AOV_POSITION),
-           "hit_id": ctx.read_aov(capi.AOV_HIT_ID), "depth": ctx.read_aov(capi.AOV_DEPTH)}
+           "hit_id": ctx.read_aov(capi.AOV_HIT_ID), "depth": ctx.read_aov(capi.AOV_DEPTH), "kernel_info": ctx.kernel_info()}
     ctx.close()
     ref["color"] = acc
     return out, ref
 
 
+@pytest.mark.parametrize("specialise", [2, 1], ids=["jit", "aot"])
 @pytest.mark.parametrize("kernel", [0, 1], ids=["mega", "wavefront"])
 @pytest.mark.parametrize("cfg", [1, 2, 3, 5])
-def test_frames_bit_exact(capi, oracle, cfg, kernel):
-    out, ref = _render_both(capi, oracle, cfg, 4, kernel=kernel, batch=(kernel == 1))
+def test_frames_bit_exact(capi, oracle, cfg, kernel, specialise):
+    """Both kernels, each as the scene-specialised build (NVRTC at run time; REQUIRE fails loudly if that is not
+    possible) and as the ahead-of-time variant, against the oracle."""
+    out, ref = _render_both(capi, oracle, cfg, 4, kernel=kernel, batch=(kernel == 1), specialise=specialise)
+    assert out["kernel_info"].startswith("jit " if specialise == 2 else "aot "), out["kernel_info"]
     assert np.array_equal(out["hit_id"], ref["hit_id"]), "primary hit ids differ"
     for name in ("depth", "normal", "position", "color"):
         assert bits_equal(out[name], ref[name]), mismatch_report(out[name], ref[name], "cfg%d %s" % (cfg, name))
