@@ -121,22 +121,40 @@ int sail_jit_get(int device, int kind, int F, int minCtas, const SailSceneBlock*
         i = j;
     }
     if (nruns > SAIL_JIT_MAX_RUNS) { setErr(err, errlen, "more than 16 runs of distinct shapes"); return 2; }
+    // which plugins the scene contains (category ids as bit positions; ids outside 0..31 select no arm anyway)
+    unsigned shapes = 0, mats = 0, texs = 0, lights = 0, glass = 0;
+    auto bit = [](int c) { return (c >= 0 && c < 32) ? (1u << c) : 0u; };
+    for (int i = 0; i < n; i++) {
+        shapes |= bit(scene->shape[i].category);
+        mats |= bit(scene->shape[i].matCategory) | bit(scene->surf[i].matCategory);
+        texs |= bit(scene->surf[i].texCategory);
+        if (scene->shape[i].matCategory == SAIL_GLASS || scene->surf[i].matCategory == SAIL_GLASS) {
+            const float ur = scene->surf[i].m[SM_GLASS_UR], vr = scene->surf[i].m[SM_GLASS_VR];
+            glass |= (ur < 1e-5f && vr < 1e-5f) ? 1u : 2u;  // the shader's test, glass.glsl:13 (EPSILON, define.glsl)
+        }
+    }
+    for (int k = 0; scene->ln > 0 && k <= scene->ln; k++) lights |= bit(scene->light[k].category);
+    char masks[96];
+    snprintf(masks, sizeof(masks), " plugins=%x/%x/%x/%x/%x", shapes, mats, texs, lights, glass);
     char head[96];
     snprintf(head, sizeof(head), "jit %s<F=%d> n=%d shapes=", kind ? "wavefront" : "mega", F, n);
-    const std::string key = "dev" + std::to_string(device) + " m" + std::to_string(minCtas) + " " + head + cats;
+    const std::string key = "dev" + std::to_string(device) + " m" + std::to_string(minCtas) + " " + head + cats + masks;
     auto it = g_cache.find(key);
     if (it != g_cache.end()) {
         out->fn = it->second;
-        snprintf(out->info, sizeof(out->info), "%s%s (cached)", head, cats.c_str());
+        snprintf(out->info, sizeof(out->info), "%s%s%s (cached)", head, cats.c_str(), masks);
         return 0;
     }
     char src[2048];
     snprintf(src, sizeof(src),
              "#define SAIL_JIT_NRUNS %d\n#define SAIL_JIT_RUN_CATS %s\n#define SAIL_JIT_RUN_STARTS %s\n#define SAIL_JIT_RUN_LENS %s\n"
+             "#define SAIL_JIT_SHAPES 0x%xu\n#define SAIL_JIT_MATS 0x%xu\n#define SAIL_JIT_TEXS 0x%xu\n#define SAIL_JIT_LIGHTS 0x%xu\n"
+             "#define SAIL_JIT_GLASS %u\n"
              "#include \"sail_mega.cuh\"\n#include \"sail_wavefront.cuh\"\n"
              "extern \"C\" __global__ void __launch_bounds__(SAIL_CTA_THREADS, %d) sail_jit_kernel(const __grid_constant__ SailLaunch L) "
              "{ %s<%d>(L); }\n",
-             nruns, runCat.c_str(), runStart.c_str(), runLen.c_str(), minCtas, kind ? "sailWaveBody" : "sailMegaBody", F);
+             nruns, runCat.c_str(), runStart.c_str(), runLen.c_str(), shapes, mats, texs, lights, glass, minCtas,
+             kind ? "sailWaveBody" : "sailMegaBody", F);
     void* prog = nullptr;
     if (g_api.createProgram(&prog, src, "sail_jit.cu", kSailJitCount, kSailJitTexts, kSailJitNames) != 0) {
         setErr(err, errlen, "nvrtcCreateProgram failed");
@@ -171,7 +189,7 @@ int sail_jit_get(int device, int kind, int F, int minCtas, const SailSceneBlock*
     }
     g_cache[key] = fn;
     out->fn = fn;
-    snprintf(out->info, sizeof(out->info), "%s%s (nvrtc %d.%d, %.2f s)", head, cats.c_str(), g_api.nvrtcMajor, g_api.nvrtcMinor, secs);
+    snprintf(out->info, sizeof(out->info), "%s%s%s (nvrtc %d.%d, %.2f s)", head, cats.c_str(), masks, g_api.nvrtcMajor, g_api.nvrtcMinor, secs);
     return 0;
 }
 

@@ -278,7 +278,7 @@ SD V3 material(const SailSurface& su, int matCategory, V3 sc, bool into, V2 u, V
     float pdf = 0.0f;
     V3 fs = splat3(0.0f);
     switch (matCategory) {
-        case SAIL_MATTE: {  // matte.glsl:8-37
+        case SAIL_MATTE: if (SAIL_HAS_MAT(SAIL_MATTE)) {  // matte.glsl:8-37
             V3 R = m[SM_MATTE_KD] * sc;
             wi = cosineSampleHemisphere<F>(u);
             pdf = sameHemisphere(wo, wi) ? absCosTheta(wi) * SAIL_INVPI : 0.0f;
@@ -287,13 +287,13 @@ SD V3 material(const SailSurface& su, int matCategory, V3 sc, bool into, V2 u, V
             f = fs;  // matte_f() evaluates the same expression on the same (wo, wi)
             break;
         }
-        case SAIL_MIRROR: {  // mirror.glsl:5-16, bsdf.glsl:93-98 with the no-op Fresnel (= WHITE)
+        case SAIL_MIRROR: if (SAIL_HAS_MAT(SAIL_MIRROR)) {  // mirror.glsl:5-16, bsdf.glsl:93-98 with the no-op Fresnel (= WHITE)
             V3 R = m[SM_MIRROR_KR] * sc;
             wi = mk3(-wo.x, -wo.y, wo.z);
             fs = vdivs(splat3(1.0f) * R, absCosTheta(wi));
             return fs * absCosTheta(wi);  // pdf = 1: `/ pdf` multiplies by rcp(1) = 1 exactly
         }
-        case SAIL_METAL: if (F & SAIL_F_GLOSSY) {  // metal.glsl:8-23
+        case SAIL_METAL: if ((F & SAIL_F_GLOSSY) && SAIL_HAS_MAT(SAIL_METAL)) {  // metal.glsl:8-23
             MicroR mr;
             mr.R = sc;
             mr.fresnelKind = 1;
@@ -305,10 +305,11 @@ SD V3 material(const SailSurface& su, int matCategory, V3 sc, bool into, V2 u, V
             fs = microfacet_r_sample_f(mr, u, wo, wi, pdf);
             break;
         }
-        case SAIL_GLASS: if (F & SAIL_F_GLOSSY) {  // glass.glsl:10-35
+        case SAIL_GLASS: if ((F & SAIL_F_GLOSSY) && SAIL_HAS_MAT(SAIL_GLASS)) {  // glass.glsl:10-35
             float kr = m[SM_GLASS_KR], kt = m[SM_GLASS_KT], eta = m[SM_GLASS_ETA];
             float ur = m[SM_GLASS_UR], vr = m[SM_GLASS_VR];
-            if (ur < SAIL_EPSILON && vr < SAIL_EPSILON) {  // bsdf.glsl:141-158 SpecularFr(1, eta)
+            const bool smooth = ur < SAIL_EPSILON && vr < SAIL_EPSILON;
+            if (SAIL_HAS_SMOOTH_GLASS && (smooth || !SAIL_HAS_ROUGH_GLASS)) {  // bsdf.glsl:141-158 SpecularFr(1, eta)
                 float Fr = frDielectric(wo.z, 1.0f, eta);
                 if (u.x < Fr) {
                     wi = mk3(-wo.x, -wo.y, wo.z);
@@ -322,7 +323,7 @@ SD V3 material(const SailSurface& su, int matCategory, V3 sc, bool into, V2 u, V
                     pdf = 1.0f;
                     fs = vdivs(ft, absCosTheta(wi));
                 }
-            } else {
+            } else if (SAIL_HAS_ROUGH_GLASS) {
                 float p = u.x;
                 u.x = fmin2(u.x * 2.0f - 1.0f, SAIL_ONEMINUSEPSILON);
                 if (p < 0.5f) {
@@ -364,7 +365,7 @@ static __device__ __noinline__ V3 stubShapeNormal(const SailShape& s) {
     switch (s.category) {
         case SAIL_CUBE: return boxFaceNormal(hit, loOf(s), hiOf(s), s.rev);       // cube.glsl:25-38
         case SAIL_CORNELLBOX: return boxFaceNormal(hit, loOf(s), hiOf(s), 1.0f);  // cornellbox.glsl:39-51
-        case SAIL_CONE: if (F & SAIL_F_QUADRICS) {  // cone.glsl:38-46
+        case SAIL_CONE: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_CONE)) {  // cone.glsl:38-46
             V3 hh = hit - ld3(q + SQ_CONE_P);
             float d = dm_sqrt(hh.x * hh.x + hh.y * hh.y);
             float x1 = d * q[SQ_CONE_INVTANA];
@@ -372,9 +373,9 @@ static __device__ __noinline__ V3 stubShapeNormal(const SailShape& s) {
             V3 no = mk3(0.0f, 0.0f, q[SQ_CONE_H] - x1 - x2);
             return s.rev * normalize3(hh - no);
         }
-        case SAIL_CYLINDER: if (F & SAIL_F_QUADRICS)  // cylinder.glsl:36-38
+        case SAIL_CYLINDER: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_CYLINDER))  // cylinder.glsl:36-38
             return s.rev * normalize3(mk3(hit.x - q[SQ_CYL_P], hit.y - q[SQ_CYL_P + 1], 0.0f));
-        case SAIL_HYPERBOLOID: if (F & SAIL_F_QUADRICS) {  // hyperboloid.glsl:48-58
+        case SAIL_HYPERBOLOID: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_HYPERBOLOID)) {  // hyperboloid.glsl:48-58
             V3 p1 = ld3(q + SQ_HYP_P1), p2 = ld3(q + SQ_HYP_P2);
             float v = (hit.z - p1.z) * q[SQ_HYP_INVDZ];
             V3 pr = (1.0f - v) * p1 + v * p2;
@@ -386,7 +387,7 @@ static __device__ __noinline__ V3 stubShapeNormal(const SailShape& s) {
             V3 dpdv = mk3((p2.x - p1.x) * cp - (p2.y - p1.y) * sp, (p2.x - p1.x) * sp + (p2.y - p1.y) * cp, p2.z - p1.z);
             return s.rev * objToWorld(normalize3(cross3(dpdu, dpdv)));
         }
-        case SAIL_PARABOLOID: if (F & SAIL_F_QUADRICS) {  // paraboloid.glsl:42-49
+        case SAIL_PARABOLOID: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_PARABOLOID)) {  // paraboloid.glsl:42-49
             V3 dpdu = dpduAround(hit.x, hit.y);
             float inv = dm_rcp(2.0f * hit.z);
             V3 dpdv = q[SQ_PAR_DZ] * mk3(hit.x * inv, hit.y * inv, 1.0f);
@@ -403,20 +404,20 @@ SD V3 sampleGeometry(const SceneView& sc, V2 u, int i, V3& normal, float& pdf) {
     const SailShape& s = sc.shape[i];
     const float* q = s.q;
     switch (s.category) {
-        case SAIL_SPHERE: {  // sphere.glsl:29-31,88-92
+        case SAIL_SPHERE: if (SAIL_HAS_SHAPE(SAIL_SPHERE)) {  // sphere.glsl:29-31,88-92
             V3 c = ld3(q + SQ_SPH_C);
             V3 p = uniformSampleSphere(u) * q[SQ_SPH_R] + c;
             pdf = q[SQ_SPH_PDF];
             normal = (s.rev * (p - c)) * q[SQ_SPH_INVR];
             return p;
         }
-        case SAIL_RECTANGLE: {  // rectangle.glsl:25-30,65-70
+        case SAIL_RECTANGLE: if (SAIL_HAS_SHAPE(SAIL_RECTANGLE)) {  // rectangle.glsl:25-30,65-70
             V3 p = loOf(s) + ld3(q + SQ_RECT_DPDU) * u.x + ld3(q + SQ_RECT_DPDV) * u.y;
             pdf = q[SQ_RECT_PDF];
             normal = s.rev * ld3(q + SQ_RECT_N);
             return p;
         }
-        case SAIL_DISK: if (F & SAIL_F_QUADRICS) {  // disk.glsl:32-34,77-83
+        case SAIL_DISK: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_DISK)) {  // disk.glsl:32-34,77-83
             V2 pd = concentricSampleDisk(u);
             V3 p = mk3(pd.x * q[SQ_DISK_R] + q[SQ_DISK_P], q[SQ_DISK_P + 1], pd.y * q[SQ_DISK_R] + q[SQ_DISK_P + 2]);
             pdf = q[SQ_DISK_PDF];
@@ -437,7 +438,7 @@ SD V3 light_sample(const SceneView& sc, V2 u, V3 hit, V3 insNormal) {
     if (index > ln) index = ln;
     const SailLight& l = sc.light[index];
     switch (l.category) {
-        case SAIL_AREA: {  // area.glsl:13-23
+        case SAIL_AREA: if (SAIL_HAS_LIGHT(SAIL_AREA)) {  // area.glsl:13-23
             V3 normal;
             float pdf;
             V3 p = sampleGeometry<F>(sc, u, l.object, normal, pdf);
@@ -446,13 +447,13 @@ SD V3 light_sample(const SceneView& sc, V2 u, V3 hit, V3 insNormal) {
             if (testShadow<F>(sc, hit, toLight)) return splat3(0.0f);
             return vdivs(ld3(l.emission) * fmax2(0.0f, dot3(normal, -normToLight)) * fmax2(0.0f, dot3(normToLight, insNormal)), pdf);
         }
-        case SAIL_POINT: {  // point.glsl:13-20
+        case SAIL_POINT: if (SAIL_HAS_LIGHT(SAIL_POINT)) {  // point.glsl:13-20
             V3 p = ld3(l.from) + uniformSampleSphere(u) * 0.1f;
             V3 toLight = p - hit;
             if (testShadow<F>(sc, hit, toLight)) return splat3(0.0f);
             return ld3(l.emission) * fmax2(0.0f, dot3(normalize3(toLight), insNormal));
         }
-        case SAIL_SPOT: {  // spot.glsl:17-39 (axis fixed to -y)
+        case SAIL_SPOT: if (SAIL_HAS_LIGHT(SAIL_SPOT)) {  // spot.glsl:17-39 (axis fixed to -y)
             V3 toLight = ld3(l.from) - hit;
             if (testShadow<F>(sc, hit, toLight)) return splat3(0.0f);
             V3 normToLight = normalize3(toLight);

@@ -61,6 +61,25 @@ enum { SAIL_F_QUADRICS = 1,  // cone, cylinder, disk, hyperboloid, paraboloid pr
        SAIL_F_NEE = 8,       // ln > 0: next-event estimation + shadow rays
        SAIL_F_ALL = 15 };
 
+// A scene-specialised kernel (sail_jit.cpp) also knows which shape / material / texture / light plugins the scene
+// contains and compiles only those arms -- the reference's per-scene shader generation (generator.js:107-123).  In the
+// ahead-of-time variants every arm the feature set F allows is present.
+#ifdef SAIL_JIT_NRUNS
+#define SAIL_HAS_SHAPE(c) ((((unsigned)(SAIL_JIT_SHAPES)) >> (c)) & 1u)
+#define SAIL_HAS_MAT(c) ((((unsigned)(SAIL_JIT_MATS)) >> (c)) & 1u)
+#define SAIL_HAS_TEX(c) ((((unsigned)(SAIL_JIT_TEXS)) >> (c)) & 1u)
+#define SAIL_HAS_LIGHT(c) ((((unsigned)(SAIL_JIT_LIGHTS)) >> (c)) & 1u)
+#define SAIL_HAS_SMOOTH_GLASS ((SAIL_JIT_GLASS) & 1)
+#define SAIL_HAS_ROUGH_GLASS ((SAIL_JIT_GLASS) & 2)
+#else
+#define SAIL_HAS_SHAPE(c) 1
+#define SAIL_HAS_MAT(c) 1
+#define SAIL_HAS_TEX(c) 1
+#define SAIL_HAS_LIGHT(c) 1
+#define SAIL_HAS_SMOOTH_GLASS 1
+#define SAIL_HAS_ROUGH_GLASS 1
+#endif
+
 // Out-of-line transcendentals: one copy per kernel instead of one per call site (I-cache footprint).
 static __device__ __noinline__ float sail_sin(float x) { return dm_sin(x); }
 static __device__ __noinline__ float2 sail_sincos(float x) { float s, c; dm_sincos(x, &s, &c); return make_float2(s, c); }
@@ -165,7 +184,7 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd, const int fixe
     }
     const int cat2 = fixedCat >= 0 ? cat : opaqueInt(cat);
     switch (cat2 == SAIL_SPHERE ? SAIL_SPHERE : (cat2 == SAIL_RECTANGLE ? SAIL_RECTANGLE : ((F & SAIL_F_QUADRICS) ? cat : 0))) {
-        case SAIL_SPHERE: {  // sphere.glsl:10-16,45-62
+        case SAIL_SPHERE: if (SAIL_HAS_SHAPE(SAIL_SPHERE)) {  // sphere.glsl:10-16,45-62
             if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_SPH_C));
             float a = dot3(dl, dl);
@@ -179,7 +198,7 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd, const int fixe
             if (t >= SAIL_MAX_DISTANCE) return SAIL_MAX_DISTANCE;
             return t;
         }
-        case SAIL_RECTANGLE: {  // rectangle.glsl:32-55
+        case SAIL_RECTANGLE: if (SAIL_HAS_SHAPE(SAIL_RECTANGLE)) {  // rectangle.glsl:32-55
             V3 nn = ld3(q + SQ_RECT_N), ss = ld3(q + SQ_RECT_SS), ts = ld3(q + SQ_RECT_TS);
             V3 dl = worldToLocal(ray.d, nn, ss, ts);
             V3 ol = worldToLocal(ray.o - loOf(s), nn, ss, ts);
@@ -191,7 +210,7 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd, const int fixe
                 return SAIL_MAX_DISTANCE;
             return t;
         }
-        case SAIL_CONE: if (F & SAIL_F_QUADRICS) {  // cone.glsl:11-17,48-81
+        case SAIL_CONE: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_CONE)) {  // cone.glsl:11-17,48-81
             if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_CONE_P));
             float k = q[SQ_CONE_K], h = q[SQ_CONE_H];
@@ -200,7 +219,7 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd, const int fixe
             float c = ol.x * ol.x + ol.y * ol.y - k * (ol.z - h) * (ol.z - h);
             return quadricRoot(a, b, c, ol, dl, -SAIL_EPSILON, h);
         }
-        case SAIL_CYLINDER: if (F & SAIL_F_QUADRICS) {  // cylinder.glsl:11-17,40-72
+        case SAIL_CYLINDER: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_CYLINDER)) {  // cylinder.glsl:11-17,40-72
             if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_CYL_P));
             float a = dl.x * dl.x + dl.y * dl.y;
@@ -208,7 +227,7 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd, const int fixe
             float c = ol.x * ol.x + ol.y * ol.y - q[SQ_CYL_RR];
             return quadricRoot(a, b, c, ol, dl, -SAIL_EPSILON, q[SQ_CYL_H]);
         }
-        case SAIL_DISK: if (F & SAIL_F_QUADRICS) {  // disk.glsl:36-53
+        case SAIL_DISK: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_DISK)) {  // disk.glsl:36-53
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_DISK_P));
             if (dl.z == 0.0f) return SAIL_MAX_DISTANCE;
             float t = fdiv(-ol.z, dl.z);
@@ -219,7 +238,7 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd, const int fixe
             if (t >= SAIL_MAX_DISTANCE) return SAIL_MAX_DISTANCE;
             return t;
         }
-        case SAIL_HYPERBOLOID: if (F & SAIL_F_QUADRICS) {  // hyperboloid.glsl:13-24,60-90
+        case SAIL_HYPERBOLOID: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_HYPERBOLOID)) {  // hyperboloid.glsl:13-24,60-90
             if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_HYP_P));
             float ah = q[SQ_HYP_AH], ch = q[SQ_HYP_CH];
@@ -228,7 +247,7 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd, const int fixe
             float c = ah * ol.x * ol.x + ah * ol.y * ol.y - ch * ol.z * ol.z - 1.0f;
             return quadricRoot(a, b, c, ol, dl, q[SQ_HYP_ZMIN], q[SQ_HYP_ZMAX]);
         }
-        case SAIL_PARABOLOID: if (F & SAIL_F_QUADRICS) {  // paraboloid.glsl:12-20,51-82
+        case SAIL_PARABOLOID: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_PARABOLOID)) {  // paraboloid.glsl:12-20,51-82
             if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_PAR_P));
             float k = q[SQ_PAR_K];
@@ -327,17 +346,17 @@ template <int F>
 SD V3 surfaceColor(const SailSurface& u, V2 uv) {
     const float* t = u.t;
     if (F & SAIL_F_TEXTURED) switch (u.texCategory) {
-        case SAIL_CHECKERBOARD: {  // checkerboard.glsl:6-20
+        case SAIL_CHECKERBOARD: if (SAIL_HAS_TEX(SAIL_CHECKERBOARD)) {  // checkerboard.glsl:6-20
             float ax = uv.x * t[13], ay = uv.y * t[13], width = t[14];
             float fx = ax - dm_floor(ax), fy = ay - dm_floor(ay);
             bool in_outline = (fx < width || fx > 1.0f - width) || (fy < width || fy > 1.0f - width);
             return in_outline ? splat3(0.5f) : splat3(1.0f);
         }
-        case SAIL_CHECKERBOARD2: {  // checkerboard2.glsl:7-16
+        case SAIL_CHECKERBOARD2: if (SAIL_HAS_TEX(SAIL_CHECKERBOARD2)) {  // checkerboard2.glsl:7-16
             float ux = dm_floor(uv.x * t[13]), uy = dm_floor(uv.y * t[13]);
             return (toInt(ux + uy) % 2 == 0) ? ld3(t + ST_C1) : ld3(t + ST_C2);
         }
-        case SAIL_BILERP: {  // bilerp.glsl:1-14 (broken in the reference, SURVEY Q12: evident intent)
+        case SAIL_BILERP: if (SAIL_HAS_TEX(SAIL_BILERP)) {  // bilerp.glsl:1-14 (broken in the reference, SURVEY Q12: evident intent)
             float ux = uv.x, uy = uv.y;
             return (1.0f - ux) * (1.0f - uy) * ld3(t + ST_B00) + (1.0f - ux) * uy * ld3(t + ST_B01) +
                    ux * (1.0f - uy) * ld3(t + ST_B10) + ux * uy * ld3(t + ST_B11);
@@ -413,7 +432,7 @@ SD void hitRecord(const SceneView& sc, int i, float t, const Ray& ray, Hit& h) {
             }
             break;
         }
-        case SAIL_SPHERE: {  // sphere.glsl:33-43,62-84
+        case SAIL_SPHERE: if (SAIL_HAS_SHAPE(SAIL_SPHERE)) {  // sphere.glsl:33-43,62-84
             V3 c = ld3(q + SQ_SPH_C);
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - c);
             V3 hl = ol + t * dl;
@@ -436,7 +455,7 @@ SD void hitRecord(const SceneView& sc, int i, float t, const Ray& ray, Hit& h) {
             h.dpdu = objToWorld(dpdu);
             break;
         }
-        case SAIL_RECTANGLE: {  // rectangle.glsl:36-62
+        case SAIL_RECTANGLE: if (SAIL_HAS_SHAPE(SAIL_RECTANGLE)) {  // rectangle.glsl:36-62
             V3 nn = ld3(q + SQ_RECT_N), ss = ld3(q + SQ_RECT_SS), ts = ld3(q + SQ_RECT_TS), mn = loOf(s);
             V3 dl = worldToLocal(ray.d, nn, ss, ts);
             V3 ol = worldToLocal(ray.o - mn, nn, ss, ts);
@@ -448,7 +467,7 @@ SD void hitRecord(const SceneView& sc, int i, float t, const Ray& ray, Hit& h) {
             h.dpdu = ld3(q + SQ_RECT_DPDU);
             break;
         }
-        case SAIL_CONE: if (F & SAIL_F_QUADRICS) {  // cone.glsl:31-36,83-98
+        case SAIL_CONE: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_CONE)) {  // cone.glsl:31-36,83-98
             V3 p = ld3(q + SQ_CONE_P);
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - p);
             V3 hl = ol + t * dl;
@@ -464,7 +483,7 @@ SD void hitRecord(const SceneView& sc, int i, float t, const Ray& ray, Hit& h) {
             h.dpdu = objToWorld(dpdu);
             break;
         }
-        case SAIL_CYLINDER: if (F & SAIL_F_QUADRICS) {  // cylinder.glsl:31-34,74-89
+        case SAIL_CYLINDER: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_CYLINDER)) {  // cylinder.glsl:31-34,74-89
             V3 p = ld3(q + SQ_CYL_P);
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - p);
             V3 hl = ol + t * dl;
@@ -478,7 +497,7 @@ SD void hitRecord(const SceneView& sc, int i, float t, const Ray& ray, Hit& h) {
             h.dpdu = objToWorld(dpdu);
             break;
         }
-        case SAIL_DISK: if (F & SAIL_F_QUADRICS) {  // disk.glsl:27-30,55-74
+        case SAIL_DISK: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_DISK)) {  // disk.glsl:27-30,55-74
             V3 p = ld3(q + SQ_DISK_P);
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - p);
             V3 hl = ol + t * dl;
@@ -497,7 +516,7 @@ SD void hitRecord(const SceneView& sc, int i, float t, const Ray& ray, Hit& h) {
             h.dpdu = objToWorld(dpdu);
             break;
         }
-        case SAIL_HYPERBOLOID: if (F & SAIL_F_QUADRICS) {  // hyperboloid.glsl:41-46,92-110
+        case SAIL_HYPERBOLOID: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_HYPERBOLOID)) {  // hyperboloid.glsl:41-46,92-110
             V3 p = ld3(q + SQ_HYP_P), p1 = ld3(q + SQ_HYP_P1), p2 = ld3(q + SQ_HYP_P2);
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - p);
             V3 hl = ol + t * dl;
