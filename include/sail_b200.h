@@ -67,7 +67,7 @@ enum {
 enum {
     SAIL_KERNEL_MEGA = 0,       /* one thread traces a whole path */
     SAIL_KERNEL_WAVEFRONT = 1,  /* per-bounce stages over ray queues regrouped by hit object, queues in shared memory */
-    SAIL_KERNEL_AUTO = 2        /* default: wavefront for scenes with quadric shapes or metal/glass, megakernel otherwise */
+    SAIL_KERNEL_AUTO = 2        /* default: wavefront for scenes with quadric shapes (and, among the ahead-of-time variants, metal/glass), megakernel otherwise */
 };
 
 enum {

@@ -322,10 +322,18 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
     // the variant follows the scene's content, never the caller's mask hints
     dim3 grid((ctx->W + SAIL_TILE_W - 1) / SAIL_TILE_W, tileRows);
     const int F = ctx->hostScene.features & SAIL_F_ALL;
-    const bool wave = ctx->cfg.kernel == SAIL_KERNEL_WAVEFRONT || (ctx->cfg.kernel == SAIL_KERNEL_AUTO && (F & (SAIL_F_QUADRICS | SAIL_F_GLOSSY)));
-    const int kind = wave ? 1 : 0;
+    // SAIL_KERNEL_AUTO, from the measured matrix: the wavefront pays where the scene has many shape codes
+    // (quadrics); among the ahead-of-time variants also where it has many BSDFs (metal / glass).
+    const bool tryJit = ctx->cfg.specialise != SAIL_SPECIALISE_OFF;
+    bool wave = ctx->cfg.kernel == SAIL_KERNEL_WAVEFRONT;
+    if (ctx->cfg.kernel == SAIL_KERNEL_AUTO) {
+        wave = (F & SAIL_F_QUADRICS) != 0;
+        const bool jitFailed = tryJit && ctx->jitTried[wave ? 1 : 0] && !ctx->jitFn[wave ? 1 : 0];
+        if (!tryJit || jitFailed) wave = (F & (SAIL_F_QUADRICS | SAIL_F_GLOSSY)) != 0;
+    }
+    int kind = wave ? 1 : 0;
     void* jit = nullptr;
-    if (ctx->cfg.specialise != SAIL_SPECIALISE_OFF) {
+    if (tryJit) {
         if (!ctx->jitTried[kind]) {
             ctx->jitTried[kind] = true;
             SailJitKernel k;
@@ -340,6 +348,12 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
             }
         }
         jit = ctx->jitFn[kind];
+        if (!jit && ctx->cfg.kernel == SAIL_KERNEL_AUTO && (F & SAIL_F_GLOSSY) && !wave) {  // first failure: re-decide for the AOT variants
+            wave = true;
+            kind = 1;
+            snprintf(ctx->jitNote[1], sizeof(ctx->jitNote[1]), "aot wavefront<F=%d> (%s)", F, ctx->jitNote[0]);
+            ctx->jitTried[1] = true;
+        }
         if (!jit && ctx->cfg.specialise == SAIL_SPECIALISE_REQUIRE)
             return setErr(ctx, SAIL_ERR_STATE, "scene-specialised kernel unavailable: %s", ctx->jitNote[kind]);
         snprintf(ctx->kernelInfo, sizeof(ctx->kernelInfo), "%s", ctx->jitNote[kind]);

@@ -178,6 +178,10 @@ int sail_jit_get(int device, int kind, int F, int minCtas, const SailSceneBlock*
     std::vector<char> cubin(cs);
     g_api.cubin(prog, cubin.data());
     g_api.destroyProgram(&prog);
+    if (const char* dump = getenv("SAIL_B200_JIT_DUMP")) {  // keep the cubin for cuobjdump / nvdisasm / tools/sass_lines.py
+        std::string name = std::string(dump) + "/sail_jit_" + (kind ? "wave" : "mega") + "_F" + std::to_string(F) + "_n" + std::to_string(n) + ".cubin";
+        if (FILE* f = fopen(name.c_str(), "wb")) { fwrite(cubin.data(), 1, cubin.size(), f); fclose(f); }
+    }
     void *mod = nullptr, *fn = nullptr;
     int cr = g_api.moduleLoadData(&mod, cubin.data());
     if (cr == 0) cr = g_api.moduleGetFunction(&fn, mod, "sail_jit_kernel");
