@@ -201,6 +201,11 @@ int sail_last_render_ms(sail_ctx* ctx, float* ms);
  * "jit mega<F=0> n=3 cats=1,9,2 (nvrtc 12.9, 0.8 s)" or "aot wavefront<F=10> (jit: NVRTC not found ...)".
  * Returns the length written (excluding the terminator), or a negative error code. */
 int sail_kernel_info(sail_ctx* ctx, char* buf, int32_t len);
+/* Compiles the scene-specialised kernel for these tables without loading it: needs NVRTC but neither a GPU nor the
+ * driver library, so a build machine can check that a scene's kernel compiles.  kernel = SAIL_KERNEL_MEGA / _WAVEFRONT.
+ * Returns 0 and a description in `info`, or a negative code and the reason (NVRTC missing, compiler log, bad tables). */
+int sail_jit_compile_check(const float* objects, int32_t n, const float* texparams, int32_t tn, const float* lights, int32_t ln,
+                           int32_t kernel, char* info, int32_t infolen);
 /* Page-locked host memory for the caller's image / table buffers, so that sail_present / sail_read_* copy
  * straight into it at full PCIe rate (the destination ArrayBuffer of the reference's gl.readPixels,
  * src/core/webgl.js:88-92 usage in renderer.js; an N-API host wraps it as an external ArrayBuffer).  Returns NULL

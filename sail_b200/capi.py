@@ -78,6 +78,8 @@ _SIGNATURES = {
     "sail_launch_count": (ctypes.c_uint64, [_P]),
     "sail_last_render_ms": (ctypes.c_int, [_P, ctypes.POINTER(ctypes.c_float)]),
     "sail_kernel_info": (ctypes.c_int, [_P, ctypes.c_char_p, ctypes.c_int32]),
+    "sail_jit_compile_check": (ctypes.c_int, [_P, ctypes.c_int32, _P, ctypes.c_int32, _P, ctypes.c_int32, ctypes.c_int32,
+                                              ctypes.c_char_p, ctypes.c_int32]),
     "sail_alloc_host": (ctypes.c_void_p, [ctypes.c_uint64]),
     "sail_free_host": (None, [ctypes.c_void_p]),
 }
@@ -357,6 +359,17 @@ def frames_from_arrays(matrices, eye, textureWeights, times):
     out = (Frame * n)()
     ctypes.memmove(out, rows.ctypes.data, rows.nbytes)
     return out
+
+
+def jit_compile_check(objects, texparams, lights, kernel=KERNEL_MEGA):
+    """Compile (not load) the scene-specialised kernel of these tables; works without a GPU.  Returns the description."""
+    o, t, l = _f32(objects).reshape(-1), _f32(texparams).reshape(-1), _f32(lights).reshape(-1)
+    buf = ctypes.create_string_buffer(600)
+    rc = load().sail_jit_compile_check(_ptr(o) if o.size else None, o.size // 18, _ptr(t) if t.size else None, t.size // 16,
+                                       _ptr(l) if l.size else None, l.size // 18, int(kernel), buf, 600)
+    if rc != 0:
+        raise SailError(rc, buf.value.decode(errors="replace"))
+    return buf.value.decode()
 
 
 def device_count():

@@ -269,6 +269,28 @@ int sail_scene_features(const float* objects, int32_t n, const float* texparams,
     return rc ? rc : feat;
 }
 
+int sail_jit_compile_check(const float* objects, int32_t n, const float* texparams, int32_t tn, const float* lights, int32_t ln,
+                           int32_t kernel, char* info, int32_t infolen) {
+    if (kernel != SAIL_KERNEL_MEGA && kernel != SAIL_KERNEL_WAVEFRONT) return SAIL_ERR_INVALID;
+    SailSceneBlock* blk = new (std::nothrow) SailSceneBlock;
+    if (!blk) return SAIL_ERR_NOMEM;
+    int rc = sail_pack_scene(objects, n, texparams, tn, lights, ln, blk, info, infolen);
+    if (rc == 0) {
+        SailJitKernel k;
+        char why[400];
+        why[0] = 0;
+        const int F = blk->features & SAIL_F_ALL;
+        if (sail_jit_get(-1, kernel == SAIL_KERNEL_WAVEFRONT ? 1 : 0, F, SAIL_MIN_CTAS(F), blk, &k, why, sizeof(why)) == 0) {
+            if (info && infolen > 0) snprintf(info, (size_t)infolen, "%s", k.info);
+        } else {
+            if (info && infolen > 0) snprintf(info, (size_t)infolen, "%s", why);
+            rc = SAIL_ERR_STATE;
+        }
+    }
+    delete blk;
+    return rc;
+}
+
 int sail_set_row_bands(sail_ctx* ctx, int32_t band_rows, int32_t band_stride, int32_t band_first) {
     if (!ctx) return SAIL_ERR_INVALID;
     if (band_stride < 1 || band_first < 0 || band_first >= band_stride || band_rows < SAIL_TILE_H || band_rows % SAIL_TILE_H)

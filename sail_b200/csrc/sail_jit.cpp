@@ -40,8 +40,9 @@ typedef int (*cuLaunchKernel_t)(void*, unsigned, unsigned, unsigned, unsigned, u
 typedef int (*cuGetErrorString_t)(int, const char**);
 
 struct Api {
-    bool tried = false, ok = false;
-    std::string why;
+    bool tried = false, ok = false;        // NVRTC
+    bool cuTried = false, cuOk = false;    // driver library (needed to load and launch, not to compile)
+    std::string why, cuWhy;
     int nvrtcMajor = 0, nvrtcMinor = 0;
     nvrtcCreateProgram_t createProgram = nullptr;
     nvrtcCompileProgram_t compileProgram = nullptr;
@@ -75,8 +76,6 @@ bool loadApi() {
     const char* envPath = getenv("SAIL_B200_NVRTC");
     void* nv = openFirst({envPath ? envPath : "", "/usr/local/cuda/lib64/libnvrtc.so.12", "libnvrtc.so.12", "libnvrtc.so"}, &tried);
     if (!nv) { g_api.why = "NVRTC not found (tried " + tried + ")"; return false; }
-    void* cu = openFirst({"libcuda.so.1", "libcuda.so"}, &tried);
-    if (!cu) { g_api.why = "CUDA driver library not found"; return false; }
 #define SYM(lib, field, name, type) g_api.field = (type)dlsym(lib, name); if (!g_api.field) { g_api.why = std::string("missing symbol ") + name; return false; }
     SYM(nv, createProgram, "nvrtcCreateProgram", nvrtcCreateProgram_t)
     SYM(nv, compileProgram, "nvrtcCompileProgram", nvrtcCompileProgram_t)
@@ -85,13 +84,25 @@ bool loadApi() {
     SYM(nv, cubinSize, "nvrtcGetCUBINSize", nvrtcGetSize_t)
     SYM(nv, cubin, "nvrtcGetCUBIN", nvrtcGetData_t)
     SYM(nv, destroyProgram, "nvrtcDestroyProgram", nvrtcDestroyProgram_t)
+#undef SYM
+    if (nvrtcVersion_t ver = (nvrtcVersion_t)dlsym(nv, "nvrtcVersion")) ver(&g_api.nvrtcMajor, &g_api.nvrtcMinor);
+    g_api.ok = true;
+    return true;
+}
+
+bool loadDriver() {
+    if (g_api.cuTried) return g_api.cuOk;
+    g_api.cuTried = true;
+    std::string tried;
+    void* cu = openFirst({"libcuda.so.1", "libcuda.so"}, &tried);
+    if (!cu) { g_api.cuWhy = "CUDA driver library not found"; return false; }
+#define SYM(lib, field, name, type) g_api.field = (type)dlsym(lib, name); if (!g_api.field) { g_api.cuWhy = std::string("missing symbol ") + name; return false; }
     SYM(cu, moduleLoadData, "cuModuleLoadData", cuModuleLoadData_t)
     SYM(cu, moduleGetFunction, "cuModuleGetFunction", cuModuleGetFunction_t)
     SYM(cu, launchKernel, "cuLaunchKernel", cuLaunchKernel_t)
     SYM(cu, errorString, "cuGetErrorString", cuGetErrorString_t)
 #undef SYM
-    if (nvrtcVersion_t ver = (nvrtcVersion_t)dlsym(nv, "nvrtcVersion")) ver(&g_api.nvrtcMajor, &g_api.nvrtcMinor);
-    g_api.ok = true;
+    g_api.cuOk = true;
     return true;
 }
 
@@ -101,9 +112,10 @@ void setErr(char* err, int errlen, const std::string& s) {
 
 }  // namespace
 
-int sail_jit_get(int device, int kind, int F, int minCtas, const SailSceneBlock* scene, SailJitKernel* out, char* err, int errlen) {
-    std::lock_guard<std::mutex> lock(g_mutex);
+// device < 0: compile only (no driver library, no GPU needed) -- sail_jit_compile_check.
+static int jitGetLocked(int device, int kind, int F, int minCtas, const SailSceneBlock* scene, SailJitKernel* out, char* err, int errlen) {
     if (!loadApi()) { setErr(err, errlen, g_api.why); return 1; }
+    if (device >= 0 && !loadDriver()) { setErr(err, errlen, g_api.cuWhy); return 1; }
     const int n = scene->n;
     if (n < 1) { setErr(err, errlen, "empty scene"); return 2; }
     // runs of equal shape category in slot order
@@ -178,6 +190,12 @@ int sail_jit_get(int device, int kind, int F, int minCtas, const SailSceneBlock*
     std::vector<char> cubin(cs);
     g_api.cubin(prog, cubin.data());
     g_api.destroyProgram(&prog);
+    if (device < 0) {
+        out->fn = nullptr;
+        snprintf(out->info, sizeof(out->info), "%s%s%s (nvrtc %d.%d, %.2f s, %zu byte cubin, not loaded)", head, cats.c_str(), masks,
+                 g_api.nvrtcMajor, g_api.nvrtcMinor, secs, cs);
+        return 0;
+    }
     if (const char* dump = getenv("SAIL_B200_JIT_DUMP")) {  // keep the cubin for cuobjdump / nvdisasm / tools/sass_lines.py
         std::string name = std::string(dump) + "/sail_jit_" + (kind ? "wave" : "mega") + "_F" + std::to_string(F) + "_n" + std::to_string(n) + ".cubin";
         if (FILE* f = fopen(name.c_str(), "wb")) { fwrite(cubin.data(), 1, cubin.size(), f); fclose(f); }
@@ -195,6 +213,11 @@ int sail_jit_get(int device, int kind, int F, int minCtas, const SailSceneBlock*
     out->fn = fn;
     snprintf(out->info, sizeof(out->info), "%s%s%s (nvrtc %d.%d, %.2f s)", head, cats.c_str(), masks, g_api.nvrtcMajor, g_api.nvrtcMinor, secs);
     return 0;
+}
+
+int sail_jit_get(int device, int kind, int F, int minCtas, const SailSceneBlock* scene, SailJitKernel* out, char* err, int errlen) {
+    std::lock_guard<std::mutex> lock(g_mutex);
+    return jitGetLocked(device, kind, F, minCtas, scene, out, err, errlen);
 }
 
 int sail_jit_launch(void* fn, const void* launch, unsigned gridX, unsigned gridY, unsigned block, unsigned smemBytes, void* stream,

@@ -12,6 +12,7 @@ struct SailJitKernel {
 
 // kind: 0 megakernel, 1 wavefront.  Returns 0 and fills `out`, or non-zero with a message in `err` (NVRTC or the
 // driver library missing, compilation failed, scene too large ...): the caller then uses the ahead-of-time variant.
+// device < 0 compiles only (NVRTC needs neither the driver library nor a GPU) and leaves out->fn null.
 int sail_jit_get(int device, int kind, int F, int minCtas, const SailSceneBlock* scene, SailJitKernel* out, char* err, int errlen);
 // Launches `fn` with the SailLaunch parameter block at `launch` on `stream`.  Returns 0 or a CUDA driver error code.
 int sail_jit_launch(void* fn, const void* launch, unsigned gridX, unsigned gridY, unsigned block, unsigned smemBytes, void* stream,

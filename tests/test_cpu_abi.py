@@ -106,3 +106,46 @@ def test_napi_addon_source_compiles_against_the_header():
     r = subprocess.run(["g++", "-std=c++17", "-fsyntax-only", "-Wall", "-I", os.path.join(ROOT, "tests", "napi_stub"), "-I",
                         os.path.join(ROOT, "include"), os.path.join(ROOT, "napi", "sail_napi.cc")], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
+
+
+@pytest.mark.parametrize("cfg", [1, 2, 3, 5])
+def test_scene_specialised_kernels_compile_without_a_gpu(capi, cfg):
+    """The kernels that NVRTC builds per scene structure at run time must compile for every
+    BASELINE config -- checked here with sail_jit_compile_check, which needs NVRTC but no device."""
+    _, o, t, l, _ = scene_tables(cfg, 64, 64)
+    for kernel in (capi.KERNEL_MEGA, capi.KERNEL_WAVEFRONT):
+        try:
+            info = capi.jit_compile_check(o, t, l, kernel)
+        except capi.SailError as e:
+            if "NVRTC not found" in str(e):
+                pytest.skip("no NVRTC on this machine: the library would run its ahead-of-time variants")
+            raise
+        assert info.startswith("jit ") and "n=%d" % o.shape[0] in info and "cubin" in info, info
+
+
+def test_scene_specialisation_limits(capi):
+    """A run of equal shapes stays one loop (64 spheres compile); more than 16 runs of distinct shapes are refused, which
+    makes the library use its ahead-of-time variant."""
+    import sail_b200 as Sail
+    m, w = Sail.Matte(0.7), Sail.Color.WHITE
+    from sail_b200.wire import serialize_scene
+
+    def tables(objs):
+        sc = Sail.Scene()
+        for ob in objs:
+            sc.add(ob)
+        sc.add(Sail.Camera([0, 1, -5], [0, 1, 0]))
+        return serialize_scene(sc)
+    try:
+        info = capi.jit_compile_check(*tables([Sail.Sphere([i * 0.1, 1, 2], 0.04, m, w) for i in range(64)]))
+    except capi.SailError as e:
+        if "NVRTC not found" in str(e):
+            pytest.skip("no NVRTC on this machine")
+        raise
+    assert "shapes=2x64" in info, info
+    alternating = []
+    for i in range(17):
+        alternating.append(Sail.Sphere([i * 0.2, 1, 2], 0.05, m, w) if i % 2 else Sail.Cube([i * 0.2, 0, 0], [i * 0.2 + 0.1, 0.1, 0.1], m, w))
+    with pytest.raises(capi.SailError) as ei:
+        capi.jit_compile_check(*tables(alternating))
+    assert "16 runs" in str(ei.value)

@@ -44,7 +44,10 @@ def function_of(idx, fl):
 
 def sass_with_lines(so, kernel):
     tmp = tempfile.mkdtemp()
-    subprocess.check_call(["cuobjdump", "-xelf", "all", os.path.abspath(so)], cwd=tmp, stdout=subprocess.DEVNULL)
+    if so.endswith(".cubin"):  # a run-time compiled kernel dumped with SAIL_B200_JIT_DUMP
+        subprocess.check_call(["cp", os.path.abspath(so), tmp])
+    else:
+        subprocess.check_call(["cuobjdump", "-xelf", "all", os.path.abspath(so)], cwd=tmp, stdout=subprocess.DEVNULL)
     out = []
     for f in sorted(os.listdir(tmp)):
         if not f.endswith(".cubin"):
@@ -93,7 +96,7 @@ def main():
     tots = sum(a[1] for a in agg.values()) or 1
     # ---- by function bucket: the outermost inlined frame that is not the kernel / bounce loop itself ----
     idx = function_index(os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "sail_b200", "csrc"))
-    skip = {"sail_trace_megakernel", "__launch_bounds__", "tracePath", "intersectObjects", "?"}
+    skip = {"sail_trace_megakernel", "sailMegaBody", "sailWaveBody", "__launch_bounds__", "tracePath", "intersectObjects", "?"}
     fagg = collections.defaultdict(lambda: [0, 0, 0])
     for i in range(n):
         chain = sass[i][3] or (sass[i][2],)
