@@ -161,11 +161,14 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
     snprintf(src, sizeof(src),
              "#define SAIL_JIT_NRUNS %d\n#define SAIL_JIT_RUN_CATS %s\n#define SAIL_JIT_RUN_STARTS %s\n#define SAIL_JIT_RUN_LENS %s\n"
              "#define SAIL_JIT_SHAPES 0x%xu\n#define SAIL_JIT_MATS 0x%xu\n#define SAIL_JIT_TEXS 0x%xu\n#define SAIL_JIT_LIGHTS 0x%xu\n"
-             "#define SAIL_JIT_GLASS %u\n"
+             "#define SAIL_JIT_GLASS %u\n%s"
              "#include \"sail_mega.cuh\"\n#include \"sail_wavefront.cuh\"\n"
              "extern \"C\" __global__ void __launch_bounds__(SAIL_CTA_THREADS, %d) sail_jit_kernel(const __grid_constant__ SailLaunch L) "
              "{ %s<%d>(L); }\n",
-             nruns, runCat.c_str(), runStart.c_str(), runLen.c_str(), shapes, mats, texs, lights, glass, minCtas,
+             nruns, runCat.c_str(), runStart.c_str(), runLen.c_str(), shapes, mats, texs, lights, glass,
+             // quadric scenes: the kernel is 2x the 32 KB instruction cache, one shared sqrt pays (config 3: +5..16 %); the
+             // metal/glass-only kernels are faster with it inlined (measured, tools/bench_outline.sh history)
+             (F & 1 /* SAIL_F_QUADRICS */) ? "#define SAIL_OUTLINE_SQRT 1\n" : "", minCtas,
              kind ? "sailWaveBody" : "sailMegaBody", F);
     void* prog = nullptr;
     if (g_api.createProgram(&prog, src, "sail_jit.cu", kSailJitCount, kSailJitTexts, kSailJitNames) != 0) {
@@ -190,15 +193,15 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
     std::vector<char> cubin(cs);
     g_api.cubin(prog, cubin.data());
     g_api.destroyProgram(&prog);
+    if (const char* dump = getenv("SAIL_B200_JIT_DUMP")) {  // keep the cubin for cuobjdump / nvdisasm / tools/sass_lines.py
+        std::string name = std::string(dump) + "/sail_jit_" + (kind ? "wave" : "mega") + "_F" + std::to_string(F) + "_n" + std::to_string(n) + ".cubin";
+        if (FILE* f = fopen(name.c_str(), "wb")) { fwrite(cubin.data(), 1, cubin.size(), f); fclose(f); }
+    }
     if (device < 0) {
         out->fn = nullptr;
         snprintf(out->info, sizeof(out->info), "%s%s%s (nvrtc %d.%d, %.2f s, %zu byte cubin, not loaded)", head, cats.c_str(), masks,
                  g_api.nvrtcMajor, g_api.nvrtcMinor, secs, cs);
         return 0;
-    }
-    if (const char* dump = getenv("SAIL_B200_JIT_DUMP")) {  // keep the cubin for cuobjdump / nvdisasm / tools/sass_lines.py
-        std::string name = std::string(dump) + "/sail_jit_" + (kind ? "wave" : "mega") + "_F" + std::to_string(F) + "_n" + std::to_string(n) + ".cubin";
-        if (FILE* f = fopen(name.c_str(), "wb")) { fwrite(cubin.data(), 1, cubin.size(), f); fclose(f); }
     }
     void *mod = nullptr, *fn = nullptr;
     int cr = g_api.moduleLoadData(&mod, cubin.data());
