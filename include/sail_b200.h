@@ -67,7 +67,9 @@ enum {
 enum {
     SAIL_KERNEL_MEGA = 0,       /* one thread traces a whole path */
     SAIL_KERNEL_WAVEFRONT = 1,  /* per-bounce stages over ray queues regrouped by hit object, queues in shared memory */
-    SAIL_KERNEL_AUTO = 2        /* default: wavefront for scenes with quadric shapes (and, among the ahead-of-time variants, metal/glass), megakernel otherwise */
+    SAIL_KERNEL_AUTO = 2,       /* default: chosen from the scene's content by the measured policy of DESIGN.md 4.2 */
+    SAIL_KERNEL_SERVER = 3      /* megakernel whose CTAs carry one server warp that evaluates the hits on non-box shapes of all
+                                   its path warps together (sail_server.cuh); exists only as a scene-specialised kernel */
 };
 
 enum {

@@ -39,12 +39,14 @@ struct sail_ctx {
     unsigned char* presentU8 = nullptr;
     uint64_t launches = 0;
     // scene-specialised kernels (sail_jit.cpp): resolved lazily per kernel kind, dropped when the scene changes
-    void* jitFn[2] = {nullptr, nullptr};
-    bool jitTried[2] = {false, false};
-    char jitNote[2][320];
+    void* jitFn[3] = {nullptr, nullptr, nullptr};  // kind 0 mega, 1 wavefront, 2 server
+    bool jitTried[3] = {false, false, false};
+    unsigned jitBlock[3] = {0, 0, 0};
+    int jitPathWarps[3] = {0, 0, 0};
+    char jitNote[3][320];
     char kernelInfo[400];
     char err[512];
-    sail_ctx() { err[0] = 0; kernelInfo[0] = 0; jitNote[0][0] = jitNote[1][0] = 0; }
+    sail_ctx() { err[0] = 0; kernelInfo[0] = 0; jitNote[0][0] = jitNote[1][0] = jitNote[2][0] = 0; }
 };
 
 extern "C" {
@@ -60,6 +62,16 @@ cudaError_t sail_launch_wave_g3(int F, const SailLaunch* L, dim3 grid, cudaStrea
 
 namespace {
 
+// A scene the server-warp kernel (sail_server.cuh) is meant for: cubes / Cornell boxes plus other shapes.
+bool hasBoxesAndOthers(const SailSceneBlock& b) {
+    bool box = false, other = false;
+    for (int i = 0; i < b.n; i++) {
+        const bool isBox = b.shape[i].category == SAIL_CUBE || b.shape[i].category == SAIL_CORNELLBOX;
+        box |= isBox;
+        other |= !isBox;
+    }
+    return box && other;
+}
 cudaError_t launchMega(int F, const SailLaunch& L, dim3 grid, cudaStream_t stream) {
     switch (F >> 2) {
         case 0: return sail_launch_mega_g0(F, &L, grid, stream);
@@ -129,8 +141,8 @@ int uploadBlock(sail_ctx* ctx) {
     CU(cudaMemcpyAsync(ctx->dScene, &ctx->hostScene, sizeof(SailSceneBlock), cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));  // hostScene may be rewritten by the next upload
     ctx->sceneLoaded = true;
-    ctx->jitTried[0] = ctx->jitTried[1] = false;  // the structure may have changed: look the specialised kernels up again
-    ctx->jitFn[0] = ctx->jitFn[1] = nullptr;
+    ctx->jitTried[0] = ctx->jitTried[1] = ctx->jitTried[2] = false;  // the structure may have changed: look the specialised kernels up again
+    ctx->jitFn[0] = ctx->jitFn[1] = ctx->jitFn[2] = nullptr;
     return SAIL_OK;
 }
 
@@ -228,7 +240,7 @@ int sail_configure(sail_ctx* ctx, const sail_config* cfg) {
     if (cfg->max_bounces < 0 || cfg->max_bounces > 1024) return setErr(ctx, SAIL_ERR_INVALID, "max_bounces %d out of range", cfg->max_bounces);
     if (cfg->filter_id < 0 || cfg->filter_id > SAIL_FILTER_TONEMAPPING) return setErr(ctx, SAIL_ERR_INVALID, "unknown filter id %d", cfg->filter_id);
     if (cfg->accum_mode != SAIL_ACCUM_MEAN && cfg->accum_mode != SAIL_ACCUM_SUM) return setErr(ctx, SAIL_ERR_INVALID, "unknown accum_mode %d", cfg->accum_mode);
-    if (cfg->kernel < SAIL_KERNEL_MEGA || cfg->kernel > SAIL_KERNEL_AUTO) return setErr(ctx, SAIL_ERR_INVALID, "unknown kernel %d", cfg->kernel);
+    if (cfg->kernel < SAIL_KERNEL_MEGA || cfg->kernel > SAIL_KERNEL_SERVER) return setErr(ctx, SAIL_ERR_INVALID, "unknown kernel %d", cfg->kernel);
     if (cfg->specialise < SAIL_SPECIALISE_AUTO || cfg->specialise > SAIL_SPECIALISE_REQUIRE) return setErr(ctx, SAIL_ERR_INVALID, "unknown specialise mode %d", cfg->specialise);
     ctx->cfg = *cfg;
     return SAIL_OK;
@@ -271,7 +283,7 @@ int sail_scene_features(const float* objects, int32_t n, const float* texparams,
 
 int sail_jit_compile_check(const float* objects, int32_t n, const float* texparams, int32_t tn, const float* lights, int32_t ln,
                            int32_t kernel, char* info, int32_t infolen) {
-    if (kernel != SAIL_KERNEL_MEGA && kernel != SAIL_KERNEL_WAVEFRONT) return SAIL_ERR_INVALID;
+    if (kernel != SAIL_KERNEL_MEGA && kernel != SAIL_KERNEL_WAVEFRONT && kernel != SAIL_KERNEL_SERVER) return SAIL_ERR_INVALID;
     SailSceneBlock* blk = new (std::nothrow) SailSceneBlock;
     if (!blk) return SAIL_ERR_NOMEM;
     int rc = sail_pack_scene(objects, n, texparams, tn, lights, ln, blk, info, infolen);
@@ -280,7 +292,7 @@ int sail_jit_compile_check(const float* objects, int32_t n, const float* texpara
         char why[400];
         why[0] = 0;
         const int F = blk->features & SAIL_F_ALL;
-        if (sail_jit_get(-1, kernel == SAIL_KERNEL_WAVEFRONT ? 1 : 0, F, SAIL_MIN_CTAS(F), blk, &k, why, sizeof(why)) == 0) {
+        if (sail_jit_get(-1, kernel == SAIL_KERNEL_SERVER ? 2 : (kernel == SAIL_KERNEL_WAVEFRONT ? 1 : 0), F, SAIL_MIN_CTAS(F), blk, &k, why, sizeof(why)) == 0) {
             if (info && infolen > 0) snprintf(info, (size_t)infolen, "%s", k.info);
         } else {
             if (info && infolen > 0) snprintf(info, (size_t)infolen, "%s", why);
@@ -348,28 +360,46 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
     // (quadrics); among the ahead-of-time variants also where it has many BSDFs (metal / glass).
     const bool tryJit = ctx->cfg.specialise != SAIL_SPECIALISE_OFF;
     bool wave = ctx->cfg.kernel == SAIL_KERNEL_WAVEFRONT;
+    bool server = ctx->cfg.kernel == SAIL_KERNEL_SERVER;
+    if (server && !tryJit) return setErr(ctx, SAIL_ERR_STATE, "SAIL_KERNEL_SERVER exists only as a scene-specialised kernel (specialise = off)");
     if (ctx->cfg.kernel == SAIL_KERNEL_AUTO) {
         wave = (F & SAIL_F_QUADRICS) != 0;
+        // The server-warp kernel is never chosen automatically: measured slower than the plain megakernel on the scene it
+        // was built for (Cornell box 9.3 vs 11.0 Gpaths/s); SAIL_B200_AUTO_SERVER=1 turns it on for A/B runs.
+        static const bool autoServer = getenv("SAIL_B200_AUTO_SERVER") && getenv("SAIL_B200_AUTO_SERVER")[0] == '1';
+        server = autoServer && tryJit && F == 0 && hasBoxesAndOthers(ctx->hostScene) && !(ctx->jitTried[2] && !ctx->jitFn[2]);
+        if (server) wave = false;
         const bool jitFailed = tryJit && ctx->jitTried[wave ? 1 : 0] && !ctx->jitFn[wave ? 1 : 0];
-        if (!tryJit || jitFailed) wave = (F & (SAIL_F_QUADRICS | SAIL_F_GLOSSY)) != 0;
+        if (!server && (!tryJit || jitFailed)) wave = (F & (SAIL_F_QUADRICS | SAIL_F_GLOSSY)) != 0;
     }
-    int kind = wave ? 1 : 0;
+    int kind = server ? 2 : (wave ? 1 : 0);
     void* jit = nullptr;
     if (tryJit) {
-        if (!ctx->jitTried[kind]) {
-            ctx->jitTried[kind] = true;
-            SailJitKernel k;
-            char why[300];
-            why[0] = 0;
-            if (sail_jit_get(ctx->device, kind, F, SAIL_MIN_CTAS(F), &ctx->hostScene, &k, why, sizeof(why)) == 0) {
-                ctx->jitFn[kind] = k.fn;
-                snprintf(ctx->jitNote[kind], sizeof(ctx->jitNote[kind]), "%s", k.info);
-            } else {
-                ctx->jitFn[kind] = nullptr;
-                snprintf(ctx->jitNote[kind], sizeof(ctx->jitNote[kind]), "aot %s<F=%d> (jit: %s)", wave ? "wavefront" : "mega", F, why);
+        for (int attempt = 0; attempt < 2 && !jit; attempt++) {
+            if (!ctx->jitTried[kind]) {
+                ctx->jitTried[kind] = true;
+                SailJitKernel k;
+                char why[300];
+                why[0] = 0;
+                if (sail_jit_get(ctx->device, kind, F, SAIL_MIN_CTAS(F), &ctx->hostScene, &k, why, sizeof(why)) == 0) {
+                    ctx->jitFn[kind] = k.fn;
+                    ctx->jitBlock[kind] = k.block;
+                    ctx->jitPathWarps[kind] = k.pathWarps;
+                    snprintf(ctx->jitNote[kind], sizeof(ctx->jitNote[kind]), "%s", k.info);
+                } else {
+                    ctx->jitFn[kind] = nullptr;
+                    snprintf(ctx->jitNote[kind], sizeof(ctx->jitNote[kind]), "aot %s<F=%d> (jit: %s)", kind == 2 ? "mega" : (wave ? "wavefront" : "mega"), F, why);
+                }
             }
+            jit = ctx->jitFn[kind];
+            if (!jit && kind == 2 && ctx->cfg.kernel == SAIL_KERNEL_AUTO) {  // no server kernel: the plain megakernel
+                server = false;
+                kind = 0;
+                continue;
+            }
+            break;
         }
-        jit = ctx->jitFn[kind];
+        if (!jit && kind == 2) return setErr(ctx, SAIL_ERR_STATE, "server kernel unavailable: %s", ctx->jitNote[2]);
         if (!jit && ctx->cfg.kernel == SAIL_KERNEL_AUTO && (F & SAIL_F_GLOSSY) && !wave) {  // first failure: re-decide for the AOT variants
             wave = true;
             kind = 1;
@@ -384,7 +414,13 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
     }
     if (jit) {
         char why[200];
-        if (sail_jit_launch(jit, &L, grid.x, grid.y, SAIL_CTA_THREADS, L.sceneSmem, ctx->stream, why, sizeof(why)) != 0)
+        unsigned gx = grid.x, gy = grid.y;
+        if (kind == 2) {  // strips of pathWarps 8x4 sub-tiles, one row group of 4 rows per grid.y
+            const unsigned subW = (unsigned)(ctx->W + 7) / 8u, pw = (unsigned)ctx->jitPathWarps[2];
+            gx = (subW + pw - 1) / pw;
+            gy = (unsigned)tileRows * (SAIL_TILE_H / 4);
+        }
+        if (sail_jit_launch(jit, &L, gx, gy, ctx->jitBlock[kind], L.sceneSmem, ctx->stream, why, sizeof(why)) != 0)
             return setErr(ctx, SAIL_ERR_CUDA, "%s", why);
     } else if (wave) CU(launchWave(F, L, grid, ctx->stream));
     else CU(launchMega(F, L, grid, ctx->stream));

@@ -134,11 +134,13 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
     }
     if (nruns > SAIL_JIT_MAX_RUNS) { setErr(err, errlen, "more than 16 runs of distinct shapes"); return 2; }
     // which plugins the scene contains (category ids as bit positions; ids outside 0..31 select no arm anyway)
-    unsigned shapes = 0, mats = 0, texs = 0, lights = 0, glass = 0;
+    unsigned shapes = 0, mats = 0, texs = 0, lights = 0, glass = 0, matsBox = 0, matsOff = 0;
     auto bit = [](int c) { return (c >= 0 && c < 32) ? (1u << c) : 0u; };
     for (int i = 0; i < n; i++) {
         shapes |= bit(scene->shape[i].category);
         mats |= bit(scene->shape[i].matCategory) | bit(scene->surf[i].matCategory);
+        const bool box = scene->shape[i].category == SAIL_CUBE || scene->shape[i].category == SAIL_CORNELLBOX;
+        (box ? matsBox : matsOff) |= bit(scene->shape[i].matCategory) | bit(scene->surf[i].matCategory);
         texs |= bit(scene->surf[i].texCategory);
         if (scene->shape[i].matCategory == SAIL_GLASS || scene->surf[i].matCategory == SAIL_GLASS) {
             const float ur = scene->surf[i].m[SM_GLASS_UR], vr = scene->surf[i].m[SM_GLASS_VR];
@@ -148,28 +150,59 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
     for (int k = 0; scene->ln > 0 && k <= scene->ln; k++) lights |= bit(scene->light[k].category);
     char masks[96];
     snprintf(masks, sizeof(masks), " plugins=%x/%x/%x/%x/%x", shapes, mats, texs, lights, glass);
+    // kind 2 (sail_server.cuh): path warps per CTA next to the one server warp; 64 registers per thread fill the SM
+    int pathWarps = 0;
+    unsigned block = SAIL_JIT_CTA_THREADS;
+    if (kind == 2) {
+        pathWarps = 7;
+        if (const char* e = getenv("SAIL_B200_SRV_WARPS")) pathWarps = atoi(e);
+        if (pathWarps < 1 || pathWarps > 31) { setErr(err, errlen, "SAIL_B200_SRV_WARPS must be 1..31"); return 2; }
+        block = (unsigned)(pathWarps + 1) * 32u;
+        minCtas = (int)(65536u / (64u * block));
+        if (minCtas < 1) minCtas = 1;
+    }
+    const char* kindName = kind == 2 ? "server" : (kind ? "wavefront" : "mega");
     char head[96];
-    snprintf(head, sizeof(head), "jit %s<F=%d> n=%d shapes=", kind ? "wavefront" : "mega", F, n);
-    const std::string key = "dev" + std::to_string(device) + " m" + std::to_string(minCtas) + " " + head + cats + masks;
+    if (kind == 2) snprintf(head, sizeof(head), "jit server<F=%d,%d+1 warps> n=%d shapes=", F, pathWarps, n);
+    else snprintf(head, sizeof(head), "jit %s<F=%d> n=%d shapes=", kindName, F, n);
+    // SAIL_B200_JIT_DEFINES="NAME=VALUE,NAME2=VALUE2": extra #defines for A/B runs of experimental code paths
+    std::string extraDefs;
+    if (const char* e = getenv("SAIL_B200_JIT_DEFINES")) {
+        std::string cur;
+        for (const char* p = e;; p++) {
+            if (*p == ',' || *p == 0) {
+                if (!cur.empty()) {
+                    const size_t eq = cur.find('=');
+                    extraDefs += "#define " + (eq == std::string::npos ? cur + " 1" : cur.substr(0, eq) + " " + cur.substr(eq + 1)) + "\n";
+                }
+                cur.clear();
+                if (*p == 0) break;
+            } else cur += *p;
+        }
+    }
+    const std::string key = extraDefs + "dev" + std::to_string(device) + " m" + std::to_string(minCtas) + " " + head + cats + masks;
     auto it = g_cache.find(key);
+    out->block = block;
+    out->pathWarps = pathWarps;
     if (it != g_cache.end()) {
         out->fn = it->second;
         snprintf(out->info, sizeof(out->info), "%s%s%s (cached)", head, cats.c_str(), masks);
         return 0;
     }
-    char src[2048];
+    char src[4096];
     snprintf(src, sizeof(src),
-             "#define SAIL_JIT_NRUNS %d\n#define SAIL_JIT_RUN_CATS %s\n#define SAIL_JIT_RUN_STARTS %s\n#define SAIL_JIT_RUN_LENS %s\n"
+             "%s#define SAIL_JIT_NRUNS %d\n#define SAIL_JIT_RUN_CATS %s\n#define SAIL_JIT_RUN_STARTS %s\n#define SAIL_JIT_RUN_LENS %s\n"
              "#define SAIL_JIT_SHAPES 0x%xu\n#define SAIL_JIT_MATS 0x%xu\n#define SAIL_JIT_TEXS 0x%xu\n#define SAIL_JIT_LIGHTS 0x%xu\n"
-             "#define SAIL_JIT_GLASS %u\n%s"
-             "#include \"sail_mega.cuh\"\n#include \"sail_wavefront.cuh\"\n"
-             "extern \"C\" __global__ void __launch_bounds__(SAIL_CTA_THREADS, %d) sail_jit_kernel(const __grid_constant__ SailLaunch L) "
+             "#define SAIL_JIT_GLASS %u\n#define SAIL_JIT_MATS_BOX 0x%xu\n#define SAIL_JIT_MATS_OFF 0x%xu\n#define SAIL_SRV_PATH_WARPS %d\n%s"
+             "#include \"sail_mega.cuh\"\n#include \"sail_wavefront.cuh\"\n#include \"sail_server.cuh\"\n"
+             "extern \"C\" __global__ void __launch_bounds__(%u, %d) sail_jit_kernel(const __grid_constant__ SailLaunch L) "
              "{ %s<%d>(L); }\n",
-             nruns, runCat.c_str(), runStart.c_str(), runLen.c_str(), shapes, mats, texs, lights, glass,
+             extraDefs.c_str(), nruns, runCat.c_str(), runStart.c_str(), runLen.c_str(), shapes, mats, texs, lights, glass, matsBox, matsOff,
+             pathWarps ? pathWarps : 7,
              // quadric scenes: the kernel is 2x the 32 KB instruction cache, one shared sqrt pays (config 3: +5..16 %); the
              // metal/glass-only kernels are faster with it inlined (measured, tools/bench_outline.sh history)
-             (F & 1 /* SAIL_F_QUADRICS */) ? "#define SAIL_OUTLINE_SQRT 1\n" : "", minCtas,
-             kind ? "sailWaveBody" : "sailMegaBody", F);
+             (F & 1 /* SAIL_F_QUADRICS */) ? "#define SAIL_OUTLINE_SQRT 1\n" : "", block, minCtas,
+             kind == 2 ? "sailServerBody" : (kind ? "sailWaveBody" : "sailMegaBody"), F);
     void* prog = nullptr;
     if (g_api.createProgram(&prog, src, "sail_jit.cu", kSailJitCount, kSailJitTexts, kSailJitNames) != 0) {
         setErr(err, errlen, "nvrtcCreateProgram failed");
@@ -194,7 +227,7 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
     g_api.cubin(prog, cubin.data());
     g_api.destroyProgram(&prog);
     if (const char* dump = getenv("SAIL_B200_JIT_DUMP")) {  // keep the cubin for cuobjdump / nvdisasm / tools/sass_lines.py
-        std::string name = std::string(dump) + "/sail_jit_" + (kind ? "wave" : "mega") + "_F" + std::to_string(F) + "_n" + std::to_string(n) + ".cubin";
+        std::string name = std::string(dump) + "/sail_jit_" + (kind == 2 ? "server" : (kind ? "wave" : "mega")) + "_F" + std::to_string(F) + "_n" + std::to_string(n) + ".cubin";
         if (FILE* f = fopen(name.c_str(), "wb")) { fwrite(cubin.data(), 1, cubin.size(), f); fclose(f); }
     }
     if (device < 0) {

@@ -270,15 +270,17 @@ SD V3 orenNayar_f(V3 R, float A, float B, V3 wo, V3 wi) {
 
 // ---- material(): shader.material.js:21-29 + matte/mirror/metal/glass.glsl ---------------------------
 // Returns fpdf (unclamped); writes wi (local frame) and, for matte only, f = matte_f().
+// matMask: material categories the caller can meet (bit = category id); arms outside it are not compiled.
+#define SAIL_MAT_ARM(c) (SAIL_HAS_MAT(c) && ((matMask >> (c)) & 1u))
 template <int F>
-SD V3 material(const SailSurface& su, int matCategory, V3 sc, bool into, V2 u, V3 wo, V3& wi, V3& f) {
+SD V3 material(const SailSurface& su, int matCategory, V3 sc, bool into, V2 u, V3 wo, V3& wi, V3& f, const unsigned matMask = 0xffffffffu) {
     const float* m = su.m;
     wi = splat3(0.0f);
     f = splat3(0.0f);
     float pdf = 0.0f;
     V3 fs = splat3(0.0f);
     switch (matCategory) {
-        case SAIL_MATTE: if (SAIL_HAS_MAT(SAIL_MATTE)) {  // matte.glsl:8-37
+        case SAIL_MATTE: if (SAIL_MAT_ARM(SAIL_MATTE)) {  // matte.glsl:8-37
             V3 R = m[SM_MATTE_KD] * sc;
             wi = cosineSampleHemisphere<F>(u);
             pdf = sameHemisphere(wo, wi) ? absCosTheta(wi) * SAIL_INVPI : 0.0f;
@@ -287,13 +289,13 @@ SD V3 material(const SailSurface& su, int matCategory, V3 sc, bool into, V2 u, V
             f = fs;  // matte_f() evaluates the same expression on the same (wo, wi)
             break;
         }
-        case SAIL_MIRROR: if (SAIL_HAS_MAT(SAIL_MIRROR)) {  // mirror.glsl:5-16, bsdf.glsl:93-98 with the no-op Fresnel (= WHITE)
+        case SAIL_MIRROR: if (SAIL_MAT_ARM(SAIL_MIRROR)) {  // mirror.glsl:5-16, bsdf.glsl:93-98 with the no-op Fresnel (= WHITE)
             V3 R = m[SM_MIRROR_KR] * sc;
             wi = mk3(-wo.x, -wo.y, wo.z);
             fs = vdivs(splat3(1.0f) * R, absCosTheta(wi));
             return fs * absCosTheta(wi);  // pdf = 1: `/ pdf` multiplies by rcp(1) = 1 exactly
         }
-        case SAIL_METAL: if ((F & SAIL_F_GLOSSY) && SAIL_HAS_MAT(SAIL_METAL)) {  // metal.glsl:8-23
+        case SAIL_METAL: if ((F & SAIL_F_GLOSSY) && SAIL_MAT_ARM(SAIL_METAL)) {  // metal.glsl:8-23
             MicroR mr;
             mr.R = sc;
             mr.fresnelKind = 1;
@@ -305,7 +307,7 @@ SD V3 material(const SailSurface& su, int matCategory, V3 sc, bool into, V2 u, V
             fs = microfacet_r_sample_f(mr, u, wo, wi, pdf);
             break;
         }
-        case SAIL_GLASS: if ((F & SAIL_F_GLOSSY) && SAIL_HAS_MAT(SAIL_GLASS)) {  // glass.glsl:10-35
+        case SAIL_GLASS: if ((F & SAIL_F_GLOSSY) && SAIL_MAT_ARM(SAIL_GLASS)) {  // glass.glsl:10-35
             float kr = m[SM_GLASS_KR], kt = m[SM_GLASS_KT], eta = m[SM_GLASS_ETA];
             float ur = m[SM_GLASS_UR], vr = m[SM_GLASS_VR];
             const bool smooth = ur < SAIL_EPSILON && vr < SAIL_EPSILON;
@@ -476,12 +478,12 @@ SD V3 light_sample(const SceneView& sc, V2 u, V3 hit, V3 insNormal) {
 
 // ---- shade(), path.glsl:1-14 ----------------------------------------------------------------------------
 template <int F>
-SD V3 shade(const SceneView& sc, const Hit& h, V2 u, V3 wo, V3& wi, V3& fpdf) {
+SD V3 shade(const SceneView& sc, const Hit& h, V2 u, V3 wo, V3& wi, V3& fpdf, const unsigned matMask = 0xffffffffu) {
     V3 f;
     // box faces: |dpdu| is exactly 1 (components 0 / +-1), so normalize() multiplies by rcp(sqrt(1)) = 1
     V3 ss = h.unitDpdu ? h.dpdu : normalize3(h.dpdu), ts = cross3(h.n, ss);
     wo = worldToLocal(wo, h.n, ss, ts);
-    fpdf = vclamp01(material<F>(sc.surf[h.index], h.matCategory, h.sc, h.into, u, wo, wi, f));
+    fpdf = vclamp01(material<F>(sc.surf[h.index], h.matCategory, h.sc, h.into, u, wo, wi, f, matMask));
     wi = localToWorld(wi, h.n, ss, ts);
     V3 direct = splat3(0.0f);
     if ((F & SAIL_F_NEE) && isblack(h.emission) && h.matCategory == SAIL_MATTE) direct = direct + light_sample<F>(sc, u, h.p, h.n) * f;

@@ -57,6 +57,20 @@ def test_frames_bit_exact(capi, oracle, cfg, kernel, specialise):
         assert bits_equal(out[name], ref[name]), mismatch_report(out[name], ref[name], "cfg%d %s" % (cfg, name))
 
 
+@pytest.mark.parametrize("warps", [7, 3, 1])
+@pytest.mark.parametrize("cfg", [1, 2, 3, 5])
+def test_server_kernel_bit_exact(capi, oracle, cfg, warps, monkeypatch):
+    """The server-warp kernel (sail_server.cuh; run-time compiled only): non-box hits of all path warps of a CTA are
+    evaluated together by one server warp -- same bits as the oracle, for every CTA shape."""
+    monkeypatch.setenv("SAIL_B200_SRV_WARPS", str(warps))
+    for batch in (False, True):
+        out, ref = _render_both(capi, oracle, cfg, 4, kernel=capi.KERNEL_SERVER, batch=batch, specialise=2)
+        assert out["kernel_info"].startswith("jit server<"), out["kernel_info"]
+        assert np.array_equal(out["hit_id"], ref["hit_id"]), "primary hit ids differ"
+        for name in ("depth", "normal", "position", "color"):
+            assert bits_equal(out[name], ref[name]), mismatch_report(out[name], ref[name], "cfg%d %s" % (cfg, name))
+
+
 @pytest.mark.parametrize("cfg", [1, 2])
 def test_render_n_equals_single_calls(capi, oracle, cfg):
     a, _ = _render_both(capi, oracle, cfg, 6, batch=False)
@@ -172,7 +186,8 @@ def test_present_filters(capi, oracle, name, params):
     assert np.array_equal(g8, r8)
 
 
-def test_tile_rows_and_sum_mode(capi, oracle):
+@pytest.mark.parametrize("kernel", [2, 3], ids=["auto", "server"])
+def test_tile_rows_and_sum_mode(capi, oracle, kernel):
     """Row-sharded contexts reproduce the full frame; SUM accumulation equals the mean within rounding."""
     W, H = SIZES[2]
     scene, o, t, l, bounces = scene_tables(2, W, H)
@@ -185,13 +200,13 @@ def test_tile_rows_and_sum_mode(capi, oracle):
     got = np.zeros_like(want)
     for rows in ((0, 24), (24, 56), (56, H)):
         with capi.Context(W, H, rows=rows) as part:
-            part.configure(max_bounces=bounces)
+            part.configure(max_bounces=bounces, kernel=kernel)
             part.upload_scene(o, t, l)
             part.render_n(frames)
             got[rows[0]:rows[1]] = part.read_accum()[rows[0]:rows[1]]
     assert bits_equal(got, want)
     with capi.Context(W, H) as s:
-        s.configure(max_bounces=bounces, accum_mode=capi.ACCUM_SUM)
+        s.configure(max_bounces=bounces, accum_mode=capi.ACCUM_SUM, kernel=kernel)
         s.upload_scene(o, t, l)
         s.render_n(frames)
         s.scale_accum(1.0 / len(frames))
@@ -235,7 +250,8 @@ def test_cuda_matches_golden_fixture(capi, cfg):
         assert bits_equal(ctx.read_accum(), gold["c%d_color" % cfg])
 
 
-def test_interleaved_row_bands(capi):
+@pytest.mark.parametrize("kernel", [2, 3], ids=["auto", "server"])
+def test_interleaved_row_bands(capi, kernel):
     """sail_set_row_bands(): 3 contexts with interleaved 8-row bands reproduce the full frame bit for bit."""
     W, H = 128, 72
     scene, o, t, l, bounces = scene_tables(5, W, H)
@@ -250,7 +266,7 @@ def test_interleaved_row_bands(capi):
     bands = sharding.row_bands(H, 3, band=8)
     for r in range(3):
         with capi.Context(W, H) as part:
-            part.configure(max_bounces=bounces)
+            part.configure(max_bounces=bounces, kernel=kernel)
             part.set_row_bands(8, 3, r)
             part.upload_scene(o, t, l)
             part.render_n(frames)
