@@ -161,6 +161,12 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
         minCtas = (int)(65536u / (64u * block));
         if (minCtas < 1) minCtas = 1;
     }
+    if (kind != 2) {
+        if (const char* e = getenv("SAIL_B200_MIN_CTAS")) {  // occupancy sweeps (tools/ab_defs.sh)
+            const int v = atoi(e);
+            if (v >= 1 && v <= 16) minCtas = v;
+        }
+    }
     const char* kindName = kind == 2 ? "server" : (kind ? "wavefront" : "mega");
     char head[96];
     if (kind == 2) snprintf(head, sizeof(head), "jit server<F=%d,%d+1 warps> n=%d shapes=", F, pathWarps, n);

@@ -76,10 +76,14 @@ SD void sailServerBody(const SailLaunch& L) {
                             aov.pix = (size_t)(unsigned)__float_as_int(slot[9][src]);
                             writeAov(aov, h.n, h.p, id, t);
                         }
-                        V3 wi, _fpdf;
-                        const V3 contrib = shade<F>(sc, h, u, -ray.d, wi, _fpdf, SAIL_JIT_MATS_OFF);
-                        const float outdot = dot3(h.n, wi);
-                        const V3 o = h.p + h.n * (outdot > SAIL_EPSILON ? 0.0001f : -0.0001f);
+                        V3 wi = splat3(0.0f), _fpdf = splat3(0.0f), contrib, o = splat3(0.0f);
+                        if (deepth == L.maxBounces && lastBounceIsEmissionOnly<F>(h)) {  // see tracePath(): dead BSDF sample
+                            contrib = h.emission + splat3(0.0f);
+                        } else {
+                            contrib = shade<F>(sc, h, u, -ray.d, wi, _fpdf, SAIL_JIT_MATS_OFF);
+                            const float outdot = dot3(h.n, wi);
+                            o = h.p + h.n * (outdot > SAIL_EPSILON ? 0.0001f : -0.0001f);
+                        }
                         slot[0][src] = contrib.x; slot[1][src] = contrib.y; slot[2][src] = contrib.z;
                         slot[3][src] = _fpdf.x; slot[4][src] = _fpdf.y; slot[5][src] = _fpdf.z;
                         slot[6][src] = o.x; slot[7][src] = o.y; slot[8][src] = o.z;
@@ -131,7 +135,8 @@ SD void sailServerBody(const SailLaunch& L) {
                 }
             }
             const float seed = f.timeSinceStart + (float)deepth;
-            const V2 u = random2<F>(fx, fy, fz, seed);
+            const bool lastNoNee = deepth == L.maxBounces && !(F & SAIL_F_NEE);  // warp-uniform: nobody needs the RNG pair
+            const V2 u = lastNoNee ? mk2(0.0f, 0.0f) : random2<F>(fx, fy, fz, seed);
             const bool off = alive && srvOffloaded(sc.shape[alive ? nr.id : 0].category);
             const unsigned m = __ballot_sync(0xffffffffu, off);
             if (m) {
@@ -156,12 +161,16 @@ SD void sailServerBody(const SailLaunch& L) {
                 Hit h;
                 hitRecord<F, 1>(sc, nr.id, nr.t, ray, h);
                 if (deepth == 1 && aov.on) writeAov(aov, h.n, h.p, h.index, h.d);
-                V3 wi, _fpdf;
-                e = e + shade<F>(sc, h, u, -ray.d, wi, _fpdf, SAIL_JIT_MATS_BOX) * fpdf;
-                fpdf = fpdf * _fpdf;
-                const float outdot = dot3(h.n, wi);
-                ray.o = h.p + h.n * (outdot > SAIL_EPSILON ? 0.0001f : -0.0001f);
-                ray.d = wi;
+                if (deepth == L.maxBounces && lastBounceIsEmissionOnly<F>(h)) {
+                    e = e + (h.emission + splat3(0.0f)) * fpdf;
+                } else {
+                    V3 wi, _fpdf;
+                    e = e + shade<F>(sc, h, u, -ray.d, wi, _fpdf, SAIL_JIT_MATS_BOX) * fpdf;
+                    fpdf = fpdf * _fpdf;
+                    const float outdot = dot3(h.n, wi);
+                    ray.o = h.p + h.n * (outdot > SAIL_EPSILON ? 0.0001f : -0.0001f);
+                    ray.d = wi;
+                }
             }
             __syncwarp();
             srvSync(2);

@@ -511,6 +511,13 @@ SD void writeAov(const AovSink& a, V3 n, V3 p, int id, float t) {
     a.depth[a.pix] = t;
 }
 
+// True when shade() of this hit reduces to `emission + BLACK` (path.glsl:10: NEE only for non-emissive matte hits).
+template <int F>
+SD bool lastBounceIsEmissionOnly(const Hit& h) {
+    if (!(F & SAIL_F_NEE)) return true;
+    return !(isblack(h.emission) && h.matCategory == SAIL_MATTE);
+}
+
 // ---- trace(), path.glsl:16-38 -----------------------------------------------------------------------------
 // fx, fy, fz = gl_FragCoord.xyz.  Returns the radiance sample e.
 template <int F>
@@ -527,10 +534,20 @@ SD V3 tracePath(const SceneView& sc, Ray ray, int maxBounces, float fx, float fy
             break;
         }
         if (deepth == 1 && aov.on) writeAov(aov, h.n, h.p, h.index, h.d);
+        // The last bounce only contributes `shade() * fpdf` (path.glsl:27): the sampled direction, the BSDF weight and the
+        // respawned ray it also produces are never read again.  shade() = emission + direct, and direct is non-zero only
+        // for non-emissive matte hits with lights present (path.glsl:10), so everywhere else the RNG pair, the shading
+        // frame and the BSDF sample are dead code on this bounce and are not evaluated; what is added to `e` is the same
+        // expression, `(emission + 0) * fpdf`.
+        if (deepth == maxBounces && lastBounceIsEmissionOnly<F>(h)) {
+            e = e + (h.emission + splat3(0.0f)) * fpdf;
+            break;
+        }
         float seed = timeSinceStart + (float)deepth;
         V2 u = random2<F>(fx, fy, fz, seed);
         V3 wi, _fpdf;
         e = e + shade<F>(sc, h, u, -ray.d, wi, _fpdf) * fpdf;
+        if (deepth == maxBounces) break;
         fpdf = fpdf * _fpdf;
         float outdot = dot3(h.n, wi);
         ray.o = h.p + h.n * (outdot > SAIL_EPSILON ? 0.0001f : -0.0001f);

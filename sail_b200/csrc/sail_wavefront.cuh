@@ -109,14 +109,18 @@ SD void sailWaveBody(const SailLaunch& L) {
                     firstHit[0][home] = h.n.x; firstHit[1][home] = h.n.y; firstHit[2][home] = h.n.z;
                     firstHit[3][home] = h.p.x; firstHit[4][home] = h.p.y; firstHit[5][home] = h.p.z;
                 }
-                const float seed = f.timeSinceStart + (float)deepth;
-                V2 u = random2<F>(fx, fy, 0.5f, seed);
-                V3 wi, _fpdf;
-                e = e + shade<F>(sc, h, u, -ray.d, wi, _fpdf) * fpdf;
-                fpdf = fpdf * _fpdf;
-                const float outdot = dot3(h.n, wi);
-                ray.o = h.p + h.n * (outdot > SAIL_EPSILON ? 0.0001f : -0.0001f);
-                ray.d = wi;
+                if (deepth == L.maxBounces && lastBounceIsEmissionOnly<F>(h)) {  // see tracePath(): dead BSDF sample
+                    e = e + (h.emission + splat3(0.0f)) * fpdf;
+                } else {
+                    const float seed = f.timeSinceStart + (float)deepth;
+                    V2 u = random2<F>(fx, fy, 0.5f, seed);
+                    V3 wi, _fpdf;
+                    e = e + shade<F>(sc, h, u, -ray.d, wi, _fpdf) * fpdf;
+                    fpdf = fpdf * _fpdf;
+                    const float outdot = dot3(h.n, wi);
+                    ray.o = h.p + h.n * (outdot > SAIL_EPSILON ? 0.0001f : -0.0001f);
+                    ray.d = wi;
+                }
             }
         }
         // ---- return the sample to its home lane ----
