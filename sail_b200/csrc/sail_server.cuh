@@ -133,6 +133,8 @@ SD void sailServerBody(const SailLaunch& L) {
                     if (deepth == 1 && aov.on) writeAov(aov, splat3(0.0f), splat3(0.0f), nr.id, nr.t);
                     alive = false;
                 }
+                // last bounce on an object that neither emits nor gets NEE: adds +0 to e (see tracePath())
+                if (alive && deepth == L.maxBounces && !(deepth == 1 && aov.on) && !lastBounceNeedsRecord<F>(sc.shape[nr.id])) alive = false;
             }
             const float seed = f.timeSinceStart + (float)deepth;
             const bool lastNoNee = deepth == L.maxBounces && !(F & SAIL_F_NEE);  // warp-uniform: nobody needs the RNG pair

@@ -518,6 +518,13 @@ SD bool lastBounceIsEmissionOnly(const Hit& h) {
     return !(isblack(h.emission) && h.matCategory == SAIL_MATTE);
 }
 
+// False when a last-bounce hit on this object cannot change the radiance sample: it emits nothing and gets no NEE.
+template <int F>
+SD bool lastBounceNeedsRecord(const SailShape& s) {
+    if (!isblack(ld3(s.emission))) return true;
+    return (F & SAIL_F_NEE) && s.matCategory == SAIL_MATTE;
+}
+
 // ---- trace(), path.glsl:16-38 -----------------------------------------------------------------------------
 // fx, fy, fz = gl_FragCoord.xyz.  Returns the radiance sample e.
 template <int F>
@@ -527,12 +534,16 @@ SD V3 tracePath(const SceneView& sc, Ray ray, int maxBounces, float fx, float fy
     int deepth = 0;
     if (aov.on && maxBounces < 1) writeAov(aov, splat3(0.0f), splat3(0.0f), -1, SAIL_MAX_DISTANCE);
     while (deepth++ < maxBounces) {
-        Hit h;
-        bool ok = intersectObjects<F>(sc, ray, h);
-        if (!ok) {
-            if (deepth == 1 && aov.on) writeAov(aov, splat3(0.0f), splat3(0.0f), h.index, h.d);
+        const Nearest nr = nearestObject<F>(sc, ray);
+        if (nr.id < 0) {
+            if (deepth == 1 && aov.on) writeAov(aov, splat3(0.0f), splat3(0.0f), nr.id, nr.t);
             break;
         }
+        // Last bounce, object without emission (and no NEE for it): the hit adds (BLACK + BLACK) * fpdf = +0 to `e`
+        // (fpdf is a product of values clamped to [0, 1]; `e` is never -0), so not even its hit record is needed.
+        if (deepth == maxBounces && !(deepth == 1 && aov.on) && !lastBounceNeedsRecord<F>(sc.shape[nr.id])) break;
+        Hit h;
+        hitRecord<F>(sc, nr.id, nr.t, ray, h);
         if (deepth == 1 && aov.on) writeAov(aov, h.n, h.p, h.index, h.d);
         // The last bounce only contributes `shade() * fpdf` (path.glsl:27): the sampled direction, the BSDF weight and the
         // respawned ray it also produces are never read again.  shade() = emission + direct, and direct is non-zero only

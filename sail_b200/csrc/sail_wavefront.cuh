@@ -68,6 +68,8 @@ SD void sailWaveBody(const SailLaunch& L) {
             if (alive) nr = nearestObject<F>(sc, ray);
             if (deepth == 1) { firstId = nr.id; firstT = nr.t; }  // still on the home lane
             if (nr.id < 0) alive = false;                          // path.glsl:22 `break`
+            // last bounce on an object that neither emits nor gets NEE: adds +0 to e (see tracePath()), the path is done
+            if (alive && deepth == L.maxBounces && deepth > 1 && !lastBounceNeedsRecord<F>(sc.shape[nr.id])) alive = false;
             float t = nr.t;
             int id = alive ? nr.id : -1;
             // Primary rays of a tile are coherent already; regroup from the second bounce on.
