@@ -258,6 +258,12 @@ int sail_pack_scene(const float* objects, int n, const float* texparams, int tn,
         if (tc == SAIL_CHECKERBOARD || tc == SAIL_CHECKERBOARD2 || tc == SAIL_BILERP || tc == SAIL_UVF) feat |= SAIL_FEAT_TEXTURED;
     }
     out->features = feat;
+    unsigned em = 0;
+    for (int i = 0; i < n && i < 32; i++) {
+        const float* e = out->shape[i].emission;
+        if (!(e[0] == 0.0f && e[1] == 0.0f && e[2] == 0.0f)) em |= 1u << i;  // NaN counts as emissive
+    }
+    out->emissiveMask = em;
 
     // ---- lights: one resolved entry per drawable index (shader.light.js:12-22) ----
     for (int index = 0; ln > 0 && index <= ln; index++) {

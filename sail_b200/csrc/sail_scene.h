@@ -90,7 +90,7 @@ struct __attribute__((aligned(16))) SailLight {
 struct __attribute__((aligned(16))) SailSceneBlock {
     int n, ln;      // object count, light count (uniforms n, ln; src/core/shader.js:41-43)
     int features;   // SAIL_F_* bits the scene content needs (kernel variant selection)
-    int pad1;
+    unsigned emissiveMask;  // bit i: object i (i < 32) has a non-zero emission; objects >= 32 count as emissive
     SailShape shape[SAIL_MAX_OBJECTS];
     SailSurface surf[SAIL_MAX_OBJECTS];
     SailLight light[SAIL_MAX_LIGHTS + 1];

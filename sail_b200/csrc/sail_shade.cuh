@@ -534,6 +534,9 @@ SD V3 tracePath(const SceneView& sc, Ray ray, int maxBounces, float fx, float fy
     int deepth = 0;
     if (aov.on && maxBounces < 1) writeAov(aov, splat3(0.0f), splat3(0.0f), -1, SAIL_MAX_DISTANCE);
     while (deepth++ < maxBounces) {
+        // Last bounce without NEE: only a hit on an emissive object adds anything (below).  If the ray does not even
+        // touch one, the nearest-hit scan over the other objects is dead code as well.
+        if (!(F & SAIL_F_NEE) && deepth == maxBounces && !(deepth == 1 && aov.on) && !touchesMasked<F>(sc, ray, sc.emissive)) break;
         const Nearest nr = nearestObject<F>(sc, ray);
         if (nr.id < 0) {
             if (deepth == 1 && aov.on) writeAov(aov, splat3(0.0f), splat3(0.0f), nr.id, nr.t);

@@ -39,12 +39,14 @@ struct SceneView {
     const SailSurface* surf;
     const SailLight* light;
     int n, ln;
+    unsigned emissive;  // SailSceneBlock::emissiveMask
 };
 SD SceneView sceneViewAt(const unsigned char* base) {
     SceneView v;
     const int* hdr = reinterpret_cast<const int*>(base);
     v.n = hdr[0];
     v.ln = hdr[1];
+    v.emissive = (unsigned)hdr[3];
     v.shape = reinterpret_cast<const SailShape*>(base + 16);
     v.surf = reinterpret_cast<const SailSurface*>(base + 16 + (size_t)v.n * sizeof(SailShape));
     v.light = reinterpret_cast<const SailLight*>(base + 16 + (size_t)v.n * (sizeof(SailShape) + sizeof(SailSurface)));
@@ -320,6 +322,35 @@ SD Nearest nearestObjectInline(const SceneView& sc, const Ray& ray) {
     }
 #endif
     return r;
+}
+// Does the ray reach the surface of ANY object selected by `mask` (bit = object index; objects >= 32 always count)?
+// Used on the last bounce of kernels without NEE, where only a hit on an emissive object can change the sample
+// (sail_shade.cuh tracePath): when no selected object is touched at all, the nearest hit -- whatever it is -- adds
+// nothing, and the scan of the other objects is skipped.  Same distance code as the scan, so no hit is ever missed.
+template <int F>
+SD bool touchesMasked(const SceneView& sc, const Ray& ray, unsigned mask) {
+    V3 rd = rcp3(ray.d);
+    bool any = false;
+#ifdef SAIL_JIT_NRUNS
+    constexpr int kRunCat[SAIL_JIT_NRUNS] = {SAIL_JIT_RUN_CATS};
+    constexpr int kRunStart[SAIL_JIT_NRUNS] = {SAIL_JIT_RUN_STARTS};
+    constexpr int kRunLen[SAIL_JIT_NRUNS] = {SAIL_JIT_RUN_LENS};
+#pragma unroll
+    for (int k = 0; k < SAIL_JIT_NRUNS; k++) {
+#pragma unroll 1
+        for (int i = kRunStart[k]; i < kRunStart[k] + kRunLen[k]; i++) {
+            if (i < 32 && !((mask >> i) & 1u)) continue;
+            any |= shapeDistance<F>(sc.shape[i], ray, rd, kRunCat[k]) < SAIL_MAX_DISTANCE;
+        }
+    }
+#else
+    const int n = sc.n;
+    for (int i = 0; i < n; i++) {
+        if (i < 32 && !((mask >> i) & 1u)) continue;
+        any |= shapeDistance<F>(sc.shape[i], ray, rd) < SAIL_MAX_DISTANCE;
+    }
+#endif
+    return any;
 }
 template <int F>
 static __device__ __noinline__ Nearest nearestObjectRegs(unsigned scAddr, float ox, float oy, float oz, float dx, float dy, float dz) {
