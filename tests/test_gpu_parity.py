@@ -71,6 +71,66 @@ def test_server_kernel_bit_exact(capi, oracle, cfg, warps, monkeypatch):
             assert bits_equal(out[name], ref[name]), mismatch_report(out[name], ref[name], "cfg%d %s" % (cfg, name))
 
 
+def _render_tables(capi, oracle, o, t, l, scene, W, H, nframes, bounces, kernel, specialise=0):
+    oracle.set_scene(o, t, l)
+    acc = np.zeros((H, W, 3), np.float32)
+    frames, ref = [], None
+    for k in range(nframes):
+        m, eye, w, tm = frame_uniforms(scene, k, W, H)
+        ref = oracle.render_frame(W, H, m, eye, w, tm, acc, max_bounces=bounces, aovs=True)
+        frames.append(capi.make_frame(m, eye, w, tm))
+    with capi.Context(W, H) as ctx:
+        ctx.configure(max_bounces=bounces, kernel=kernel, specialise=specialise)
+        ctx.upload_scene(o, t, l)
+        ctx.render_n(frames)
+        out = {"color": ctx.read_accum(), "normal": ctx.read_aov(capi.AOV_NORMAL), "position": ctx.read_aov(capi.AOV_POSITION),
+               "hit_id": ctx.read_aov(capi.AOV_HIT_ID), "depth": ctx.read_aov(capi.AOV_DEPTH)}
+    ref["color"] = acc
+    return out, ref
+
+
+def _assert_same(out, ref, what):
+    assert np.array_equal(out["hit_id"], ref["hit_id"]), what + ": primary hit ids differ"
+    for name in ("depth", "normal", "position", "color"):
+        assert bits_equal(out[name], ref[name]), mismatch_report(out[name], ref[name], "%s %s" % (what, name))
+
+
+@pytest.mark.parametrize("kernel", [0, 1, 3], ids=["mega", "wavefront", "server"])
+@pytest.mark.parametrize("bounces", [1, 2, 3])
+@pytest.mark.parametrize("cfg", [1, 2])
+def test_short_paths_bit_exact(capi, oracle, cfg, bounces, kernel):
+    """The last bounce evaluates only what reaches the image (no BSDF sample, no hit record for objects that neither
+    emit nor get NEE, no scan when no emissive object is touched -- sail_shade.cuh tracePath): with 1..3 bounces the
+    last bounce is also the first / second / third one, AOVs included."""
+    W, H = SIZES[cfg]
+    scene, o, t, l, _ = scene_tables(cfg, W, H)
+    out, ref = _render_tables(capi, oracle, o, t, l, scene, W, H, 3, bounces, kernel)
+    _assert_same(out, ref, "cfg%d bounces=%d" % (cfg, bounces))
+
+
+@pytest.mark.parametrize("kernel", [0, 1, 3], ids=["mega", "wavefront", "server"])
+def test_emissive_mask_edge_cases(capi, oracle, kernel):
+    """Emission that is negative, NaN-free but signed-zero, on a sphere and on objects past index 31 (the emissive
+    mask of the scene header covers 32 objects; later ones always count as emissive)."""
+    import sail_b200 as Sail
+    from sail_b200 import wire
+    W, H = 64, 48
+    scene, _, _, _, _ = scene_tables(1, W, H)
+    s2 = Sail.Scene()
+    s2.add(Sail.Cornellbox([0, 0, -7], [5.560, 5.488, 5.592]))
+    s2.add(Sail.Sphere([2, 1.25, 2.70], 1.2, Sail.Matte(0.7), Sail.UniformColor([1, 1, 1]), [0.0, -0.0, 0.0]))     # signed zero: not emissive
+    s2.add(Sail.Sphere([4.2, 0.8, 1.5], 0.8, Sail.Matte(0.7), Sail.UniformColor([0.8, 0.8, 0.2]), [3, -2, 0.5]))  # negative component
+    for i in range(34):  # objects 3..36: small cubes, the last two emissive (indices 35, 36 >= 32)
+        x, y = 0.3 + 0.15 * i, 0.2 + 0.1 * (i % 5)
+        em = [5, 5, 5] if i >= 32 else [0, 0, 0]
+        s2.add(Sail.Cube([x, y, 0.5], [x + 0.1, y + 0.1, 0.6], Sail.Matte(0.7), Sail.UniformColor([0.5, 0.5, 0.5]), em))
+    s2.add(scene.camera)
+    o, t, l = wire.serialize_scene(s2)
+    for bounces in (1, 4):
+        out, ref = _render_tables(capi, oracle, o, t, l, s2, W, H, 3, bounces, kernel)
+        _assert_same(out, ref, "emissive edge cases, bounces=%d" % bounces)
+
+
 @pytest.mark.parametrize("cfg", [1, 2])
 def test_render_n_equals_single_calls(capi, oracle, cfg):
     a, _ = _render_both(capi, oracle, cfg, 6, batch=False)
