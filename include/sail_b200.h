@@ -114,7 +114,7 @@ typedef struct sail_frame {
     float matrix[16];     /* uniform mat4 matrix, column-major, already inverted and jittered on the host */
     float eye[3];         /* uniform vec3 eye */
     float textureWeight;  /* sampleCount / (sampleCount + 1) */
-    float timeSinceStart; /* seconds; seeds the per-pixel hash RNG (src/shader/trace/path.glsl:21) */
+    float timeSinceStart; /* seconds since the renderer started, >= 0 (SAIL_ERR_INVALID otherwise); seeds the per-pixel hash RNG (src/shader/trace/path.glsl:21) */
 } sail_frame;
 
 const char* sail_version(void);

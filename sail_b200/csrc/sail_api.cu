@@ -351,6 +351,10 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
     L.accum = ctx->accum; L.normal = ctx->normal; L.position = ctx->position; L.hitId = ctx->hitId; L.depth = ctx->depth;
     L.scene = ctx->dScene;
     L.sceneSmem = (unsigned)sailSceneSmemBytes(ctx->hostScene.n, ctx->hostScene.ln);
+    // timeSinceStart is seconds since the renderer started (tracer.js:98): never negative.  The cosine sampler relies on
+    // seed = timeSinceStart + bounce >= 1 (sail_shade.cuh cosineSampleHemisphere).
+    for (int k = 0; k < count; k++)
+        if (!(frames[k].timeSinceStart >= 0.0f)) return setErr(ctx, SAIL_ERR_INVALID, "frame %d: timeSinceStart must be >= 0", k);
     for (int k = 0; k < count; k++) lowerFrame(frames[k], L.frames[k]);
     CU(cudaEventRecord(ctx->evStart, ctx->stream));
     // the variant follows the scene's content, never the caller's mask hints
@@ -555,6 +559,7 @@ int sail_trace_dump(sail_ctx* ctx, const sail_frame* frame, int32_t* hit_id, flo
     L.rcpW = dm_rcp((float)ctx->W); L.rcpH = dm_rcp((float)ctx->H);
     L.scene = ctx->dScene;
     L.hitId = nullptr; L.t = nullptr; L.rays = nullptr; L.radiance = nullptr;
+    if (!(frame->timeSinceStart >= 0.0f)) return setErr(ctx, SAIL_ERR_INVALID, "timeSinceStart must be >= 0");
     lowerFrame(*frame, L.frame);
     if (hit_id) CU(cudaMalloc(&L.hitId, n * B * sizeof(int)));
     if (t) CU(cudaMalloc(&L.t, n * B * sizeof(float)));
@@ -602,6 +607,7 @@ int sail_selftest_math(sail_ctx* ctx, uint64_t* mismatches) {
     CU(cudaMalloc(&d, sizeof(unsigned long long)));
     CU(cudaMemsetAsync(d, 0, sizeof(unsigned long long), ctx->stream));
     sail_selftest_rcp_kernel<<<(1u << 20) / 256, 256, 0, ctx->stream>>>(d);
+    sail_selftest_unit_kernel<<<(1u << 19) / 256, 256, 0, ctx->stream>>>(d);
     ctx->launches++;
     CU(cudaGetLastError());
     unsigned long long h = 0;

@@ -121,6 +121,32 @@ __global__ void sail_selftest_rcp_kernel(unsigned long long* mismatches) {
     if (bad) atomicAdd(mismatches, (unsigned long long)bad);
 }
 
+// Exhaustive check of the domain-restricted helpers of the cosine sampler: sqrtUnit against sqrt.rn for x = 0 and every
+// float in [2^-100, FLT_MAX] (plus NaN -> NaN), sincosUnit against dm_sincos for every float in [0, 8] and its negative.
+// One thread per 2^12 consecutive positive bit patterns.
+__global__ void sail_selftest_unit_kernel(unsigned long long* mismatches) {
+    unsigned base = (blockIdx.x * blockDim.x + threadIdx.x) << 12;
+    unsigned bad = 0;
+    for (unsigned k = 0; k < 4096; k++) {
+        const unsigned u = base + k;
+        const float a = __uint_as_float(u);
+        if (u == 0u || (u >= 0x0d800000u && u <= 0x7f7fffffu) || u > 0x7f800000u) {
+            const float got = sqrtUnit(a), want = __fsqrt_rn(a);
+            bad += ((got != got && want != want) || __float_as_uint(got) == __float_as_uint(want)) ? 0u : 1u;
+        }
+        if (u <= 0x41000000u) {  // [0, 8]
+            for (int sgn = 0; sgn < 2; sgn++) {
+                const float x = sgn ? -a : a;
+                float s, c;
+                dm_sincos(x, &s, &c);
+                const float2 g = sincosUnit(x);
+                bad += (__float_as_uint(g.x) == __float_as_uint(s) && __float_as_uint(g.y) == __float_as_uint(c)) ? 0u : 1u;
+            }
+        }
+    }
+    if (bad) atomicAdd(mismatches, (unsigned long long)bad);
+}
+
 __global__ void sail_scale_kernel(float* p, size_t count, float s) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < count) p[i] = p[i] * s;

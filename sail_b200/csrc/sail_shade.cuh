@@ -70,10 +70,13 @@ SD V3 uniformSampleSphere(V2 u) {
 }
 template <int F>
 SD V3 cosineSampleHemisphere(V2 u) {
-    float r = dm_sqrt(u.x);
+    // u comes from random2(): fract() of a value that is 0 or at least 2^-24 in magnitude after the cancellation with a
+    // seed >= 1 (sail_render_n rejects timeSinceStart < 0), so u.x, u.y and 1 - u.x lie in {0} u [2^-24, 1] (or are NaN):
+    // the domain of sqrtUnit / sincosUnit.
+    float r = sqrtUnit(u.x);
     float2 sc2 = sincosF<F>(SAIL_TWO_PI * u.y);
     float s = sc2.x, c = sc2.y;
-    return mk3(r * c, r * s, dm_sqrt(1.0f - u.x));
+    return mk3(r * c, r * s, sqrtUnit(1.0f - u.x));
 }
 SD V2 concentricSampleDisk(V2 u) {
     float uOffset = 2.0f * u.x - 1.0f;

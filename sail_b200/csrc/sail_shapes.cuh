@@ -89,8 +89,33 @@ static __device__ __noinline__ float sail_acos(float x) { return dm_acos(x); }
 static __device__ __noinline__ float sail_atan2(float y, float x) { return dm_atan2(y, x); }
 // Single-use sites of the small variants are inlined instead (no call overhead, code still fits the I-cache).
 #define SAIL_SMALL(F) (!((F) & (SAIL_F_GLOSSY | SAIL_F_QUADRICS | SAIL_F_NEE)))
+// dm_sincos for |x| < 2^22 (the caller passes 2*pi*u, u in [0, 1]): its out-of-range arm is unreachable and dropped, and the
+// sine and cosine polynomials, which share z = r*r, advance as one packed pair (FFMA2 / FMUL2).  Every operation and its
+// order are those of dm_sin_kernel / dm_cos_kernel, so the result equals dm_sincos(x) bit for bit
+// (tests/test_gpu_parity.py::test_unit_domain_math).
+static __constant__ float2 sailSinCosC0 = {-1.9515295891e-4f, 2.443315711809948e-5f};
+static __constant__ float2 sailSinCosC1 = {8.3321608736e-3f, -1.388731625493765e-3f};
+static __constant__ float2 sailSinCosC2 = {-1.6666654611e-1f, 4.166664568298827e-2f};
+SD float2 sincosUnit(float x) {
+    const float n = rintf(dm_mul(x, DM_TWO_OVER_PI));
+    float r = dm_fma(-n, DM_PIO2_HI, x);
+    r = dm_fma(-n, DM_PIO2_MID, r);
+    r = dm_fma(-n, DM_PIO2_LO, r);
+    const int q = (int)n;
+    const float z = dm_mul(r, r);
+    const F2 zz = splat2(z);
+    F2 p = fma2(*reinterpret_cast<const F2*>(&sailSinCosC0), zz, *reinterpret_cast<const F2*>(&sailSinCosC1));
+    p = fma2(p, zz, *reinterpret_cast<const F2*>(&sailSinCosC2));
+    p = mul2(p, zz);
+    float psz, pcz;
+    upk2(p, psz, pcz);
+    const float s = dm_fma(psz, r, r);
+    const float c = dm_add(dm_fma(-0.5f, z, 1.0f), dm_mul(pcz, z));
+    const float vs = (q & 1) ? c : s, vc = (q & 1) ? s : c;
+    return make_float2((q & 2) ? -vs : vs, ((q + 1) & 2) ? -vc : vc);
+}
 template <int F> SD float2 sincosF(float x) {
-    if (SAIL_SMALL(F)) { float s, c; dm_sincos(x, &s, &c); return make_float2(s, c); }
+    if (SAIL_SMALL(F)) return sincosUnit(x);
     return sail_sincos(x);
 }
 template <int F> SD float acosF(float x) { return SAIL_SMALL(F) ? dm_acos(x) : sail_acos(x); }

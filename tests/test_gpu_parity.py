@@ -275,6 +275,25 @@ def test_tile_rows_and_sum_mode(capi, oracle, kernel):
     assert np.all(np.abs(summed - want) <= 1e-5 * np.maximum(1.0, np.abs(want)))
 
 
+def test_unit_domain_math(capi):
+    """sail_selftest_math: dm_rcp on all 2^32 inputs; sqrtUnit == sqrt.rn for 0 and every float in [2^-100, FLT_MAX];
+    sincosUnit == dm_sincos for every float in [-8, 8] (the domain-restricted helpers of the cosine sampler)."""
+    with capi.Context(32, 32) as ctx:
+        assert ctx.selftest_math() == 0
+
+
+def test_negative_time_is_rejected(capi):
+    W, H = 32, 32
+    scene, o, t, l, bounces = scene_tables(1, W, H)
+    with capi.Context(W, H) as ctx:
+        ctx.upload_scene(o, t, l)
+        m, eye, w, tm = frame_uniforms(scene, 0, W, H)
+        for bad in (-1.0, float("nan")):
+            with pytest.raises(capi.SailError) as ei:
+                ctx.render(m, eye, w, bad)
+            assert ei.value.code == capi.ERR_INVALID
+
+
 def test_error_paths(capi):
     with pytest.raises(capi.SailError):
         capi.Context(0, 10)
