@@ -113,7 +113,7 @@ def test_scene_specialised_kernels_compile_without_a_gpu(capi, cfg):
     """The kernels that NVRTC builds per scene structure at run time must compile for every
     BASELINE config -- checked here with sail_jit_compile_check, which needs NVRTC but no device."""
     _, o, t, l, _ = scene_tables(cfg, 64, 64)
-    for kernel in (capi.KERNEL_MEGA, capi.KERNEL_WAVEFRONT):
+    for kernel in (capi.KERNEL_MEGA, capi.KERNEL_WAVEFRONT, capi.KERNEL_SERVER):
         try:
             info = capi.jit_compile_check(o, t, l, kernel)
         except capi.SailError as e:
