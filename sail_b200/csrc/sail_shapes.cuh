@@ -118,6 +118,8 @@ template <int F> SD float2 sincosF(float x) {
     if (SAIL_SMALL(F)) return sincosUnit(x);
     return sail_sincos(x);
 }
+// theta = acos(..) lies in [0, pi] (or is NaN): inside sincosUnit's domain; the unused cosine select is dropped by the compiler
+template <int F> SD float sinF(float x) { return SAIL_SMALL(F) ? sincosUnit(x).x : sail_sin(x); }
 template <int F> SD float acosF(float x) { return SAIL_SMALL(F) ? dm_acos(x) : sail_acos(x); }
 
 // The winning hit (const/struct.glsl:1-13 minus the dead dpdv / seed fields).
@@ -213,10 +215,15 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd, const int fixe
     switch (cat2 == SAIL_SPHERE ? SAIL_SPHERE : (cat2 == SAIL_RECTANGLE ? SAIL_RECTANGLE : ((F & SAIL_F_QUADRICS) ? cat : 0))) {
         case SAIL_SPHERE: if (SAIL_HAS_SHAPE(SAIL_SPHERE)) {  // sphere.glsl:10-16,45-62
             if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
-            V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_SPH_C));
-            float a = dot3(dl, dl);
-            float b = 2.0f * dot3(ol, dl);
-            float c = dot3(ol, ol) - q[SQ_SPH_RR];
+            // dl = objToLocal(d) = (-d.z, d.x, d.y), ol likewise from w = o - c.  A product of two negated factors equals the
+            // product of the factors, so the nine products of dot(dl,dl), dot(ol,dl), dot(ol,ol) are formed from the world-space
+            // components as they lie in registers (three packed multiplies, no swizzled copies) and summed in the local
+            // order x, y, z = world z, x, y -- the same values in the same order as dot3() on the swizzled vectors.
+            const V3 w = ray.o - ld3(q + SQ_SPH_C);
+            const V3 dd = ray.d * ray.d, wd = w * ray.d, ww = w * w;
+            float a = dd.z + dd.x + dd.y;
+            float b = 2.0f * (wd.z + wd.x + wd.y);
+            float c = ww.z + ww.x + ww.y - q[SQ_SPH_RR];
             float t1, t2;
             if (!quadratic(a, b, c, t1, t2)) return SAIL_MAX_DISTANCE;
             if (t2 < SAIL_EPSILON) return SAIL_MAX_DISTANCE;
@@ -493,8 +500,9 @@ SD void hitRecord(const SceneView& sc, int i, float t, const Ray& ray, Hit& h) {
         }
         case SAIL_SPHERE: if (SAIL_HAS_SHAPE(SAIL_SPHERE)) {  // sphere.glsl:33-43,62-84
             V3 c = ld3(q + SQ_SPH_C);
-            V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - c);
-            V3 hl = ol + t * dl;
+            // ol + t*dl with ol, dl the swizzles (-z, x, y) of w = o - c and d: negation commutes with every rounding, so this is
+            // the swizzle of w + t*d
+            V3 hl = objToLocal((ray.o - c) + t * ray.d);
             float r = q[SQ_SPH_R];
             float theta = acosF<F>(fclamp(hl.z * q[SQ_SPH_INVR], -1.0f, 1.0f));
             if (wantUV) {
@@ -506,7 +514,7 @@ SD void hitRecord(const SceneView& sc, int i, float t, const Ray& ray, Hit& h) {
             float invZRadius = dm_rcp(zRadius);
             float cosPhi = hl.x * invZRadius, sinPhi = hl.y * invZRadius;
             V3 dpdu = dpduAround(hl.x, hl.y);
-            V3 dpdv = SAIL_PI * mk3(hl.z * cosPhi, hl.z * sinPhi, -r * sail_sin(theta));
+            V3 dpdv = SAIL_PI * mk3(hl.z * cosPhi, hl.z * sinPhi, -r * sinF<F>(theta));
             V3 nl = normalize3(cross3(dpdv, dpdu));
             h.sc = surfaceColor<F>(u, uv);
             h.p = objToWorld(hl) + c;
