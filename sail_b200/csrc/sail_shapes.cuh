@@ -193,9 +193,13 @@ SD int opaqueInt(int v) {
     asm("" : "+r"(v));
     return v;
 }
+// Shapes whose intersectX() starts with testBoundboxForX() (sphere.glsl:10-16, cone / cylinder / hyperboloid / paraboloid alike)
+#define SAIL_BOUNDED_SHAPE(c) ((c) == SAIL_SPHERE || (c) == SAIL_CONE || (c) == SAIL_CYLINDER || (c) == SAIL_HYPERBOLOID || (c) == SAIL_PARABOLOID)
+// Runs shorter than this are unrolled object by object (measured: two spheres are faster unrolled, config 5 -1.3 % otherwise).
+#define SAIL_JIT_UNROLL_BELOW(c) 3
 // Phase 1: the value intersectX() would leave in `result.d` (MAX_DISTANCE = no hit).
 template <int F>
-SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd, const int fixedCat = -1) {
+SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd, const int fixedCat = -1, const bool boundsDone = false) {
     const float* q = s.q;
     // The three common shapes are tested by a compare chain (2-3 instructions each); a `switch` over all
     // categories compiles to a bounds check + jump-table load + indirect branch, 11 instructions per object.
@@ -214,7 +218,7 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd, const int fixe
     const int cat2 = fixedCat >= 0 ? cat : opaqueInt(cat);
     switch (cat2 == SAIL_SPHERE ? SAIL_SPHERE : (cat2 == SAIL_RECTANGLE ? SAIL_RECTANGLE : ((F & SAIL_F_QUADRICS) ? cat : 0))) {
         case SAIL_SPHERE: if (SAIL_HAS_SHAPE(SAIL_SPHERE)) {  // sphere.glsl:10-16,45-62
-            if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
+            if (!boundsDone && !boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
             // dl = objToLocal(d) = (-d.z, d.x, d.y), ol likewise from w = o - c.  A product of two negated factors equals the
             // product of the factors, so the nine products of dot(dl,dl), dot(ol,dl), dot(ol,ol) are formed from the world-space
             // components as they lie in registers (three packed multiplies, no swizzled copies) and summed in the local
@@ -245,7 +249,7 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd, const int fixe
             return t;
         }
         case SAIL_CONE: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_CONE)) {  // cone.glsl:11-17,48-81
-            if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
+            if (!boundsDone && !boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_CONE_P));
             float k = q[SQ_CONE_K], h = q[SQ_CONE_H];
             float a = dl.x * dl.x + dl.y * dl.y - k * dl.z * dl.z;
@@ -254,7 +258,7 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd, const int fixe
             return quadricRoot(a, b, c, ol, dl, -SAIL_EPSILON, h);
         }
         case SAIL_CYLINDER: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_CYLINDER)) {  // cylinder.glsl:11-17,40-72
-            if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
+            if (!boundsDone && !boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_CYL_P));
             float a = dl.x * dl.x + dl.y * dl.y;
             float b = 2.0f * (dl.x * ol.x + dl.y * ol.y);
@@ -273,7 +277,7 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd, const int fixe
             return t;
         }
         case SAIL_HYPERBOLOID: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_HYPERBOLOID)) {  // hyperboloid.glsl:13-24,60-90
-            if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
+            if (!boundsDone && !boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_HYP_P));
             float ah = q[SQ_HYP_AH], ch = q[SQ_HYP_CH];
             float a = ah * dl.x * dl.x + ah * dl.y * dl.y - ch * dl.z * dl.z;
@@ -282,7 +286,7 @@ SD float shapeDistance(const SailShape& s, const Ray& ray, V3 rd, const int fixe
             return quadricRoot(a, b, c, ol, dl, q[SQ_HYP_ZMIN], q[SQ_HYP_ZMAX]);
         }
         case SAIL_PARABOLOID: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_PARABOLOID)) {  // paraboloid.glsl:12-20,51-82
-            if (!boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
+            if (!boundsDone && !boundsHit(s, ray.o, rd)) return SAIL_MAX_DISTANCE;
             V3 dl = objToLocal(ray.d), ol = objToLocal(ray.o - ld3(q + SQ_PAR_P));
             float k = q[SQ_PAR_K];
             float a = k * (dl.x * dl.x + dl.y * dl.y);
@@ -332,11 +336,27 @@ SD Nearest nearestObjectInline(const SceneView& sc, const Ray& ray) {
     constexpr int kRunLen[SAIL_JIT_NRUNS] = {SAIL_JIT_RUN_LENS};
 #pragma unroll
     for (int k = 0; k < SAIL_JIT_NRUNS; k++) {
-        if (kRunLen[k] < 3) {
+        if (kRunLen[k] < SAIL_JIT_UNROLL_BELOW(kRunCat[k])) {
 #pragma unroll
             for (int j = 0; j < kRunLen[k]; j++) {
                 float t = shapeDistance<F>(sc.shape[kRunStart[k] + j], ray, rd, kRunCat[k]);
                 if (t < r.t) { r.t = t; r.id = kRunStart[k] + j; }
+            }
+        } else if (SAIL_BOUNDED_SHAPE(kRunCat[k]) && kRunLen[k] <= 32) {
+            // A run of equal shapes that test their bounding box first (sphere.glsl:10-16 ...): all the (cheap, uniform)
+            // box tests first, then every lane walks ITS OWN list of boxes it passed, in ascending index.  One pass through
+            // the quadratic serves different objects on different lanes, so the warp makes max-over-lanes passes (typically
+            // 1-2) instead of one per object with a few lanes each.  Per object the same two steps in the same order, and the
+            // running minimum still sees the objects in ascending index: identical result.
+            unsigned pend = 0;
+#pragma unroll 1
+            for (int j = 0; j < kRunLen[k]; j++)
+                if (boundsHit(sc.shape[kRunStart[k] + j], ray.o, rd)) pend |= 1u << j;
+            while (pend) {
+                const int i = kRunStart[k] + (__ffs(pend) - 1);
+                pend &= pend - 1u;
+                float t = shapeDistance<F>(sc.shape[i], ray, rd, kRunCat[k], true);
+                if (t < r.t) { r.t = t; r.id = i; }
             }
         } else {
 #pragma unroll 1
