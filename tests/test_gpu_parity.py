@@ -131,6 +131,29 @@ def test_emissive_mask_edge_cases(capi, oracle, kernel):
         _assert_same(out, ref, "emissive edge cases, bounces=%d" % bounces)
 
 
+@pytest.mark.parametrize("kernel", [0, 1], ids=["mega", "wavefront"])
+@pytest.mark.parametrize("count", [10, 40])
+def test_runs_of_spheres_bit_exact(capi, oracle, count, kernel):
+    """Runs of equal bounded shapes: the scan tests all bounding boxes first and each lane walks its own list of passed
+    boxes (sail_shapes.cuh); 10 overlapping spheres take that path, 40 exceed its 32-bit list and take the plain loop."""
+    import sail_b200 as Sail
+    from sail_b200 import wire
+    W, H = 64, 48
+    scene, _, _, _, _ = scene_tables(1, W, H)
+    s2 = Sail.Scene()
+    s2.add(Sail.Cube([2.13, 5.487, 2.27], [3.43, 5.488, 3.32], Sail.Matte(0.7), Sail.UniformColor([0, 0, 0]), [8, 8, 8]))
+    s2.add(Sail.Cornellbox([0, 0, -7], [5.560, 5.488, 5.592]))
+    rng = np.random.default_rng(7)
+    for i in range(count):
+        c = [float(rng.uniform(0.8, 4.8)), float(rng.uniform(0.5, 3.5)), float(rng.uniform(0.5, 4.5))]
+        mat = [Sail.Matte(0.7), Sail.Mirror(1.0), Sail.Glass(1, 1, 1.5), Sail.Metal(0, 0.05, 0.1)][i % 4]
+        s2.add(Sail.Sphere(c, float(rng.uniform(0.3, 0.9)), mat, Sail.UniformColor([0.9, 0.8, 0.7])))
+    s2.add(scene.camera)
+    o, t, l = wire.serialize_scene(s2)
+    out, ref = _render_tables(capi, oracle, o, t, l, s2, W, H, 2, 5, kernel, specialise=2)
+    _assert_same(out, ref, "%d spheres" % count)
+
+
 @pytest.mark.parametrize("cfg", [1, 2])
 def test_render_n_equals_single_calls(capi, oracle, cfg):
     a, _ = _render_both(capi, oracle, cfg, 6, batch=False)
