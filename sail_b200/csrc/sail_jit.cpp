@@ -161,6 +161,15 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
         minCtas = (int)(65536u / (64u * block));
         if (minCtas < 1) minCtas = 1;
     }
+    if (kind == 1) {  // wavefront: paths per CTA (sail_wavefront.cuh SAIL_WF_THREADS), 64 registers per thread fill the SM
+        // measured (tools/wf_sweep.sh, Mpaths/s at 128 / 256 / 512 paths): config 3 (quadrics) 1744 / 2059 / 2269, config 5 1204 / 1303 / 1336,
+        // config 2 3930 / 3956 / 3768
+        int wf = (F & 1 /* SAIL_F_QUADRICS */) ? 512 : ((F & 2 /* SAIL_F_GLOSSY */) ? 256 : SAIL_JIT_WF_THREADS_DEFAULT);
+        if (const char* e = getenv("SAIL_B200_WF_THREADS")) wf = atoi(e);
+        if (wf != 128 && wf != 256 && wf != 512) { setErr(err, errlen, "SAIL_B200_WF_THREADS must be 128, 256 or 512"); return 2; }
+        block = (unsigned)wf;
+        if (wf != 128) minCtas = (int)(65536u / (64u * block));
+    }
     if (kind != 2) {
         if (const char* e = getenv("SAIL_B200_MIN_CTAS")) {  // occupancy sweeps (tools/ab_defs.sh)
             const int v = atoi(e);
@@ -170,6 +179,7 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
     const char* kindName = kind == 2 ? "server" : (kind ? "wavefront" : "mega");
     char head[96];
     if (kind == 2) snprintf(head, sizeof(head), "jit server<F=%d,%d+1 warps> n=%d shapes=", F, pathWarps, n);
+    else if (kind == 1 && block != 128) snprintf(head, sizeof(head), "jit wavefront<F=%d,%u paths> n=%d shapes=", F, block, n);
     else snprintf(head, sizeof(head), "jit %s<F=%d> n=%d shapes=", kindName, F, n);
     // SAIL_B200_JIT_DEFINES="NAME=VALUE,NAME2=VALUE2": extra #defines for A/B runs of experimental code paths
     std::string extraDefs;
@@ -199,12 +209,12 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
     snprintf(src, sizeof(src),
              "%s#define SAIL_JIT_NRUNS %d\n#define SAIL_JIT_RUN_CATS %s\n#define SAIL_JIT_RUN_STARTS %s\n#define SAIL_JIT_RUN_LENS %s\n"
              "#define SAIL_JIT_SHAPES 0x%xu\n#define SAIL_JIT_MATS 0x%xu\n#define SAIL_JIT_TEXS 0x%xu\n#define SAIL_JIT_LIGHTS 0x%xu\n"
-             "#define SAIL_JIT_GLASS %u\n#define SAIL_JIT_MATS_BOX 0x%xu\n#define SAIL_JIT_MATS_OFF 0x%xu\n#define SAIL_SRV_PATH_WARPS %d\n%s"
+             "#define SAIL_JIT_GLASS %u\n#define SAIL_JIT_MATS_BOX 0x%xu\n#define SAIL_JIT_MATS_OFF 0x%xu\n#define SAIL_SRV_PATH_WARPS %d\n#define SAIL_WF_THREADS %u\n%s"
              "#include \"sail_mega.cuh\"\n#include \"sail_wavefront.cuh\"\n#include \"sail_server.cuh\"\n"
              "extern \"C\" __global__ void __launch_bounds__(%u, %d) sail_jit_kernel(const __grid_constant__ SailLaunch L) "
              "{ %s<%d>(L); }\n",
              extraDefs.c_str(), nruns, runCat.c_str(), runStart.c_str(), runLen.c_str(), shapes, mats, texs, lights, glass, matsBox, matsOff,
-             pathWarps ? pathWarps : 7,
+             pathWarps ? pathWarps : 7, kind == 1 ? block : 128u,
              // quadric scenes: the kernel is 2x the 32 KB instruction cache, one shared sqrt pays (config 3: +5..16 %); the
              // metal/glass-only kernels are faster with it inlined (measured, tools/bench_outline.sh history)
              (F & 1 /* SAIL_F_QUADRICS */) ? "#define SAIL_OUTLINE_SQRT 1\n" : "", block, minCtas,

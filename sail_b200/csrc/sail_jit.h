@@ -11,6 +11,7 @@ struct SailJitKernel {
     unsigned block;  // threads per CTA the kernel was compiled for
     int pathWarps;   // kind 2: path warps per CTA (sail_server.cuh); 0 otherwise
 };
+#define SAIL_JIT_WF_THREADS_DEFAULT 128  // paths per wavefront CTA of the run-time compiled kernel (SAIL_B200_WF_THREADS overrides)
 #define SAIL_JIT_CTA_THREADS 128u  // = SAIL_CTA_THREADS of sail_mega.cuh (kinds 0 and 1)
 
 // kind: 0 megakernel, 1 wavefront, 2 megakernel with a server warp (sail_server.cuh; run-time compiled only).  Returns 0 and fills `out`, or non-zero with a message in `err` (NVRTC or the

@@ -18,22 +18,31 @@
 #include "sail_mega.cuh"
 
 #define SAIL_WF_STATE 16  // words of path state exchanged per bounce
+// Paths per wavefront (= threads per CTA).  128 in the ahead-of-time variants; the run-time compiled kernel may use more
+// (sail_jit.cpp): a larger wavefront regroups over more paths (fuller warps per object) and keeps more of an SM's warps in
+// the same phase of the bounce, which matters once the kernel is larger than the 32 KB instruction cache.  The CTA's pixel
+// tile is (SAIL_WF_THREADS / 8) x 8: two rows of 8x4 warp sub-tiles, so row bands keep their 8-row granularity.
+#ifndef SAIL_WF_THREADS
+#define SAIL_WF_THREADS SAIL_CTA_THREADS
+#endif
+#define SAIL_WF_TILE_W (SAIL_WF_THREADS / 8)
+#define SAIL_WF_WARPS_X (SAIL_WF_TILE_W / 8)
 
 template <int F>
 SD void sailWaveBody(const SailLaunch& L) {
-    __shared__ float slot[SAIL_WF_STATE][SAIL_CTA_THREADS];  // SoA: lane-consecutive words, conflict free
-    __shared__ float firstHit[6][SAIL_CTA_THREADS];          // n, p of the primary hit, indexed by home lane
+    __shared__ float slot[SAIL_WF_STATE][SAIL_WF_THREADS];  // SoA: lane-consecutive words, conflict free
+    __shared__ float firstHit[6][SAIL_WF_THREADS];          // n, p of the primary hit, indexed by home lane
     __shared__ int hist[2][SAIL_MAX_OBJECTS + 2];  // double buffered: the next bounce's counters are cleared while this one scatters
     const SceneView sc = stageScene(L.scene);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int x = blockIdx.x * SAIL_TILE_W + (warp & 1) * 8 + (lane & 7);
+    const int x = blockIdx.x * SAIL_WF_TILE_W + (warp % SAIL_WF_WARPS_X) * 8 + (lane & 7);
     int tileY = L.y0 + blockIdx.y * SAIL_TILE_H;
     if (L.bandStride > 1) {
         const int tpb = L.bandRows / SAIL_TILE_H;
         tileY = (L.bandFirst + ((int)blockIdx.y / tpb) * L.bandStride) * L.bandRows + ((int)blockIdx.y % tpb) * SAIL_TILE_H;
     }
-    const int y = tileY + (warp >> 1) * 4 + (lane >> 3);
+    const int y = tileY + (warp / SAIL_WF_WARPS_X) * 4 + (lane >> 3);
     const bool inside = x < L.W && y < L.y1;  // no early exit: every lane takes part in the barriers
     const size_t pix = inside ? (size_t)y * L.W + x : 0;
     const float hx = (float)x + 0.5f, hy = (float)y + 0.5f;  // gl_FragCoord of the home pixel
