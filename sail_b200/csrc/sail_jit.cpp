@@ -38,6 +38,7 @@ typedef int (*cuModuleLoadData_t)(void**, const void*);
 typedef int (*cuModuleGetFunction_t)(void**, void*, const char*);
 typedef int (*cuLaunchKernel_t)(void*, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, void*, void**, void**);
 typedef int (*cuGetErrorString_t)(int, const char**);
+typedef int (*cuFuncSetAttribute_t)(void*, int, int);
 
 struct Api {
     bool tried = false, ok = false;        // NVRTC
@@ -53,6 +54,7 @@ struct Api {
     cuModuleGetFunction_t moduleGetFunction = nullptr;
     cuLaunchKernel_t launchKernel = nullptr;
     cuGetErrorString_t errorString = nullptr;
+    cuFuncSetAttribute_t funcSetAttribute = nullptr;
 };
 Api g_api;
 std::mutex g_mutex;
@@ -101,6 +103,7 @@ bool loadDriver() {
     SYM(cu, moduleGetFunction, "cuModuleGetFunction", cuModuleGetFunction_t)
     SYM(cu, launchKernel, "cuLaunchKernel", cuLaunchKernel_t)
     SYM(cu, errorString, "cuGetErrorString", cuGetErrorString_t)
+    SYM(cu, funcSetAttribute, "cuFuncSetAttribute", cuFuncSetAttribute_t)
 #undef SYM
     g_api.cuOk = true;
     return true;
@@ -255,6 +258,9 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
     void *mod = nullptr, *fn = nullptr;
     int cr = g_api.moduleLoadData(&mod, cubin.data());
     if (cr == 0) cr = g_api.moduleGetFunction(&fn, mod, "sail_jit_kernel");
+    // A 512-path wavefront holds 45 KB of static shared memory (exchange slots); together with the scene block of a large
+    // scene (up to 17 KB, dynamic) that passes the 48 KB a kernel gets without opting in.
+    if (cr == 0 && block > 128) cr = g_api.funcSetAttribute(fn, 8 /* CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES */, (int)sizeof(SailSceneBlock));
     if (cr != 0) {
         const char* es = nullptr;
         g_api.errorString(cr, &es);

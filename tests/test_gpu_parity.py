@@ -154,6 +154,24 @@ def test_runs_of_spheres_bit_exact(capi, oracle, count, kernel):
     _assert_same(out, ref, "%d spheres" % count)
 
 
+def test_large_quadric_scene_wavefront(capi, oracle):
+    """Config 3 plus 40 more objects: the 512-path wavefront's 45 KB of exchange slots and a 13 KB scene block together exceed
+    the default 48 KB of shared memory; the kernel opts in (sail_jit.cpp) and stays bit-exact."""
+    import sail_b200 as Sail
+    from sail_b200 import wire
+    W, H = 64, 48
+    scene, _, _, _, bounces = scene_tables(3, W, H)
+    rng = np.random.default_rng(3)
+    for i in range(40):
+        c = [float(rng.uniform(0.5, 5.0)), float(rng.uniform(0.3, 4.0)), float(rng.uniform(0.5, 5.0))]
+        if i < 20: scene.add(Sail.Sphere(c, 0.25, Sail.Matte(0.7), Sail.Color.WHITE))  # two runs: the scene stays specialisable
+        else: scene.add(Sail.Cube(c, [c[0] + 0.3, c[1] + 0.3, c[2] + 0.3], Sail.Mirror(1.0), Sail.Color.WHITE))
+    o, t, l = wire.serialize_scene(scene)
+    assert "512 paths" in capi.jit_compile_check(o, t, l, kernel=capi.KERNEL_WAVEFRONT)
+    out, ref = _render_tables(capi, oracle, o, t, l, scene, W, H, 2, bounces, capi.KERNEL_AUTO, specialise=2)
+    _assert_same(out, ref, "config 3 + 40 objects")
+
+
 @pytest.mark.parametrize("cfg", [1, 2])
 def test_render_n_equals_single_calls(capi, oracle, cfg):
     a, _ = _render_both(capi, oracle, cfg, 6, batch=False)
