@@ -360,14 +360,14 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
     // the variant follows the scene's content, never the caller's mask hints
     dim3 grid((ctx->W + SAIL_TILE_W - 1) / SAIL_TILE_W, tileRows);
     const int F = ctx->hostScene.features & SAIL_F_ALL;
-    // SAIL_KERNEL_AUTO, from the measured matrix: the wavefront pays where the scene has many shape codes
-    // (quadrics) or many BSDFs (metal / glass); its run-time compiled form uses 512 / 256 paths per CTA there.
+    // SAIL_KERNEL_AUTO, from the measured matrix: the wavefront (512 paths per CTA when compiled at run time) pays
+    // where the scene has many shape codes (quadrics); among the ahead-of-time variants also where it has many BSDFs (metal / glass).
     const bool tryJit = ctx->cfg.specialise != SAIL_SPECIALISE_OFF;
     bool wave = ctx->cfg.kernel == SAIL_KERNEL_WAVEFRONT;
     bool server = ctx->cfg.kernel == SAIL_KERNEL_SERVER;
     if (server && !tryJit) return setErr(ctx, SAIL_ERR_STATE, "SAIL_KERNEL_SERVER exists only as a scene-specialised kernel (specialise = off)");
     if (ctx->cfg.kernel == SAIL_KERNEL_AUTO) {
-        wave = (F & (SAIL_F_QUADRICS | SAIL_F_GLOSSY)) != 0;
+        wave = (F & SAIL_F_QUADRICS) != 0;
         // The server-warp kernel is never chosen automatically: measured slower than the plain megakernel on the scene it
         // was built for (Cornell box 9.3 vs 11.0 Gpaths/s); SAIL_B200_AUTO_SERVER=1 turns it on for A/B runs.
         static const bool autoServer = getenv("SAIL_B200_AUTO_SERVER") && getenv("SAIL_B200_AUTO_SERVER")[0] == '1';

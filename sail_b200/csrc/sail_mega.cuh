@@ -71,8 +71,11 @@ SD SceneView stageScene(const SailSceneBlock* __restrict__ src) {
     const int nShape = n * (int)(sizeof(SailShape) / 16), nSurf = n * (int)(sizeof(SailSurface) / 16);
     const int nLight = (ln + 1) * (int)(sizeof(SailLight) / 16);
     if (tid == 0) d4[0] = s4[0];
+#pragma unroll 1
     for (int i = tid; i < nShape; i += nt) d4[1 + i] = s4[shapeOff + i];
+#pragma unroll 1
     for (int i = tid; i < nSurf; i += nt) d4[1 + nShape + i] = s4[surfOff + i];
+#pragma unroll 1
     for (int i = tid; i < nLight; i += nt) d4[1 + nShape + nSurf + i] = s4[lightOff + i];
     __syncthreads();
 #ifndef SAIL_NO_OPAQUE_SMEM_BASE

@@ -287,8 +287,9 @@ SD V3 material(const SailSurface& su, int matCategory, V3 sc, bool into, V2 u, V
             V3 R = m[SM_MATTE_KD] * sc;
             wi = cosineSampleHemisphere<F>(u);
             pdf = sameHemisphere(wo, wi) ? absCosTheta(wi) * SAIL_INVPI : 0.0f;
-            if (m[SM_MATTE_SIGMA] < SAIL_EPSILON) fs = R * SAIL_INVPI;                    // bsdf.glsl:7-19
-            else fs = orenNayar_f(R, m[SM_MATTE_A], m[SM_MATTE_B], wo, wi);              // bsdf.glsl:45-76
+            // SAIL_HAS_LAMBERT / SAIL_HAS_OREN_NAYAR: which of the two the scene's matte materials select (sail_jit.cpp)
+            if (SAIL_HAS_LAMBERT && (!SAIL_HAS_OREN_NAYAR || m[SM_MATTE_SIGMA] < SAIL_EPSILON)) fs = R * SAIL_INVPI;  // bsdf.glsl:7-19
+            else if (SAIL_HAS_OREN_NAYAR) fs = orenNayar_f(R, m[SM_MATTE_A], m[SM_MATTE_B], wo, wi);  // bsdf.glsl:45-76
             f = fs;  // matte_f() evaluates the same expression on the same (wo, wi)
             break;
         }

@@ -73,7 +73,11 @@ enum { SAIL_F_QUADRICS = 1,  // cone, cylinder, disk, hyperboloid, paraboloid pr
 #define SAIL_HAS_LIGHT(c) ((((unsigned)(SAIL_JIT_LIGHTS)) >> (c)) & 1u)
 #define SAIL_HAS_SMOOTH_GLASS ((SAIL_JIT_GLASS) & 1)
 #define SAIL_HAS_ROUGH_GLASS ((SAIL_JIT_GLASS) & 2)
+#define SAIL_HAS_LAMBERT ((SAIL_JIT_MATTE) & 1)
+#define SAIL_HAS_OREN_NAYAR ((SAIL_JIT_MATTE) & 2)
 #else
+#define SAIL_HAS_LAMBERT 1
+#define SAIL_HAS_OREN_NAYAR 1
 #define SAIL_HAS_SHAPE(c) 1
 #define SAIL_HAS_MAT(c) 1
 #define SAIL_HAS_TEX(c) 1
