@@ -137,7 +137,7 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
     }
     if (nruns > SAIL_JIT_MAX_RUNS) { setErr(err, errlen, "more than 16 runs of distinct shapes"); return 2; }
     // which plugins the scene contains (category ids as bit positions; ids outside 0..31 select no arm anyway)
-    unsigned shapes = 0, mats = 0, texs = 0, lights = 0, glass = 0, matsBox = 0, matsOff = 0, matte = 0;
+    unsigned shapes = 0, mats = 0, texs = 0, lights = 0, glass = 0, matsBox = 0, matsOff = 0, matte = 0, tr = 0;
     auto bit = [](int c) { return (c >= 0 && c < 32) ? (1u << c) : 0u; };
     for (int i = 0; i < n; i++) {
         shapes |= bit(scene->shape[i].category);
@@ -150,11 +150,14 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
         if (scene->shape[i].matCategory == SAIL_GLASS || scene->surf[i].matCategory == SAIL_GLASS) {
             const float ur = scene->surf[i].m[SM_GLASS_UR], vr = scene->surf[i].m[SM_GLASS_VR];
             glass |= (ur < 1e-5f && vr < 1e-5f) ? 1u : 2u;  // the shader's test, glass.glsl:13 (EPSILON, define.glsl)
+            if (!(ur < 1e-5f && vr < 1e-5f)) tr |= (ur == vr) ? 1u : 2u;  // microfacet.glsl:44 `alphax == alphay`
         }
+        if (scene->shape[i].matCategory == SAIL_METAL || scene->surf[i].matCategory == SAIL_METAL)
+            tr |= (scene->surf[i].m[SM_METAL_UR] == scene->surf[i].m[SM_METAL_VR]) ? 1u : 2u;
     }
     for (int k = 0; scene->ln > 0 && k <= scene->ln; k++) lights |= bit(scene->light[k].category);
     char masks[96];
-    snprintf(masks, sizeof(masks), " plugins=%x/%x/%x/%x/%x/%x", shapes, mats, texs, lights, glass, matte);
+    snprintf(masks, sizeof(masks), " plugins=%x/%x/%x/%x/%x/%x/%x", shapes, mats, texs, lights, glass, matte, tr);
     // kind 2 (sail_server.cuh): path warps per CTA next to the one server warp; 64 registers per thread fill the SM
     int pathWarps = 0;
     unsigned block = SAIL_JIT_CTA_THREADS;
@@ -214,11 +217,11 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
     snprintf(src, sizeof(src),
              "%s#define SAIL_JIT_NRUNS %d\n#define SAIL_JIT_RUN_CATS %s\n#define SAIL_JIT_RUN_STARTS %s\n#define SAIL_JIT_RUN_LENS %s\n"
              "#define SAIL_JIT_SHAPES 0x%xu\n#define SAIL_JIT_MATS 0x%xu\n#define SAIL_JIT_TEXS 0x%xu\n#define SAIL_JIT_LIGHTS 0x%xu\n"
-             "#define SAIL_JIT_GLASS %u\n#define SAIL_JIT_MATTE %u\n#define SAIL_JIT_MATS_BOX 0x%xu\n#define SAIL_JIT_MATS_OFF 0x%xu\n#define SAIL_SRV_PATH_WARPS %d\n#define SAIL_WF_THREADS %u\n%s"
+             "#define SAIL_JIT_GLASS %u\n#define SAIL_JIT_MATTE %u\n#define SAIL_JIT_TR %u\n#define SAIL_JIT_MATS_BOX 0x%xu\n#define SAIL_JIT_MATS_OFF 0x%xu\n#define SAIL_SRV_PATH_WARPS %d\n#define SAIL_WF_THREADS %u\n%s"
              "#include \"sail_mega.cuh\"\n#include \"sail_wavefront.cuh\"\n#include \"sail_server.cuh\"\n"
              "extern \"C\" __global__ void __launch_bounds__(%u, %d) sail_jit_kernel(const __grid_constant__ SailLaunch L) "
              "{ %s<%d>(L); }\n",
-             extraDefs.c_str(), nruns, runCat.c_str(), runStart.c_str(), runLen.c_str(), shapes, mats, texs, lights, glass, matte, matsBox, matsOff,
+             extraDefs.c_str(), nruns, runCat.c_str(), runStart.c_str(), runLen.c_str(), shapes, mats, texs, lights, glass, matte, tr, matsBox, matsOff,
              pathWarps ? pathWarps : 7, kind == 1 ? block : 128u,
              // quadric scenes: the kernel is 2x the 32 KB instruction cache, one shared sqrt pays (config 3: +5..16 %); the
              // metal/glass-only kernels are faster with it inlined (measured, tools/bench_outline.sh history)

@@ -155,10 +155,11 @@ SD V3 frConductor(float cosThetaI, V3 etaI, V3 etaT, V3 k) {
 // ---- material/microfacet.glsl:41-71 (Trowbridge-Reitz; Beckmann is never constructed) ----------------
 SD V3 trowbridgeReitz_sample_wh(V2 u, float alphax, float alphay, V3 wo) {
     float cosTheta_ = 0.0f, phi = SAIL_TWO_PI * u.x;
-    if (alphax == alphay) {
+    // SAIL_HAS_TR_ISO / SAIL_HAS_TR_ANISO: which arm the scene's metal / rough-glass roughness pairs select (sail_jit.cpp)
+    if (SAIL_HAS_TR_ISO && (!SAIL_HAS_TR_ANISO || alphax == alphay)) {
         float tanTheta2 = fdiv(alphax * alphax * u.x, 1.0f - u.x);
         cosTheta_ = dm_rcp(dm_sqrt(1.0f + tanTheta2));
-    } else {
+    } else if (SAIL_HAS_TR_ANISO) {
         phi = dm_atan(fdiv(alphay, alphax) * dm_tan(SAIL_PIOVER2 + SAIL_TWO_PI * u.x));
         if (u.x > 0.5f) phi += SAIL_PI;
         float2 sc2 = sail_sincos(phi);

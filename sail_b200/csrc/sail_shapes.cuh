@@ -75,9 +75,13 @@ enum { SAIL_F_QUADRICS = 1,  // cone, cylinder, disk, hyperboloid, paraboloid pr
 #define SAIL_HAS_ROUGH_GLASS ((SAIL_JIT_GLASS) & 2)
 #define SAIL_HAS_LAMBERT ((SAIL_JIT_MATTE) & 1)
 #define SAIL_HAS_OREN_NAYAR ((SAIL_JIT_MATTE) & 2)
+#define SAIL_HAS_TR_ISO ((SAIL_JIT_TR) & 1)
+#define SAIL_HAS_TR_ANISO ((SAIL_JIT_TR) & 2)
 #else
 #define SAIL_HAS_LAMBERT 1
 #define SAIL_HAS_OREN_NAYAR 1
+#define SAIL_HAS_TR_ISO 1
+#define SAIL_HAS_TR_ANISO 1
 #define SAIL_HAS_SHAPE(c) 1
 #define SAIL_HAS_MAT(c) 1
 #define SAIL_HAS_TEX(c) 1
