@@ -160,6 +160,15 @@ def measured_traffic():
         return None
 
 
+def measured_ncu():
+    """Pipe-side counters of the same ncu capture (issue-slot utilisation, executed instructions), or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(_workload, {}).get("ncu")
+    except (OSError, ValueError):
+        return None
+
+
 def cpu_baseline(seconds=12.0, min_frames=8, threads=0):
     """The CPU oracle (a port: the reference has no CPU implementation) on a bounded sample of the workload: whole
     1080p frames of 1 spp until about ``seconds`` of CPU work are done, all host cores (OpenMP over rows)."""
@@ -337,7 +346,7 @@ def run_ours(args, rank, world, local_rank):
                        "l2": "flushed between steps (256 MiB memset outside the per-step events)"},
             "spp_per_s": value * 1e6 / (W * H),
             "roofline": {"bound": "fp32_issue", "achieved": achieved, "peak": peak, "unit": "Tops/s (FP32 lane-ops)",
-                         "frac": achieved / peak, "traffic": measured_traffic(), "ops_per_path": ops,
+                         "frac": achieved / peak, "traffic": measured_traffic(), "ncu": measured_ncu(), "ops_per_path": ops,
                          "peak_def": "%d SMs x 128 lanes x %.0f MHz (%s sm_max_mhz)" % (n_sm, pk["sm_max_mhz"], pk["source"]),
                          "hbm": {"achieved": hbm_gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": hbm_gbs / pk["hbm_gbs"],
                                  "bytes_per_launch": W * H * 24}},
