@@ -361,6 +361,20 @@ def run_ours(args, rank, world, local_rank):
             line["cpu_baseline"] = cpu_baseline()
         if world == 1 and not args.no_cpu and _workload == "cornell":
             line["other_workloads"] = [other_workload(w, local_rank, peak) for w in ("config2", "config3", "config5")]
+            # The same workload with the last-bounce reductions compiled out (every bounce evaluated in full, as the
+            # reference's loop does; identical image): how much of `value` is skipped dead work.
+            keep = os.environ.get("SAIL_B200_JIT_DEFINES")
+            os.environ["SAIL_B200_JIT_DEFINES"] = (keep + "," if keep else "") + "SAIL_LITERAL_LAST_BOUNCE"
+            try:
+                lit = other_workload("cornell", local_rank, peak)
+            finally:
+                if keep is None:
+                    del os.environ["SAIL_B200_JIT_DEFINES"]
+                else:
+                    os.environ["SAIL_B200_JIT_DEFINES"] = keep
+            line["literal_last_bounce"] = {"value": lit["value"], "unit": UNIT, "ms_per_step": lit["ms_per_step"], "steps": lit["steps"],
+                                           "roofline_frac": lit["roofline_frac"], "kernel_used": lit["kernel_used"],
+                                           "note": "same workload, kernel built with -DSAIL_LITERAL_LAST_BOUNCE"}
         print(json.dumps(line))
     r.close()
     if dist:

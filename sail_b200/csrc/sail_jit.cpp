@@ -156,8 +156,24 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
             tr |= (scene->surf[i].m[SM_METAL_UR] == scene->surf[i].m[SM_METAL_VR]) ? 1u : 2u;
     }
     for (int k = 0; scene->ln > 0 && k <= scene->ln; k++) lights |= bit(scene->light[k].category);
-    char masks[96];
+    // SAIL_B200_JIT_DEFINES="NAME=VALUE,NAME2=VALUE2": extra #defines for A/B runs of experimental code paths
+    std::string extraDefs;
+    if (const char* e = getenv("SAIL_B200_JIT_DEFINES")) {
+        std::string cur;
+        for (const char* p = e;; p++) {
+            if (*p == ',' || *p == 0) {
+                if (!cur.empty()) {
+                    const size_t eq = cur.find('=');
+                    extraDefs += "#define " + (eq == std::string::npos ? cur + " 1" : cur.substr(0, eq) + " " + cur.substr(eq + 1)) + "\n";
+                }
+                cur.clear();
+                if (*p == 0) break;
+            } else cur += *p;
+        }
+    }
+    char masks[200];
     snprintf(masks, sizeof(masks), " plugins=%x/%x/%x/%x/%x/%x/%x", shapes, mats, texs, lights, glass, matte, tr);
+    if (const char* e = extraDefs.empty() ? nullptr : getenv("SAIL_B200_JIT_DEFINES")) snprintf(masks + strlen(masks), sizeof(masks) - strlen(masks), " -D%.60s", e);
     // kind 2 (sail_server.cuh): path warps per CTA next to the one server warp; 64 registers per thread fill the SM
     int pathWarps = 0;
     unsigned block = SAIL_JIT_CTA_THREADS;
@@ -189,21 +205,6 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
     if (kind == 2) snprintf(head, sizeof(head), "jit server<F=%d,%d+1 warps> n=%d shapes=", F, pathWarps, n);
     else if (kind == 1 && block != 128) snprintf(head, sizeof(head), "jit wavefront<F=%d,%u paths> n=%d shapes=", F, block, n);
     else snprintf(head, sizeof(head), "jit %s<F=%d> n=%d shapes=", kindName, F, n);
-    // SAIL_B200_JIT_DEFINES="NAME=VALUE,NAME2=VALUE2": extra #defines for A/B runs of experimental code paths
-    std::string extraDefs;
-    if (const char* e = getenv("SAIL_B200_JIT_DEFINES")) {
-        std::string cur;
-        for (const char* p = e;; p++) {
-            if (*p == ',' || *p == 0) {
-                if (!cur.empty()) {
-                    const size_t eq = cur.find('=');
-                    extraDefs += "#define " + (eq == std::string::npos ? cur + " 1" : cur.substr(0, eq) + " " + cur.substr(eq + 1)) + "\n";
-                }
-                cur.clear();
-                if (*p == 0) break;
-            } else cur += *p;
-        }
-    }
     const std::string key = extraDefs + "dev" + std::to_string(device) + " m" + std::to_string(minCtas) + " " + head + cats + masks;
     auto it = g_cache.find(key);
     out->block = block;

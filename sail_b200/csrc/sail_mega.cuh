@@ -125,7 +125,13 @@ SD void sailMegaBody(const SailLaunch& L) {
 
     const size_t pix = (size_t)y * L.W + x;
     // gl_FragCoord of the full-screen quad at z = 0 (depth 0.5)
-    const float fx = (float)x + 0.5f, fy = (float)y + 0.5f, fz = 0.5f;
+    float fx = (float)x + 0.5f, fy = (float)y + 0.5f;
+    const float fz = 0.5f;
+#ifndef SAIL_REMAT_FRAGCOORD
+    // Opaque to the compiler: otherwise ptxas re-derives fx from %tid / %ctaid in every bounce (9 issue slots) instead of
+    // keeping one register (or one local-memory word) alive.
+    asm volatile("" : "+f"(fx), "+f"(fy));
+#endif
     const float a = fx * L.rcpW, b = fy * L.rcpH;
 
     V3 c = mk3(L.accum[3 * pix], L.accum[3 * pix + 1], L.accum[3 * pix + 2]);

@@ -77,7 +77,7 @@ SD void sailServerBody(const SailLaunch& L) {
                             writeAov(aov, h.n, h.p, id, t);
                         }
                         V3 wi = splat3(0.0f), _fpdf = splat3(0.0f), contrib, o = splat3(0.0f);
-                        if (deepth == L.maxBounces && lastBounceIsEmissionOnly<F>(h)) {  // see tracePath(): dead BSDF sample
+                        if (SAIL_IS_LAST_BOUNCE(deepth, L.maxBounces) && lastBounceIsEmissionOnly<F>(h)) {  // see tracePath(): dead BSDF sample
                             contrib = h.emission + splat3(0.0f);
                         } else {
                             contrib = shade<F>(sc, h, u, -ray.d, wi, _fpdf, SAIL_JIT_MATS_OFF);
@@ -134,10 +134,10 @@ SD void sailServerBody(const SailLaunch& L) {
                     alive = false;
                 }
                 // last bounce on an object that neither emits nor gets NEE: adds +0 to e (see tracePath())
-                if (alive && deepth == L.maxBounces && !(deepth == 1 && aov.on) && !lastBounceNeedsRecord<F>(sc.shape[nr.id])) alive = false;
+                if (alive && SAIL_IS_LAST_BOUNCE(deepth, L.maxBounces) && !(deepth == 1 && aov.on) && !lastBounceNeedsRecord<F>(sc.shape[nr.id])) alive = false;
             }
             const float seed = f.timeSinceStart + (float)deepth;
-            const bool lastNoNee = deepth == L.maxBounces && !(F & SAIL_F_NEE);  // warp-uniform: nobody needs the RNG pair
+            const bool lastNoNee = SAIL_IS_LAST_BOUNCE(deepth, L.maxBounces) && !(F & SAIL_F_NEE);  // warp-uniform: nobody needs the RNG pair
             const V2 u = lastNoNee ? mk2(0.0f, 0.0f) : random2<F>(fx, fy, fz, seed);
             const bool off = alive && srvOffloaded(sc.shape[alive ? nr.id : 0].category);
             const unsigned m = __ballot_sync(0xffffffffu, off);
@@ -163,7 +163,7 @@ SD void sailServerBody(const SailLaunch& L) {
                 Hit h;
                 hitRecord<F, 1>(sc, nr.id, nr.t, ray, h);
                 if (deepth == 1 && aov.on) writeAov(aov, h.n, h.p, h.index, h.d);
-                if (deepth == L.maxBounces && lastBounceIsEmissionOnly<F>(h)) {
+                if (SAIL_IS_LAST_BOUNCE(deepth, L.maxBounces) && lastBounceIsEmissionOnly<F>(h)) {
                     e = e + (h.emission + splat3(0.0f)) * fpdf;
                 } else {
                     V3 wi, _fpdf;

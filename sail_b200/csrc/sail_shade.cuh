@@ -516,6 +516,14 @@ SD void writeAov(const AovSink& a, V3 n, V3 p, int id, float t) {
     a.depth[a.pix] = t;
 }
 
+// The last-bounce reductions of tracePath() hang on this test.  -DSAIL_LITERAL_LAST_BOUNCE (SAIL_B200_JIT_DEFINES) turns them
+// off: every bounce is then evaluated in full like the reference's loop -- same image, bit for bit; bench.py reports that rate too.
+#ifdef SAIL_LITERAL_LAST_BOUNCE
+#define SAIL_IS_LAST_BOUNCE(d, maxB) false
+#else
+#define SAIL_IS_LAST_BOUNCE(d, maxB) ((d) == (maxB))
+#endif
+
 // True when shade() of this hit reduces to `emission + BLACK` (path.glsl:10: NEE only for non-emissive matte hits).
 template <int F>
 SD bool lastBounceIsEmissionOnly(const Hit& h) {
@@ -541,7 +549,7 @@ SD V3 tracePath(const SceneView& sc, Ray ray, int maxBounces, float fx, float fy
     while (deepth++ < maxBounces) {
         // Last bounce without NEE: only a hit on an emissive object adds anything (below).  If the ray does not even
         // touch one, the nearest-hit scan over the other objects is dead code as well.
-        if (!(F & SAIL_F_NEE) && deepth == maxBounces && !(deepth == 1 && aov.on) && !touchesMasked<F>(sc, ray, sc.emissive)) break;
+        if (!(F & SAIL_F_NEE) && SAIL_IS_LAST_BOUNCE(deepth, maxBounces) && !(deepth == 1 && aov.on) && !touchesMasked<F>(sc, ray, sc.emissive)) break;
         const Nearest nr = nearestObject<F>(sc, ray);
         if (nr.id < 0) {
             if (deepth == 1 && aov.on) writeAov(aov, splat3(0.0f), splat3(0.0f), nr.id, nr.t);
@@ -549,7 +557,7 @@ SD V3 tracePath(const SceneView& sc, Ray ray, int maxBounces, float fx, float fy
         }
         // Last bounce, object without emission (and no NEE for it): the hit adds (BLACK + BLACK) * fpdf = +0 to `e`
         // (fpdf is a product of values clamped to [0, 1]; `e` is never -0), so not even its hit record is needed.
-        if (deepth == maxBounces && !(deepth == 1 && aov.on) && !lastBounceNeedsRecord<F>(sc.shape[nr.id])) break;
+        if (SAIL_IS_LAST_BOUNCE(deepth, maxBounces) && !(deepth == 1 && aov.on) && !lastBounceNeedsRecord<F>(sc.shape[nr.id])) break;
         Hit h;
         hitRecord<F>(sc, nr.id, nr.t, ray, h);
         if (deepth == 1 && aov.on) writeAov(aov, h.n, h.p, h.index, h.d);
@@ -558,7 +566,7 @@ SD V3 tracePath(const SceneView& sc, Ray ray, int maxBounces, float fx, float fy
         // for non-emissive matte hits with lights present (path.glsl:10), so everywhere else the RNG pair, the shading
         // frame and the BSDF sample are dead code on this bounce and are not evaluated; what is added to `e` is the same
         // expression, `(emission + 0) * fpdf`.
-        if (deepth == maxBounces && lastBounceIsEmissionOnly<F>(h)) {
+        if (SAIL_IS_LAST_BOUNCE(deepth, maxBounces) && lastBounceIsEmissionOnly<F>(h)) {
             e = e + (h.emission + splat3(0.0f)) * fpdf;
             break;
         }
@@ -566,7 +574,7 @@ SD V3 tracePath(const SceneView& sc, Ray ray, int maxBounces, float fx, float fy
         V2 u = random2<F>(fx, fy, fz, seed);
         V3 wi, _fpdf;
         e = e + shade<F>(sc, h, u, -ray.d, wi, _fpdf) * fpdf;
-        if (deepth == maxBounces) break;
+        if (SAIL_IS_LAST_BOUNCE(deepth, maxBounces)) break;
         fpdf = fpdf * _fpdf;
         float outdot = dot3(h.n, wi);
         ray.o = h.p + h.n * (outdot > SAIL_EPSILON ? 0.0001f : -0.0001f);

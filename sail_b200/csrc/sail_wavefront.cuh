@@ -78,7 +78,7 @@ SD void sailWaveBody(const SailLaunch& L) {
             if (deepth == 1) { firstId = nr.id; firstT = nr.t; }  // still on the home lane
             if (nr.id < 0) alive = false;                          // path.glsl:22 `break`
             // last bounce on an object that neither emits nor gets NEE: adds +0 to e (see tracePath()), the path is done
-            if (alive && deepth == L.maxBounces && deepth > 1 && !lastBounceNeedsRecord<F>(sc.shape[nr.id])) alive = false;
+            if (alive && SAIL_IS_LAST_BOUNCE(deepth, L.maxBounces) && deepth > 1 && !lastBounceNeedsRecord<F>(sc.shape[nr.id])) alive = false;
             float t = nr.t;
             int id = alive ? nr.id : -1;
             // Primary rays of a tile are coherent already; regroup from the second bounce on.
@@ -120,7 +120,7 @@ SD void sailWaveBody(const SailLaunch& L) {
                     firstHit[0][home] = h.n.x; firstHit[1][home] = h.n.y; firstHit[2][home] = h.n.z;
                     firstHit[3][home] = h.p.x; firstHit[4][home] = h.p.y; firstHit[5][home] = h.p.z;
                 }
-                if (deepth == L.maxBounces && lastBounceIsEmissionOnly<F>(h)) {  // see tracePath(): dead BSDF sample
+                if (SAIL_IS_LAST_BOUNCE(deepth, L.maxBounces) && lastBounceIsEmissionOnly<F>(h)) {  // see tracePath(): dead BSDF sample
                     e = e + (h.emission + splat3(0.0f)) * fpdf;
                 } else {
                     const float seed = f.timeSinceStart + (float)deepth;
