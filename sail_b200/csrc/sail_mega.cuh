@@ -144,7 +144,11 @@ SD void sailMegaBody(const SailLaunch& L) {
         ray.o = ld3(f.eye);
         ray.d = primaryDir(f, a, b);
         aov.on = L.writeAov && k == L.nframes - 1;  // the AOVs of a launch are those of its last frame
-        V3 e = tracePath<F>(sc, ray, L.maxBounces, fx, fy, fz, f.timeSinceStart, aov);
+        float tss = f.timeSinceStart;
+#ifndef SAIL_RELOAD_TIME
+        asm volatile("" : "+f"(tss));  // one register instead of three uniform-path instructions per bounce to re-read it
+#endif
+        V3 e = tracePath<F>(sc, ray, L.maxBounces, fx, fy, fz, tss, aov);
         e = mk3(nanToZero(e.x), nanToZero(e.y), nanToZero(e.z));
         if (L.accumMode == 0) c = mix3(e, c, f.textureWeight);  // fstrace.glsl:14
         else c = c + e;
