@@ -175,6 +175,15 @@ int sail_scale_accum(sail_ctx* ctx, float s);
  * (what the canvas would hold: clamped to [0,1], rounded to 8 bits). */
 int sail_present(sail_ctx* ctx, float* rgba_f32, uint8_t* rgba8);
 
+/* The same display pass as a swapchain of two, for hosts that keep rendering while an image travels to the host -- what the
+ * browser's compositor does with the canvas of src/core/renderer.js:63 between two requestAnimationFrame callbacks
+ * (ui/ui.js:67-70).  sail_present_begin() queues the display filter behind the frames rendered so far and starts the
+ * device-to-host copy of the RGBA8 image on a second stream; it does not wait, and the next sail_render*() may be issued
+ * at once (it overlaps the copy).  sail_present_end() waits until `rgba8` (page-locked memory from sail_alloc_host for a
+ * truly asynchronous copy) holds the image.  One image in flight per context: begin, end, begin, end ... */
+int sail_present_begin(sail_ctx* ctx, uint8_t* rgba8);
+int sail_present_end(sail_ctx* ctx);
+
 /* Device-side handles for hosts that combine buffers across GPUs themselves (torch.distributed / NCCL on
  * the host side): raw device pointers of the full-image buffers and the CUDA stream (cudaStream_t). */
 void* sail_device_ptr(sail_ctx* ctx, int32_t which);

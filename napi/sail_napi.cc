@@ -137,6 +137,23 @@ static napi_value Present(napi_env env, napi_callback_info info) {
     NAPI_OK(napi_create_typedarray(env, napi_uint8_clamped_array, bytes, buf, 0, &out));
     return out;
 }
+// presentBegin(handle, Uint8ClampedArray out) / presentEnd(handle): the display pass as a swapchain of two -- the caller keeps
+// `out` alive and does not read it before presentEnd() returns; the next render() may be issued in between.
+static napi_value PresentBegin(napi_env env, napi_callback_info info) {
+    size_t argc = 2; napi_value a[2];
+    NAPI_OK(napi_get_cb_info(env, info, &argc, a, nullptr, nullptr));
+    sail_ctx* ctx = handle(env, a[0]);
+    napi_typedarray_type type; napi_value buf; size_t off, len; void* data = nullptr;
+    NAPI_OK(napi_get_typedarray_info(env, a[1], &type, &len, &data, &buf, &off));
+    check(env, ctx, sail_present_begin(ctx, (uint8_t*)data));
+    return nullptr;
+}
+static napi_value PresentEnd(napi_env env, napi_callback_info info) {
+    size_t argc = 1; napi_value a[1];
+    NAPI_OK(napi_get_cb_info(env, info, &argc, a, nullptr, nullptr));
+    check(env, handle(env, a[0]), sail_present_end(handle(env, a[0])));
+    return nullptr;
+}
 // readAov(handle, which, Float32Array|Int32Array out)        [gl.readPixels on frameCache[i]]
 static napi_value ReadAov(napi_env env, napi_callback_info info) {
     size_t argc = 3; napi_value a[3];
@@ -159,6 +176,8 @@ static napi_value Init(napi_env env, napi_value exports) {
         {"uploadObjects", nullptr, UploadObjects, nullptr, nullptr, nullptr, napi_default, nullptr},
         {"render", nullptr, Render, nullptr, nullptr, nullptr, napi_default, nullptr},
         {"present", nullptr, Present, nullptr, nullptr, nullptr, napi_default, nullptr},
+        {"presentBegin", nullptr, PresentBegin, nullptr, nullptr, nullptr, napi_default, nullptr},
+        {"presentEnd", nullptr, PresentEnd, nullptr, nullptr, nullptr, napi_default, nullptr},
         {"readAov", nullptr, ReadAov, nullptr, nullptr, nullptr, napi_default, nullptr},
     };
     napi_define_properties(env, exports, sizeof(d) / sizeof(d[0]), d);

@@ -69,6 +69,8 @@ _SIGNATURES = {
     "sail_write_accum": (ctypes.c_int, [_P, _P, ctypes.c_size_t]),
     "sail_scale_accum": (ctypes.c_int, [_P, ctypes.c_float]),
     "sail_present": (ctypes.c_int, [_P, _P, _P]),
+    "sail_present_begin": (ctypes.c_int, [_P, _P]),
+    "sail_present_end": (ctypes.c_int, [_P]),
     "sail_device_ptr": (_P, [_P, ctypes.c_int32]),
     "sail_stream": (_P, [_P]),
     "sail_intersect_rays": (ctypes.c_int, [_P, _P, ctypes.c_int32, _P, _P, _P, _P]),
@@ -289,6 +291,17 @@ class Context:
         if both:
             return f32, u8
         return u8 if as_u8 else f32
+
+    def present_begin(self, slot):
+        """Queue the display pass and start the asynchronous copy of the RGBA8 image into page-locked buffer ``slot``
+        (0 or 1); returns that buffer, valid after ``present_end()``."""
+        H, W = self.height, self.width
+        buf = self.host_buffer((2, H, W, 4), np.uint8)[slot]
+        self._check(self.lib.sail_present_begin(self._h, buf.ctypes.data_as(ctypes.c_void_p)))
+        return buf
+
+    def present_end(self):
+        self._check(self.lib.sail_present_end(self._h))
 
     def device_ptr(self, which):
         return self.lib.sail_device_ptr(self._h, which)

@@ -26,6 +26,10 @@ struct sail_ctx {
     int bandRows = 0, bandStride = 1, bandFirst = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t evStart = nullptr, evStop = nullptr;
+    // double-buffered display (sail_present_begin / _end): copy stream, filter-done and copy-done events
+    cudaStream_t copyStream = nullptr;
+    cudaEvent_t evPresented = nullptr, evCopied = nullptr;
+    bool copyInFlight = false, copiedOnce = false;
     bool timed = false;
     sail_config cfg;
     bool sceneLoaded = false;
@@ -207,6 +211,9 @@ int sail_create(const sail_create_info* info, sail_ctx** out) {
     CU(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     CU(cudaEventCreate(&ctx->evStart));
     CU(cudaEventCreate(&ctx->evStop));
+    CU(cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&ctx->evPresented, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&ctx->evCopied, cudaEventDisableTiming));
     size_t n = npix(ctx);
     CU(cudaMalloc(&ctx->dScene, sizeof(SailSceneBlock)));
     CU(cudaMalloc(&ctx->accum, n * 3 * sizeof(float)));
@@ -223,11 +230,15 @@ void sail_destroy(sail_ctx* ctx) {
     if (ctx->stream) {
         cudaSetDevice(ctx->device);
         cudaStreamSynchronize(ctx->stream);
+        if (ctx->copyStream) cudaStreamSynchronize(ctx->copyStream);
     }
     cudaFree(ctx->dScene); cudaFree(ctx->accum); cudaFree(ctx->normal); cudaFree(ctx->position);
     cudaFree(ctx->depth); cudaFree(ctx->hitId); cudaFree(ctx->presentF32); cudaFree(ctx->presentU8);
     if (ctx->evStart) cudaEventDestroy(ctx->evStart);
     if (ctx->evStop) cudaEventDestroy(ctx->evStop);
+    if (ctx->evPresented) cudaEventDestroy(ctx->evPresented);
+    if (ctx->evCopied) cudaEventDestroy(ctx->evCopied);
+    if (ctx->copyStream) cudaStreamDestroy(ctx->copyStream);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -498,12 +509,59 @@ int sail_scale_accum(sail_ctx* ctx, float s) {
     return SAIL_OK;
 }
 
+namespace {
+void fillPresentParams(sail_ctx* ctx, PresentParams& P) {
+    P.W = ctx->W; P.H = ctx->H;
+    P.filter_id = ctx->cfg.filter_id;
+    P.gamma_c = ctx->cfg.filter_gamma_c;
+    P.radius[0] = ctx->cfg.filter_radius[0]; P.radius[1] = ctx->cfg.filter_radius[1];
+    memcpy(P.weights, ctx->cfg.filter_weights, sizeof(P.weights));
+    P.color = ctx->accum; P.normal = ctx->normal; P.position = ctx->position;
+    P.out_f32 = nullptr;
+    P.out_u8 = nullptr;
+}
+}  // namespace
+
+int sail_present_begin(sail_ctx* ctx, uint8_t* rgba8) {
+    if (!ctx || !ctx->accum || !rgba8) return SAIL_ERR_INVALID;
+    if (ctx->copyInFlight) return setErr(ctx, SAIL_ERR_STATE, "sail_present_begin: the previous image has not been collected with sail_present_end");
+    CU(cudaSetDevice(ctx->device));
+    size_t n = npix(ctx);
+    if (!ctx->presentU8) CU(cudaMalloc(&ctx->presentU8, n * 4));
+    PresentParams P;
+    fillPresentParams(ctx, P);
+    P.out_u8 = ctx->presentU8;
+    // the filter overwrites the device image: it must not overtake the previous copy (long finished in practice)
+    if (ctx->copiedOnce) CU(cudaStreamWaitEvent(ctx->stream, ctx->evCopied, 0));
+    dim3 grid((ctx->W + 31) / 32, (ctx->H + 7) / 8);
+    sail_present_kernel<<<grid, 256, 0, ctx->stream>>>(P);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(ctx->evPresented, ctx->stream));
+    CU(cudaStreamWaitEvent(ctx->copyStream, ctx->evPresented, 0));
+    CU(cudaMemcpyAsync(rgba8, ctx->presentU8, n * 4, cudaMemcpyDeviceToHost, ctx->copyStream));
+    CU(cudaEventRecord(ctx->evCopied, ctx->copyStream));
+    ctx->copyInFlight = true;
+    ctx->copiedOnce = true;
+    return SAIL_OK;
+}
+
+int sail_present_end(sail_ctx* ctx) {
+    if (!ctx) return SAIL_ERR_INVALID;
+    if (!ctx->copyInFlight) return setErr(ctx, SAIL_ERR_STATE, "sail_present_end without sail_present_begin");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaEventSynchronize(ctx->evCopied));
+    ctx->copyInFlight = false;
+    return SAIL_OK;
+}
+
 int sail_present(sail_ctx* ctx, float* rgba_f32, uint8_t* rgba8) {
     if (!ctx || !ctx->accum) return SAIL_ERR_INVALID;
     CU(cudaSetDevice(ctx->device));
     size_t n = npix(ctx);
     if (rgba_f32 && !ctx->presentF32) CU(cudaMalloc(&ctx->presentF32, n * 4 * sizeof(float)));
     if (rgba8 && !ctx->presentU8) CU(cudaMalloc(&ctx->presentU8, n * 4));
+    if (rgba8 && ctx->copyInFlight) return setErr(ctx, SAIL_ERR_STATE, "sail_present while a sail_present_begin image is in flight");
     PresentParams P;
     P.W = ctx->W; P.H = ctx->H;
     P.filter_id = ctx->cfg.filter_id;

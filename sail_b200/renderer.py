@@ -104,6 +104,27 @@ class Renderer:
         self.trace(scene, frames)
         return self.ctx.present(as_u8=as_u8, pinned=True)
 
+    def render_pipelined(self, scene, frames=1):
+        """``render`` with a swapchain of two: the display pass and the device-to-host copy of THIS call's image are only
+        queued (sail_present_begin), and the image of the PREVIOUS call -- complete by now, its copy overlapped this call's
+        tracing -- is returned (``None`` on the first call).  ``flush()`` returns the last image.  This is the pacing of the
+        reference's loop: ``renderer.render(scene)`` per requestAnimationFrame, the canvas reaching the screen a frame later
+        (ui/ui.js:67-70)."""
+        self.trace(scene, frames)
+        prev = self.flush()
+        self._slot = 1 - getattr(self, "_slot", 1)
+        self._inflight = self.ctx.present_begin(self._slot)
+        return prev
+
+    def flush(self):
+        """Wait for the image queued by the last ``render_pipelined`` and return it (``None`` if there is none)."""
+        buf = getattr(self, "_inflight", None)
+        if buf is None:
+            return None
+        self.ctx.present_end()
+        self._inflight = None
+        return buf
+
     def save(self, path, img=None):
         """Write the displayed image (``img`` or a fresh display pass of the current accumulation) as .png or .ppm --
         the headless stand-in for the canvas of renderer.js:63."""

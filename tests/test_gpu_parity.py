@@ -316,6 +316,34 @@ def test_tile_rows_and_sum_mode(capi, oracle, kernel):
     assert np.all(np.abs(summed - want) <= 1e-5 * np.maximum(1.0, np.abs(want)))
 
 
+def test_pipelined_present_equals_synchronous(capi):
+    """Renderer.render_pipelined (sail_present_begin / _end: display double-buffered, the copy overlapping the next
+    trace) returns, one call late, exactly the images Renderer.render returns."""
+    from sail_b200.renderer import Renderer
+    W, H = 96, 64
+    want = []
+    scene, _, _, _, _ = scene_tables(2, W, H)
+    r = Renderer((W, H))
+    r.update(scene)
+    for _ in range(4):
+        want.append(np.array(r.render(scene, frames=3)))
+    r.close()
+    scene, _, _, _, _ = scene_tables(2, W, H)
+    r = Renderer((W, H))
+    r.update(scene)
+    got = []
+    for _ in range(4):
+        img = r.render_pipelined(scene, frames=3)
+        if img is not None:
+            got.append(np.array(img))
+    with pytest.raises(capi.SailError):
+        r.ctx.present(as_u8=True)  # an image is in flight: the synchronous display pass would overwrite it
+    got.append(np.array(r.flush()))
+    assert r.flush() is None
+    r.close()
+    assert len(got) == 4 and all(np.array_equal(a, b) for a, b in zip(got, want))
+
+
 def test_unit_domain_math(capi):
     """sail_selftest_math: dm_rcp on all 2^32 inputs; sqrtUnit == sqrt.rn for 0 and every float in [2^-100, FLT_MAX];
     sincosUnit == dm_sincos for every float in [-8, 8] (the domain-restricted helpers of the cosine sampler)."""
