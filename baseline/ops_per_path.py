@@ -37,7 +37,8 @@ if __name__ == "__main__":
            "config1_512": count(configs.config1, frames),
            "config2_1080p": count(configs.config2, max(1, frames // 4)),
            "config3_1080p": count(configs.config3, max(1, frames // 4)),
-           "config5_1080p": count(configs.config5, max(1, frames // 8))}
+           "config5_1080p": count(configs.config5, max(1, frames // 8)),
+           "config4_2160p": count(configs.config4, max(1, frames // 8))}
     with open(os.path.join(ROOT, "baseline", "ops_per_path.json"), "w") as f:
         json.dump(out, f, indent=1)
     print(json.dumps(out, indent=1))

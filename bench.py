@@ -47,7 +47,8 @@ def peaks():
 
 
 def ops_per_path():
-    key = {"cornell": "cornell_1080p", "config2": "config2_1080p", "config3": "config3_1080p", "config5": "config5_1080p"}[_workload]
+    key = {"cornell": "cornell_1080p", "config2": "config2_1080p", "config3": "config3_1080p", "config5": "config5_1080p",
+           "config4": "config4_2160p"}[_workload]
     with open(os.path.join(ROOT, "baseline", "ops_per_path.json")) as f:
         return float(json.load(f)[key]["ops_per_path"])
 
@@ -97,7 +98,8 @@ class ClockSampler:
 WORKLOADS = {"cornell": ("cornell_1080p", WORKLOAD),
              "config2": ("config2", "materials demo (mirror/glass/metal/matte spheres, area light) 1920x1080, 5 bounces"),
              "config3": ("config3", "quadrics + textures + area/point/spot lights 1920x1080, 5 bounces"),
-             "config5": ("config5", "glass + metal spheres 1920x1080, 16 bounces")}
+             "config5": ("config5", "glass + metal spheres 1920x1080, 16 bounces"),
+             "config4": ("config4", "Cornell box 3840x2160, 5 bounces, sample-sharded across the GPUs (BASELINE config 4)")}
 _workload = "cornell"
 
 
