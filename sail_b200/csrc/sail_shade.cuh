@@ -63,7 +63,7 @@ SD V2 random2(float fx, float fy, float fz, float seed) {
 // ---- util/sampler.glsl ---------------------------------------------------------------------------
 SD V3 uniformSampleSphere(V2 u) {
     float z = 1.0f - 2.0f * u.x;
-    float r = dm_sqrt(1.0f - z * z);
+    float r = sqrtUnit(1.0f - z * z);  // z = 1 - 2u in [-1, 1]: the argument is 0 or >= 2^-24 (see sinTheta)
     float2 sc2 = sail_sincos(SAIL_TWO_PI * u.y);
     float s = sc2.x, c = sc2.y;
     return mk3(r * c, r * s, z);
@@ -99,7 +99,9 @@ SD V2 concentricSampleDisk(V2 u) {
 SD float absCosTheta(V3 w) { return dm_abs(w.z); }
 SD float cos2Theta(V3 w) { return w.z * w.z; }
 SD float sin2Theta(V3 w) { return fmax2(0.0f, 1.0f - cos2Theta(w)); }
-SD float sinTheta(V3 w) { return dm_sqrt(sin2Theta(w)); }
+// max(0, 1 - c*c) is 0, or >= 2^-24: for c*c in [1/2, 1] the subtraction is exact, a multiple of 2^-24; below 1/2 the result
+// exceeds 1/2; above 1, infinite or NaN it is clamped to 0 (FMNMX returns the non-NaN operand).  So sqrtUnit's domain holds.
+SD float sinTheta(V3 w) { return sqrtUnit(sin2Theta(w)); }
 SD bool equalZero(float x) { return x < 1e-3f && x > -1e-3f; }
 SD float tan2Theta(V3 w) {
     float c2 = cos2Theta(w);
@@ -119,10 +121,10 @@ SD bool sameHemisphere(V3 w, V3 wp) { return w.z * wp.z > SAIL_EPSILON; }
 // ---- material/fresnel.glsl:31-70 -------------------------------------------------------------------
 SD float frDielectric(float cosThetaI, float etaI, float etaT) {
     cosThetaI = fclamp(cosThetaI, -1.0f, 1.0f);
-    float sinThetaI = dm_sqrt(fmax2(0.0f, 1.0f - cosThetaI * cosThetaI));
+    float sinThetaI = sqrtUnit(fmax2(0.0f, 1.0f - cosThetaI * cosThetaI));  // domain: see sinTheta()
     float sinThetaT = fdiv(etaI, etaT) * sinThetaI;
     if (sinThetaT >= 1.0f) return 1.0f;
-    float cosThetaT = dm_sqrt(fmax2(0.0f, 1.0f - sinThetaT * sinThetaT));
+    float cosThetaT = sqrtUnit(fmax2(0.0f, 1.0f - sinThetaT * sinThetaT));
     float TI = etaT * cosThetaI, IT = etaI * cosThetaT, II = etaI * cosThetaI, TT = etaT * cosThetaT;
     float Rparl = fdiv(TI - IT, TI + IT);
     float Rperp = fdiv(II - TT, II + TT);
@@ -169,7 +171,7 @@ SD V3 trowbridgeReitz_sample_wh(V2 u, float alphax, float alphay, V3 wo) {
         float tanTheta2 = fdiv(alpha2 * u.x, 1.0f - u.x);
         cosTheta_ = dm_rcp(dm_sqrt(1.0f + tanTheta2));
     }
-    float sinTheta_ = dm_sqrt(fmax2(0.0f, 1.0f - cosTheta_ * cosTheta_));
+    float sinTheta_ = sqrtUnit(fmax2(0.0f, 1.0f - cosTheta_ * cosTheta_));
     float2 scw = sail_sincos(phi);
     float sp = scw.x, cp = scw.y;
     V3 wh = mk3(sinTheta_ * cp, sinTheta_ * sp, cosTheta_);  // sphericalDirection, utility.glsl:53-56
