@@ -123,6 +123,28 @@ def test_scene_specialised_kernels_compile_without_a_gpu(capi, cfg):
         assert info.startswith("jit ") and "n=%d" % o.shape[0] in info and "cubin" in info, info
 
 
+def test_kernel_build_knobs_compile(capi, monkeypatch):
+    """The knobs sail_jit.cpp reads from the environment when it builds a kernel: extra #defines (the literal last bounce
+    that bench.py reports next to the default), the wavefront's paths per CTA, the server kernel's path warps."""
+    _, o, t, l, _ = scene_tables(3, 64, 64)
+    try:
+        monkeypatch.setenv("SAIL_B200_JIT_DEFINES", "SAIL_LITERAL_LAST_BOUNCE")
+        assert "-DSAIL_LITERAL_LAST_BOUNCE" in capi.jit_compile_check(o, t, l, capi.KERNEL_MEGA)
+        monkeypatch.delenv("SAIL_B200_JIT_DEFINES")
+        assert "512 paths" in capi.jit_compile_check(o, t, l, capi.KERNEL_WAVEFRONT)  # quadric scene: the measured default
+        monkeypatch.setenv("SAIL_B200_WF_THREADS", "256")
+        assert "256 paths" in capi.jit_compile_check(o, t, l, capi.KERNEL_WAVEFRONT)
+        monkeypatch.setenv("SAIL_B200_WF_THREADS", "100")
+        with pytest.raises(capi.SailError):
+            capi.jit_compile_check(o, t, l, capi.KERNEL_WAVEFRONT)
+        monkeypatch.setenv("SAIL_B200_SRV_WARPS", "3")
+        assert "3+1 warps" in capi.jit_compile_check(o, t, l, capi.KERNEL_SERVER)
+    except capi.SailError as e:
+        if "NVRTC not found" in str(e):
+            pytest.skip("no NVRTC on this machine")
+        raise
+
+
 def test_scene_specialisation_limits(capi):
     """A run of equal shapes stays one loop (64 spheres compile); more than 16 runs of distinct shapes are refused, which
     makes the library use its ahead-of-time variant."""
