@@ -22,6 +22,35 @@ class Renderer {
         return native.present(this.ctx.handle, this.ctx.width, this.ctx.height);
     }
 
+    // render() with the display double-buffered (sail_present_begin / _end): queues this frame's display pass and its copy to
+    // the host, returns the PREVIOUS frame's pixels (null on the first call) -- the copy overlaps the next frame's tracing,
+    // like the canvas reaching the screen one requestAnimationFrame later (ui/ui.js:67-70).  flush() returns the last frame.
+    renderPipelined(scene) {
+        if (scene.moving) {
+            scene.sampleCount = 0;
+            this.updateObjects(scene);
+        }
+        this.tracer.render(scene.mat, scene.eye, scene.sampleCount++);
+        const prev = this.flush();
+        if (!this.frames) {
+            const bytes = this.ctx.width * this.ctx.height * 4;
+            this.frames = [new Uint8ClampedArray(bytes), new Uint8ClampedArray(bytes)];
+            this.slot = 1;
+        }
+        this.slot = 1 - this.slot;
+        native.presentBegin(this.ctx.handle, this.frames[this.slot]);
+        this.inflight = this.frames[this.slot];
+        return prev;
+    }
+
+    flush() {
+        if (!this.inflight) return null;
+        native.presentEnd(this.ctx.handle);
+        const done = this.inflight;
+        this.inflight = null;
+        return done;
+    }
+
     destroy() { native.destroy(this.ctx.handle); }
 }
 
