@@ -205,7 +205,12 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
     if (kind == 2) snprintf(head, sizeof(head), "jit server<F=%d,%d+1 warps> n=%d shapes=", F, pathWarps, n);
     else if (kind == 1 && block != 128) snprintf(head, sizeof(head), "jit wavefront<F=%d,%u paths> n=%d shapes=", F, block, n);
     else snprintf(head, sizeof(head), "jit %s<F=%d> n=%d shapes=", kindName, F, n);
-    const std::string key = extraDefs + "dev" + std::to_string(device) + " m" + std::to_string(minCtas) + " " + head + cats + masks;
+    // One shared sqrt instead of ~50 inlined copies: pays for quadric kernels that overflow the 32 KB instruction cache (megakernel,
+    // 128-path wavefront: config 3 +5..16 %), costs 3.7 % once the 512-path wavefront has taken that pressure away (2318 vs 2404
+    // Mpaths/s); metal/glass-only kernels are faster inlined.  SAIL_B200_INLINE_SQRT=0/1 overrides for A/B runs.
+    bool outlineSqrt = (F & 1 /* SAIL_F_QUADRICS */) && !(kind == 1 && block >= 256);
+    if (const char* e = getenv("SAIL_B200_INLINE_SQRT")) outlineSqrt = e[0] == '0';
+    const std::string key = extraDefs + (outlineSqrt ? "osqrt " : "") + "dev" + std::to_string(device) + " m" + std::to_string(minCtas) + " " + head + cats + masks;
     auto it = g_cache.find(key);
     out->block = block;
     out->pathWarps = pathWarps;
@@ -224,9 +229,7 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
              "{ %s<%d>(L); }\n",
              extraDefs.c_str(), nruns, runCat.c_str(), runStart.c_str(), runLen.c_str(), shapes, mats, texs, lights, glass, matte, tr, matsBox, matsOff,
              pathWarps ? pathWarps : 7, kind == 1 ? block : 128u,
-             // quadric scenes: the kernel is 2x the 32 KB instruction cache, one shared sqrt pays (config 3: +5..16 %); the
-             // metal/glass-only kernels are faster with it inlined (measured, tools/bench_outline.sh history)
-             (F & 1 /* SAIL_F_QUADRICS */) ? "#define SAIL_OUTLINE_SQRT 1\n" : "", block, minCtas,
+             outlineSqrt ? "#define SAIL_OUTLINE_SQRT 1\n" : "", block, minCtas,
              kind == 2 ? "sailServerBody" : (kind ? "sailWaveBody" : "sailMegaBody"), F);
     void* prog = nullptr;
     if (g_api.createProgram(&prog, src, "sail_jit.cu", kSailJitCount, kSailJitTexts, kSailJitNames) != 0) {
