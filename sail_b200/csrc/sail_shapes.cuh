@@ -96,7 +96,11 @@ static __device__ __noinline__ float2 sail_sincos(float x) { float s, c; dm_sinc
 static __device__ __noinline__ float sail_acos(float x) { return dm_acos(x); }
 static __device__ __noinline__ float sail_atan2(float y, float x) { return dm_atan2(y, x); }
 // Single-use sites of the small variants are inlined instead (no call overhead, code still fits the I-cache).
+#ifdef SAIL_INLINE_TRANSCENDENTALS  // sail_jit.cpp / SAIL_B200_JIT_DEFINES: inline them in a big kernel too
+#define SAIL_SMALL(F) 1
+#else
 #define SAIL_SMALL(F) (!((F) & (SAIL_F_GLOSSY | SAIL_F_QUADRICS | SAIL_F_NEE)))
+#endif
 // dm_sincos for |x| < 2^22 (the caller passes 2*pi*u, u in [0, 1]): its out-of-range arm is unreachable and dropped, and the
 // sine and cosine polynomials, which share z = r*r, advance as one packed pair (FFMA2 / FMUL2).  Every operation and its
 // order are those of dm_sin_kernel / dm_cos_kernel, so the result equals dm_sincos(x) bit for bit
