@@ -219,6 +219,10 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
         snprintf(out->info, sizeof(out->info), "%s%s%s (cached)", head, cats.c_str(), masks);
         return 0;
     }
+    std::string tuning = outlineSqrt ? "#define SAIL_OUTLINE_SQRT 1\n" : "#define SAIL_INLINE_TRANSCENDENTALS 1\n";
+    // small scenes without quadrics: the nearest-hit scan inlined at both call sites (path ray, shadow ray) instead of one shared
+    // out-of-line copy -- config 5 +2.8 %, config 2 +-0; with quadrics the scan is too large (config 3 -23 %)
+    if (!(F & 1 /* SAIL_F_QUADRICS */) && n <= 8) tuning += "#define SAIL_INLINE_SCAN 1\n";
     char src[4096];
     snprintf(src, sizeof(src),
              "%s#define SAIL_JIT_NRUNS %d\n#define SAIL_JIT_RUN_CATS %s\n#define SAIL_JIT_RUN_STARTS %s\n#define SAIL_JIT_RUN_LENS %s\n"
@@ -231,7 +235,7 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
              pathWarps ? pathWarps : 7, kind == 1 ? block : 128u,
              // kernels that are not instruction-cache bound also inline the sines of the RNG, the sampler's sincos and the sphere's
              // acos / sin (measured: config 2 +2.2 %, config 5 +2.9 %, config 3 +0.5 %)
-             outlineSqrt ? "#define SAIL_OUTLINE_SQRT 1\n" : "#define SAIL_INLINE_TRANSCENDENTALS 1\n", block, minCtas,
+             tuning.c_str(), block, minCtas,
              kind == 2 ? "sailServerBody" : (kind ? "sailWaveBody" : "sailMegaBody"), F);
     void* prog = nullptr;
     if (g_api.createProgram(&prog, src, "sail_jit.cu", kSailJitCount, kSailJitTexts, kSailJitNames) != 0) {

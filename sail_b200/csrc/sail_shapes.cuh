@@ -428,6 +428,9 @@ static __device__ __noinline__ Nearest nearestObjectRegs(unsigned scAddr, float 
 // shadow rays are a second site and one out-of-line copy serves both (I-cache footprint).
 template <int F>
 SD Nearest nearestObject(const SceneView& sc, const Ray& ray) {
+#ifdef SAIL_INLINE_SCAN  // A/B knob: two inlined copies (path ray, shadow ray) instead of one shared out-of-line copy
+    return nearestObjectInline<F>(sc, ray);
+#endif
     if (!(F & SAIL_F_NEE)) return nearestObjectInline<F>(sc, ray);
     return nearestObjectRegs<F>((unsigned)__cvta_generic_to_shared(reinterpret_cast<const unsigned char*>(sc.shape) - 16), ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z);
 }
