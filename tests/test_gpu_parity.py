@@ -154,11 +154,12 @@ def test_runs_of_spheres_bit_exact(capi, oracle, count, kernel):
     _assert_same(out, ref, "%d spheres" % count)
 
 
-def test_large_quadric_scene_wavefront(capi, oracle):
+def test_large_quadric_scene_wavefront(capi, oracle, monkeypatch):
     """Config 3 plus 40 more objects: the 512-path wavefront's 45 KB of exchange slots and a 13 KB scene block together exceed
     the default 48 KB of shared memory; the kernel opts in (sail_jit.cpp) and stays bit-exact."""
     import sail_b200 as Sail
     from sail_b200 import wire
+    monkeypatch.delenv("SAIL_B200_WF_THREADS", raising=False)  # the default size for quadric scenes is what is tested
     W, H = 64, 48
     scene, _, _, _, bounces = scene_tables(3, W, H)
     rng = np.random.default_rng(3)
