@@ -132,6 +132,8 @@ def other_workload(name, local_rank, peak_tops, steps=8, warm=3):
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     for s in range(warm):
         r.ctx.render_n(batches[s])
+        if s == 0:
+            r.ctx.specialise_wait()
     r.ctx.synchronize()
     with torch.cuda.stream(stream):
         for s in range(steps):
@@ -234,17 +236,67 @@ def run_reference(args, rank, world):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}))
 
 
-class _DevBuf:
-    """__cuda_array_interface__ view of a device buffer owned by a sail_ctx (for torch.distributed)."""
+def _share_group_id(dist, rank):
+    """The 128-byte rendezvous token of sail_group_join, made on rank 0 and carried to the others by torch.distributed --
+    the only thing the bench uses torch.distributed for besides its barriers and the max over ranks."""
+    from sail_b200 import capi
+    box = [capi.group_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    return box[0]
 
-    def __init__(self, ptr, shape):
-        self.__cuda_array_interface__ = {"shape": shape, "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+
+def sustained_leg(local_rank, peak_tops, min_seconds=2.0):
+    """BASELINE config 4 in full on one GPU -- Cornell box 3840x2160, 1024 spp as 32 launches of 32 spp, repeated until at
+    least ``min_seconds`` of device time -- with its own clock record: the SM clock under seconds of sustained FP32 load."""
+    global _workload
+    import torch
+    from sail_b200.renderer import Renderer
+    keep, _workload = _workload, "config4"
+    try:
+        scene, W, H, bounces, _ = build_workload()
+        ops = ops_per_path()
+    finally:
+        _workload = keep
+    r = Renderer((W, H), device=local_rank)
+    r.ctx.configure(max_bounces=bounces)
+    r.update(scene)
+    launches_per_pass = 1024 // SPP_PER_STEP
+    batches = [r.tracer.frames(scene.mat, scene.eye, s * SPP_PER_STEP, SPP_PER_STEP) for s in range(launches_per_pass)]
+    r.ctx.render_n(batches[0])
+    r.ctx.specialise_wait()
+    r.ctx.render_n(batches[1])
+    r.ctx.synchronize()
+    stream = torch.cuda.ExternalStream(r.ctx.stream(), device=local_rank)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    passes, ms = 0, 0.0
+    while ms < min_seconds * 1e3 and passes < 16:
+        r.ctx.reset()
+        with torch.cuda.stream(stream):
+            e0.record(stream)
+            for b in batches:
+                r.ctx.render_n(b)
+            e1.record(stream)
+        r.ctx.synchronize()
+        torch.cuda.synchronize()
+        ms += e0.elapsed_time(e1)
+        passes += 1
+    clocks = sampler.stop()
+    used = r.ctx.kernel_info()
+    r.close()
+    paths_s = passes * W * H * 1024 / (ms * 1e-3)
+    return {"workload": WORKLOADS["config4"][1] + ", 1024 spp per pass, sustained", "value": paths_s / 1e6, "unit": UNIT,
+            "seconds": ms * 1e-3, "passes": passes, "launches": passes * launches_per_pass, "kernel_used": used,
+            "roofline_frac": paths_s * ops / 1e12 / peak_tops, "ops_per_path": ops, "clocks": clocks}
 
 
 def run_ours(args, rank, world, local_rank):
     import torch
 
     from sail_b200 import capi
+    from sail_b200.filters import lower_filter
+    from sail_b200.generator import PluginParams
     from sail_b200.renderer import Renderer
     dist = None
     if world > 1:
@@ -256,21 +308,34 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     scene, W, H, bounces, (o, t, l) = build_workload()
     steps, warm = args.steps, args.warmup
-    paths_per_step = W * H * SPP_PER_STEP
+    tile = args.sharding == "tile" and world > 1
+    shard = capi.SHARD_TILE if tile else capi.SHARD_SAMPLE
+    # sample sharding: every rank traces SPP_PER_STEP frames per step (weak scaling); tile sharding: the N ranks share the
+    # rows of SPP_PER_STEP frames (strong scaling)
+    frames_per_step = SPP_PER_STEP if (tile or world == 1) else SPP_PER_STEP * world
+    paths_per_step = W * H * frames_per_step  # whole job
 
-    # ---------------- device-resident arm -----------------
-    r = Renderer((W, H), device=local_rank)
+    # One renderer per rank; with N > 1 it joins the group: the split of every sail_render_n(), the collective and the
+    # combined image all live behind the C ABI (sail_group_join).
+    group = (world, rank, _share_group_id(dist, rank)) if world > 1 else None
+    r = Renderer((W, H), device=local_rank, group=group, shard=shard, band_rows=args.band_rows)
     ctx = r.ctx
-    ctx.configure(max_bounces=bounces, accum_mode=capi.ACCUM_SUM if world > 1 else capi.ACCUM_MEAN,
-                  kernel={"wavefront": capi.KERNEL_WAVEFRONT, "mega": capi.KERNEL_MEGA, "auto": capi.KERNEL_AUTO, "server": capi.KERNEL_SERVER}[args.kernel],
+    ctx.configure(max_bounces=bounces,
+                  kernel={"wavefront": capi.KERNEL_WAVEFRONT, "mega": capi.KERNEL_MEGA, "auto": capi.KERNEL_AUTO}[args.kernel],
                   specialise=capi.SPECIALISE_OFF if args.no_jit else capi.SPECIALISE_AUTO)
     r.update(scene)
+    filters = []
+    if tile:  # BASELINE config 5: the filter sweep runs on the root after the gather
+        for name in args.filters.split(","):
+            pp = PluginParams(name)
+            pp.addParam("r", "vec2(2.0,2.0)")
+            pp.addParam("tau", "3.0")
+            pp.addParam("alpha", "2.0")
+            filters.append(lower_filter(pp))
     total_steps = warm + steps
-    # rank g owns frame indices k = g (mod world)
-    batches = []
-    for s in range(total_steps):
-        ks = [(s * SPP_PER_STEP + i) * world + rank for i in range(SPP_PER_STEP)]
-        batches.append(capi.frame_array([r.tracer.frame(scene.mat, scene.eye, k) for k in ks]))
+
+    # ---------------- device-resident arm: the trace kernels alone, CUDA events on each rank's stream -----------------
+    batches = [r.tracer.frames(scene.mat, scene.eye, s * frames_per_step, frames_per_step) for s in range(total_steps)]
     stream = torch.cuda.ExternalStream(ctx.stream(), device=local_rank)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
@@ -278,6 +343,8 @@ def run_ours(args, rank, world, local_rank):
     sampler.start()  # runs through the warm-up (same kernel, same load) and the timed region
     for s in range(warm):
         ctx.render_n(batches[s])
+        if s == 0:
+            ctx.specialise_wait()  # NVRTC works on another thread: the remaining warm-up steps already run the kernel that is timed
     ctx.synchronize()
     torch.cuda.synchronize()
     if dist:
@@ -298,68 +365,89 @@ def run_ours(args, rank, world, local_rank):
         dist.barrier()
     dev_ms = sum(a.elapsed_time(b) for a, b in ev)
 
-    # ---------------- multi-GPU combine (once per presentation, outside the per-step timing) -----------------
-    reduce_ms = None
+    # ---------------- the combine alone (device time on the root, warmed) -----------------
+    combine_ms = None
     if dist:
-        acc = torch.as_tensor(_DevBuf(ctx.device_ptr(capi.AOV_COLOR), (H, W, 3)), device="cuda")
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        dist.reduce(acc, dst=0, op=dist.ReduceOp.SUM)
-        e1.record()
-        torch.cuda.synchronize()
-        reduce_ms = e0.elapsed_time(e1)
+        samples = []
+        for i in range(6):
+            ctx.render_n(batches[i % total_steps])
+            img = ctx.read_accum()          # collective: ncclReduce to rank 0 (+ scale), then the read-back on rank 0
+            if rank == 0 and i >= 2:
+                samples.append(ctx.last_combine_ms())
         if rank == 0:
-            ctx.scale_accum(1.0 / (total_steps * SPP_PER_STEP * world))
-            img = ctx.read_accum()
-            assert np.isfinite(img).all() and 0.0 < float(img.mean()) < 1.0, "reduced image is not sane"
+            combine_ms = float(np.median(samples))
+            assert np.isfinite(img).all() and 0.0 < float(img.mean()) < 1.0, "combined image is not sane"
 
-    # ---------------- end-to-end arm: Renderer API, host buffers in and out -----------------
+    # ---------------- end-to-end arm: Renderer API, host buffers in and out, combined image on rank 0 -----------------
+    def present_sweep(pipelined):
+        """One step's display work: with a filter sweep (config 5) every filter is applied to the same gathered image."""
+        if not filters:
+            return r.render_pipelined(scene, frames=frames_per_step) if pipelined else r.render(scene, frames=frames_per_step)
+        r.trace(scene, frames_per_step)
+        out = None
+        for f in filters:
+            ctx.configure(filter_id=f["filter_id"], filter_gamma_c=f["gamma_c"], filter_radius=f["radius"], filter_weights=f["weights"])
+            out = ctx.present(as_u8=True, pinned=True)
+        return out
+
     scene.sampleCount = 0
     e2e_steps = max(1, min(steps, 20))
     for _ in range(2):
-        r.render(scene, frames=SPP_PER_STEP)
+        present_sweep(False)
+    ctx.synchronize()
     if dist:
         dist.barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        # host: 32 x (jitter, inverse MVP) -> sail_frame[] -> H2D as kernel parameters; trace; display filter;
-        # D2H of the RGBA8 image into page-locked host memory (synchronises)
-        img8 = r.render(scene, frames=SPP_PER_STEP)
+        # host: N x 32 x (jitter, inverse MVP) -> sail_frame[] -> H2D as kernel parameters; trace on every GPU; combine on the
+        # root (N > 1); display filter; D2H of the RGBA8 image into page-locked host memory (synchronises on the root)
+        img8 = present_sweep(False)
+    ctx.synchronize()
     e2e_s = time.perf_counter() - t0
-    assert img8.shape == (H, W, 4)
+    assert rank != 0 or img8.shape == (H, W, 4)
     # the same steps with the display double-buffered (Renderer.render_pipelined: step i's image is collected by call i+1,
     # its device-to-host copy overlaps the tracing of step i+1; every copy still lies inside the timed region)
-    for _ in range(2):
-        r.render_pipelined(scene, frames=SPP_PER_STEP)
-    r.flush()
-    if dist:
-        dist.barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        img8 = r.render_pipelined(scene, frames=SPP_PER_STEP)
-    img8 = r.flush()
-    e2e_pipe_s = time.perf_counter() - t0
-    assert img8.shape == (H, W, 4)
+    e2e_pipe_s = None
+    if not filters:
+        for _ in range(2):
+            present_sweep(True)
+        r.flush()
+        ctx.synchronize()
+        if dist:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            img8 = present_sweep(True)
+        img8 = r.flush()
+        ctx.synchronize()
+        e2e_pipe_s = time.perf_counter() - t0
+        assert rank != 0 or img8.shape == (H, W, 4)
+    group_info = ctx.group_info()[2]
 
-    times = torch.tensor([dev_ms, e2e_s * 1e3, e2e_pipe_s * 1e3], dtype=torch.float64, device="cuda")
+    times = torch.tensor([dev_ms, e2e_s * 1e3, (e2e_pipe_s or e2e_s) * 1e3], dtype=torch.float64, device="cuda")
+    tmin = times.clone()
     if dist:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tmin, op=dist.ReduceOp.MIN)
     dev_ms, e2e_ms, e2e_pipe_ms = float(times[0]), float(times[1]), float(times[2])
     if rank == 0:
         pk = peaks()
         n_sm = torch.cuda.get_device_properties(local_rank).multi_processor_count
-        value = world * steps * paths_per_step / (dev_ms * 1e-3) / 1e6
-        per_gpu_paths_s = steps * paths_per_step / (dev_ms * 1e-3)
+        value = steps * paths_per_step / (dev_ms * 1e-3) / 1e6
+        per_gpu_paths_s = steps * paths_per_step / world / (dev_ms * 1e-3)
         ops = ops_per_path()
         peak = n_sm * 128 * pk["sm_max_mhz"] * 1e6 / 1e12
         achieved = per_gpu_paths_s * ops / 1e12
-        hbm_gbs = (W * H * 24) / (dev_ms / steps * 1e-3) / 1e9
+        launches_per_step = max(1, launches // max(1, steps))
+        hbm_gbs = (W * H * 24 / (world if tile else 1)) * launches_per_step / (dev_ms / steps * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warm,
-            "ms_per_step": dev_ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "ms_per_step": dev_ms / steps, "higher_is_better": True, "scaling": "strong" if tile else "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": WORKLOADS[_workload][1], "spp_per_step": SPP_PER_STEP, "paths_per_step_per_gpu": paths_per_step,
-                       "kernel": args.kernel, "kernel_used": kernel_used, "arithmetic": "strict (bit-exact vs oracle)", "sharding": "sample index mod N",
+            "config": {"workload": WORKLOADS[_workload][1], "spp_per_step": SPP_PER_STEP, "paths_per_step": paths_per_step,
+                       "kernel": args.kernel, "kernel_used": kernel_used, "arithmetic": "strict (bit-exact vs oracle)",
+                       "sharding": ("interleaved %d-row bands mod N (tile)" % (args.band_rows or 16)) if tile else "sample index mod N",
+                       "group": group_info,
                        "l2": "flushed between steps (256 MiB memset outside the per-step events)"},
             "spp_per_s": value * 1e6 / (W * H),
             "roofline": {"bound": "fp32_issue", "achieved": achieved, "peak": peak, "unit": "Tops/s (FP32 lane-ops)",
@@ -368,21 +456,30 @@ def run_ours(args, rank, world, local_rank):
                          "hbm": {"achieved": hbm_gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": hbm_gbs / pk["hbm_gbs"],
                                  "bytes_per_launch": W * H * 24}},
             "clocks": clocks,
-            "e2e": {"value": world * e2e_steps * paths_per_step / (e2e_pipe_ms * 1e-3) / 1e6, "unit": UNIT,
-                    "h2d_bytes_per_step": SPP_PER_STEP * 84, "d2h_bytes_per_step": W * H * 4, "steps": e2e_steps,
-                    "mode": "Renderer.render_pipelined per step: host frame construction, H2D of the frame uniforms, trace, display "
-                            "filter, D2H of the RGBA8 image into page-locked memory; the display is double-buffered (step i's image "
-                            "is collected by call i+1, its copy overlaps the next trace), every copy lies inside the timed region",
-                    "synchronous_value": world * e2e_steps * paths_per_step / (e2e_ms * 1e-3) / 1e6,
+            "e2e": {"value": e2e_steps * paths_per_step / (e2e_pipe_ms * 1e-3) / 1e6, "unit": UNIT,
+                    "h2d_bytes_per_step": frames_per_step * 84, "d2h_bytes_per_step": W * H * 4 * max(1, len(filters)), "steps": e2e_steps,
+                    "mode": ("Renderer.render_pipelined per step" if e2e_pipe_s is not None else "trace + one sail_present per filter per step") +
+                            ": host frame construction, H2D of the frame uniforms, trace on every GPU, "
+                            + ("combine of the %d GPUs' buffers on rank 0 INSIDE the timed region (%s), " % (world, group_info) if world > 1 else "")
+                            + "display filter, D2H of the RGBA8 image into page-locked memory"
+                            + ("; the display is double-buffered (step i's image is collected by call i+1, its copy overlaps the next trace), "
+                               "every copy lies inside the timed region" if e2e_pipe_s is not None else ""),
+                    "synchronous_value": e2e_steps * paths_per_step / (e2e_ms * 1e-3) / 1e6,
                     "synchronous_mode": "Renderer.render per step: the same work, the call returns its own image (waits for the copy)"},
             "gpu_launches": int(launches),
         }
-        if reduce_ms is not None:
-            line["reduce_ms"] = reduce_ms
+        if world > 1:
+            line["trace_ms_per_step_min_over_ranks"] = float(tmin[0]) / steps
+            line["trace_ms_per_step_max_over_ranks"] = dev_ms / steps
+            line["combine"] = {"ms": combine_ms, "bytes": W * H * 12, "gbs": W * H * 12 / (combine_ms * 1e-3) / 1e9 if combine_ms else None,
+                               "how": group_info, "note": "device time on rank 0 from the end of its own trace to the combined buffer, median of 4 warmed calls"}
+            if filters:
+                line["config"]["filters"] = args.filters
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline()
         if world == 1 and not args.no_cpu and _workload == "cornell":
             line["other_workloads"] = [other_workload(w, local_rank, peak) for w in ("config2", "config3", "config5")]
+            line["other_workloads"].append(sustained_leg(local_rank, peak))
             # The same workload with the last-bounce reductions compiled out (every bounce evaluated in full, as the
             # reference's loop does; identical image): how much of `value` is skipped dead work.
             keep = os.environ.get("SAIL_B200_JIT_DEFINES")
@@ -400,6 +497,7 @@ def run_ours(args, rank, world, local_rank):
         print(json.dumps(line))
     r.close()
     if dist:
+        dist.barrier()
         dist.destroy_process_group()
 
 
@@ -409,10 +507,13 @@ def main():
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--kernel", default="auto", choices=["auto", "mega", "wavefront", "server"])
+    ap.add_argument("--kernel", default="auto", choices=["auto", "mega", "wavefront"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-jit", action="store_true", help="ahead-of-time kernel variants only (no per-scene NVRTC build)")
     ap.add_argument("--workload", default="cornell", choices=sorted(WORKLOADS), help="cornell = the headline; others are extra")
+    ap.add_argument("--sharding", default="sample", choices=["sample", "tile"], help="N > 1: sample index mod N (config 4) or row bands (config 5)")
+    ap.add_argument("--band-rows", type=int, default=0, help="tile sharding: rows per interleaved band (multiple of 8; 0 = 16)")
+    ap.add_argument("--filters", default="box,sinc,gaussian", help="tile sharding: display filters applied to the gathered image each step")
     args = ap.parse_args()
     global _workload
     _workload = args.workload

@@ -24,13 +24,15 @@
 extern "C" {
 #endif
 
-#define SAIL_ABI_VERSION 1
+#define SAIL_ABI_VERSION 2
 
 /* Row widths of the wire format (src/core/webgl.js:137-139). */
 #define SAIL_OBJECTS_LENGTH 18
 #define SAIL_TEXPARAMS_LENGTH 16
 #define SAIL_LIGHTS_LENGTH 18
 #define SAIL_MAX_FRAMES_PER_CALL 32
+#define SAIL_MAX_DEVICES 8
+#define SAIL_GROUP_ID_BYTES 128
 
 enum {
     SAIL_OK = 0,
@@ -67,17 +69,33 @@ enum {
 enum {
     SAIL_KERNEL_MEGA = 0,       /* one thread traces a whole path */
     SAIL_KERNEL_WAVEFRONT = 1,  /* per-bounce stages over ray queues regrouped by hit object, queues in shared memory */
-    SAIL_KERNEL_AUTO = 2,       /* default: chosen from the scene's content by the measured policy of DESIGN.md 4.2 */
-    SAIL_KERNEL_SERVER = 3      /* megakernel whose CTAs carry one server warp that evaluates the hits on non-box shapes of all
-                                   its path warps together (sail_server.cuh); exists only as a scene-specialised kernel */
+    SAIL_KERNEL_AUTO = 2        /* default: chosen from the scene's content by the measured policy of DESIGN.md 4.2 */
 };
 
 enum {
-    SAIL_SPECIALISE_AUTO = 0,    /* default: compile the kernel for the scene's structure at first use (NVRTC; object count
-                                    and per-slot shape categories become constants -- the per-scene shader generation of
-                                    src/shader/generator.js:107-123); use the ahead-of-time variant when that is not possible */
+    SAIL_SPECIALISE_AUTO = 0,    /* default: compile the kernel for the scene's structure (NVRTC; object count and per-slot shape
+                                    categories become constants -- the per-scene shader generation of
+                                    src/shader/generator.js:107-123) on a worker thread; frames rendered before it is ready use the
+                                    resident ahead-of-time variant (bit-identical), as they do when compiling is not possible.  The
+                                    reference blocks in createProgram instead (src/core/webgl.js:165-213). */
     SAIL_SPECIALISE_OFF = 1,     /* ahead-of-time variants only */
-    SAIL_SPECIALISE_REQUIRE = 2  /* fail sail_render* with SAIL_ERR_STATE if the scene-specialised kernel cannot be built */
+    SAIL_SPECIALISE_REQUIRE = 2  /* compile synchronously at the first sail_render* after an upload and fail with SAIL_ERR_STATE if the
+                                    scene-specialised kernel cannot be built */
+};
+
+/* How the images of a multi-GPU context are split (the reference has one GL context, src/core/webgl.js:215-227). */
+enum {
+    SAIL_SHARD_NONE = 0,
+    SAIL_SHARD_SAMPLE = 1,  /* member g traces the frames whose index (counted since the last restart) is congruent to g modulo the
+                               group size, into its own FP32 sum; the display / read-back calls combine the sums (BASELINE config 4) */
+    SAIL_SHARD_TILE = 2     /* member g traces every frame for its interleaved row bands; display / read-back gather the rows (config 5) */
+};
+/* How a sharded context combines its members' buffers when an image is asked for. */
+enum {
+    SAIL_COMBINE_AUTO = 0,  /* peer memory when every member can map the root's and its peers' buffers, NCCL otherwise */
+    SAIL_COMBINE_NCCL = 1,  /* ncclReduce(sum) to the root (libnccl.so.2 is opened with dlopen; no link-time dependency) */
+    SAIL_COMBINE_P2P = 2    /* members add / copy their share straight into the root's buffer over NVLink peer mappings, in a fixed
+                               member order (deterministic sums) */
 };
 
 typedef struct sail_ctx sail_ctx;
@@ -86,9 +104,16 @@ typedef struct sail_ctx sail_ctx;
  * + the frameCache allocation (webgl.js:12-28).  The 512x512 canvas becomes an explicit size. */
 typedef struct sail_create_info {
     int32_t width, height;  /* full image size in pixels */
-    int32_t device;         /* CUDA device ordinal */
-    int32_t row_begin;      /* rows [row_begin, row_end) are rendered by this context (tile sharding); */
+    int32_t device;         /* CUDA device ordinal (ndev <= 1) */
+    int32_t row_begin;      /* rows [row_begin, row_end) are rendered by this context (host-managed tile sharding); */
     int32_t row_end;        /* 0,0 = the whole image.  Buffers always cover the full image. */
+    /* ABI 2: one context over several GPUs of this process.  The context owns a stream, the buffers and the communicator of every
+     * member; device_ids[0] is the root, where combined images are formed, filtered and read back. */
+    int32_t ndev;           /* 0 or 1: single device.  2..SAIL_MAX_DEVICES: device_ids[0..ndev) */
+    int32_t shard_mode;     /* SAIL_SHARD_SAMPLE or SAIL_SHARD_TILE when ndev > 1 */
+    int32_t band_rows;      /* SAIL_SHARD_TILE: rows per interleaved band, a multiple of 8 (0 = 16) */
+    int32_t device_ids[SAIL_MAX_DEVICES];
+    int32_t combine;        /* SAIL_COMBINE_* */
     int32_t reserved[3];
 } sail_create_info;
 
@@ -124,6 +149,20 @@ int sail_device_count(void);
 
 int sail_create(const sail_create_info* info, sail_ctx** out);
 void sail_destroy(sail_ctx* ctx);
+
+/* One GPU per process (torchrun-style hosts): every process creates a single-device context and joins the same group; the
+ * context then is member `rank` of `nranks` and behaves like one device of a sharded context.  sail_group_id() makes the
+ * 128-byte rendezvous token (ncclGetUniqueId) on one process; the host carries it to the others (any channel: a file, MPI,
+ * torch.distributed ...).  After the join every process issues the SAME sequence of sail_upload_* / sail_render* /
+ * sail_present* / sail_read_* / sail_reset calls with the same arguments (they are collective); images arrive on rank 0,
+ * the other ranks' output pointers may be NULL.  sail_group_join is collective and blocks until all ranks have joined. */
+int sail_group_id(uint8_t id[SAIL_GROUP_ID_BYTES]);
+int sail_group_join(sail_ctx* ctx, int32_t nranks, int32_t rank, const uint8_t id[SAIL_GROUP_ID_BYTES], int32_t shard_mode,
+                    int32_t band_rows, int32_t combine);
+/* Group size, this context's first member index, and a description of the combine path ("p2p", "nccl 2.28.9", ...). */
+int sail_group_info(sail_ctx* ctx, int32_t* nmembers, int32_t* first_member, char* buf, int32_t len);
+/* Device time of the most recent combine (reduce / gather to the root) in milliseconds, on the root's stream. */
+int sail_last_combine_ms(sail_ctx* ctx, float* ms);
 const char* sail_last_error(const sail_ctx* ctx);
 void sail_default_config(sail_config* cfg);
 
@@ -156,11 +195,18 @@ int sail_reset(sail_ctx* ctx);
  * src/core/webgl.js:51-93.  One call = 1 sample per pixel over this context's rows. */
 int sail_render(sail_ctx* ctx, const float matrix_colmajor[16], const float eye[3], float textureWeight,
                 float timeSinceStart);
-/* `count` consecutive frames; pixel results equal `count` sail_render() calls, the accumulator stays in
- * registers between frames.  AOVs are those of the last frame, as they would be after `count` calls. */
+/* `count` consecutive frames (1..SAIL_MAX_FRAMES_PER_CALL; a sample-sharded context takes that many per member, i.e. up to
+ * SAIL_MAX_FRAMES_PER_CALL x group size); pixel results equal `count` sail_render() calls, the accumulator stays in
+ * registers between frames.  AOVs are those of the last frame, as they would be after `count` calls.
+ * Sharded contexts: collective (every member of a joined group passes the same frames and traces its share); with
+ * SAIL_SHARD_SAMPLE and SAIL_ACCUM_MEAN a frame with textureWeight == 0 restarts the sums, as it restarts the running mean. */
 int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count);
 
 int sail_synchronize(sail_ctx* ctx);
+/* Blocks until the scene-specialised kernel requested by the last upload / render has been compiled (or has failed) and, when
+ * it is ready, makes the next sail_render* use it.  Returns 0 when that kernel is in place, 1 when the context keeps running
+ * the ahead-of-time variant (sail_kernel_info() says why).  Benchmarks call it once after the first frame. */
+int sail_specialise_wait(sail_ctx* ctx);
 
 /* Read back a full-image buffer (what readPixels on frameCache[0], [2], [3] would give). */
 int sail_read_aov(sail_ctx* ctx, int32_t which, void* out, size_t out_bytes);

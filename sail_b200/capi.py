@@ -16,9 +16,14 @@ LIB_PATH = os.path.join(_HERE, "libsail_b200.so")
 MAX_FRAMES_PER_CALL = 32
 AOV_COLOR, AOV_NORMAL, AOV_POSITION, AOV_HIT_ID, AOV_DEPTH = range(5)
 ACCUM_MEAN, ACCUM_SUM = 0, 1
-KERNEL_MEGA, KERNEL_WAVEFRONT, KERNEL_AUTO, KERNEL_SERVER = 0, 1, 2, 3
+KERNEL_MEGA, KERNEL_WAVEFRONT, KERNEL_AUTO = 0, 1, 2
 SPECIALISE_AUTO, SPECIALISE_OFF, SPECIALISE_REQUIRE = 0, 1, 2
 ERR_CUDA, ERR_INVALID, ERR_STATE, ERR_NOMEM = -1, -2, -3, -4
+SHARD_NONE, SHARD_SAMPLE, SHARD_TILE = 0, 1, 2
+COMBINE_AUTO, COMBINE_NCCL, COMBINE_P2P = 0, 1, 2
+MAX_DEVICES = 8
+GROUP_ID_BYTES = 128
+ABI_VERSION = 2
 
 
 class SailError(RuntimeError):
@@ -29,7 +34,9 @@ class SailError(RuntimeError):
 
 class CreateInfo(ctypes.Structure):
     _fields_ = [("width", ctypes.c_int32), ("height", ctypes.c_int32), ("device", ctypes.c_int32),
-                ("row_begin", ctypes.c_int32), ("row_end", ctypes.c_int32), ("reserved", ctypes.c_int32 * 3)]
+                ("row_begin", ctypes.c_int32), ("row_end", ctypes.c_int32), ("ndev", ctypes.c_int32),
+                ("shard_mode", ctypes.c_int32), ("band_rows", ctypes.c_int32), ("device_ids", ctypes.c_int32 * MAX_DEVICES),
+                ("combine", ctypes.c_int32), ("reserved", ctypes.c_int32 * 3)]
 
 
 class Config(ctypes.Structure):
@@ -53,6 +60,11 @@ _SIGNATURES = {
     "sail_device_count": (ctypes.c_int, []),
     "sail_create": (ctypes.c_int, [ctypes.POINTER(CreateInfo), ctypes.POINTER(_P)]),
     "sail_destroy": (None, [_P]),
+    "sail_group_id": (ctypes.c_int, [_P]),
+    "sail_group_join": (ctypes.c_int, [_P, ctypes.c_int32, ctypes.c_int32, _P, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32]),
+    "sail_group_info": (ctypes.c_int, [_P, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32), ctypes.c_char_p, ctypes.c_int32]),
+    "sail_last_combine_ms": (ctypes.c_int, [_P, ctypes.POINTER(ctypes.c_float)]),
+    "sail_specialise_wait": (ctypes.c_int, [_P]),
     "sail_last_error": (ctypes.c_char_p, [_P]),
     "sail_default_config": (None, [ctypes.POINTER(Config)]),
     "sail_configure": (ctypes.c_int, [_P, ctypes.POINTER(Config)]),
@@ -131,14 +143,23 @@ def make_frame(matrix, eye, textureWeight, timeSinceStart):
 
 
 class Context:
-    """One ``sail_ctx``: a device, a stream and the full-image device buffers."""
+    """One ``sail_ctx``: one GPU (a device, a stream and the full-image device buffers) or, with ``devices=[...]``,
+    one context sharded over several GPUs of this process (``shard`` = SHARD_SAMPLE / SHARD_TILE)."""
 
-    def __init__(self, width, height, device=0, rows=None):
+    def __init__(self, width, height, device=0, rows=None, devices=None, shard=SHARD_SAMPLE, band_rows=0, combine=COMBINE_AUTO):
         self.lib = load()
         self.width, self.height = int(width), int(height)
         info = CreateInfo(self.width, self.height, int(device), 0, 0)
         if rows is not None:
             info.row_begin, info.row_end = int(rows[0]), int(rows[1])
+        if devices is not None and len(devices) > 1:
+            if len(devices) > MAX_DEVICES:
+                raise SailError(ERR_INVALID, "at most %d devices" % MAX_DEVICES)
+            info.ndev = len(devices)
+            info.device_ids[:len(devices)] = [int(d) for d in devices]
+            info.shard_mode, info.band_rows, info.combine = int(shard), int(band_rows), int(combine)
+        self.is_root = True
+        self._sample_members = len(devices) if (devices is not None and len(devices) > 1 and shard == SHARD_SAMPLE) else 0
         handle = _P()
         self._pinned = {}
         rc = self.lib.sail_create(ctypes.byref(info), ctypes.byref(handle))
@@ -218,13 +239,41 @@ class Context:
         if isinstance(frames, (list, tuple)):
             frames = (Frame * len(frames))(*frames)
         count = len(frames)
-        for start in range(0, count, MAX_FRAMES_PER_CALL):
-            n = min(MAX_FRAMES_PER_CALL, count - start)
+        per_call = MAX_FRAMES_PER_CALL * (self._sample_members or 1)
+        for start in range(0, count, per_call):
+            n = min(per_call, count - start)
             chunk = ctypes.cast(ctypes.byref(frames, start * ctypes.sizeof(Frame)), ctypes.POINTER(Frame))
             self._check(self.lib.sail_render_n(self._h, chunk, n))
 
     def synchronize(self):
         self._check(self.lib.sail_synchronize(self._h))
+
+    def specialise_wait(self):
+        """Block until the scene-specialised kernel is in place; False when the context stays on the ahead-of-time variant."""
+        rc = self.lib.sail_specialise_wait(self._h)
+        if rc < 0:
+            self._check(rc)
+        return rc == 0
+
+    # ---- groups: one GPU per process (torchrun-style) ---------------------------------------------------------
+    def group_join(self, nranks, rank, group_id, shard=SHARD_SAMPLE, band_rows=0, combine=COMBINE_AUTO):
+        """Collective: become member ``rank`` of ``nranks`` (``group_id`` = the 128 bytes of ``capi.group_id()`` made on
+        one rank and carried to the others by the host)."""
+        buf = (ctypes.c_uint8 * GROUP_ID_BYTES).from_buffer_copy(bytes(group_id))
+        self._check(self.lib.sail_group_join(self._h, int(nranks), int(rank), buf, int(shard), int(band_rows), int(combine)))
+        self.is_root = rank == 0
+        self._sample_members = int(nranks) if shard == SHARD_SAMPLE else 0
+
+    def group_info(self):
+        n, first = ctypes.c_int32(), ctypes.c_int32()
+        buf = ctypes.create_string_buffer(200)
+        self._check(self.lib.sail_group_info(self._h, ctypes.byref(n), ctypes.byref(first), buf, 200))
+        return int(n.value), int(first.value), buf.value.decode()
+
+    def last_combine_ms(self):
+        ms = ctypes.c_float()
+        self._check(self.lib.sail_last_combine_ms(self._h, ctypes.byref(ms)))
+        return ms.value
 
     def last_render_ms(self):
         ms = ctypes.c_float()
@@ -251,6 +300,9 @@ class Context:
             shape, dtype = (H, W), np.float32
         else:
             raise SailError(ERR_INVALID, "unknown AOV %r" % (which,))
+        if not self.is_root:  # member of a multi-process group: takes part in the combine, the image arrives on rank 0
+            self._check(self.lib.sail_read_aov(self._h, which, None, 0))
+            return None
         if out is None:
             out = np.empty(shape, dtype)
         assert out.shape == shape and out.dtype == dtype and out.flags.c_contiguous
@@ -284,6 +336,9 @@ class Context:
         """Display pass + read-back.  ``pinned=True`` returns views of context-owned page-locked buffers that the
         next ``present`` overwrites (like the canvas); the default returns fresh arrays."""
         H, W = self.height, self.width
+        if not self.is_root:
+            self._check(self.lib.sail_present(self._h, None, None))
+            return (None, None) if both else None
         alloc = self.host_buffer if pinned else (lambda shape, dtype: np.empty(shape, dtype))
         f32 = alloc((H, W, 4), np.float32) if (both or not as_u8) else None
         u8 = alloc((H, W, 4), np.uint8) if (both or as_u8) else None
@@ -296,6 +351,9 @@ class Context:
         """Queue the display pass and start the asynchronous copy of the RGBA8 image into page-locked buffer ``slot``
         (0 or 1); returns that buffer, valid after ``present_end()``."""
         H, W = self.height, self.width
+        if not self.is_root:
+            self._check(self.lib.sail_present_begin(self._h, None))
+            return None
         buf = self.host_buffer((2, H, W, 4), np.uint8)[slot]
         self._check(self.lib.sail_present_begin(self._h, buf.ctypes.data_as(ctypes.c_void_p)))
         return buf
@@ -387,3 +445,12 @@ def jit_compile_check(objects, texparams, lights, kernel=KERNEL_MEGA):
 
 def device_count():
     return int(load().sail_device_count())
+
+
+def group_id():
+    """The 128-byte rendezvous token of a multi-process group (sail_group_id; needs NCCL)."""
+    buf = (ctypes.c_uint8 * GROUP_ID_BYTES)()
+    rc = load().sail_group_id(buf)
+    if rc != 0:
+        raise SailError(rc, "sail_group_id failed (NCCL not available?)")
+    return bytes(buf)

@@ -19,9 +19,11 @@
 #include <string.h>
 
 #include <chrono>
+#include <condition_variable>
 #include <map>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "sail_jit_sources.inc"
@@ -58,7 +60,6 @@ struct Api {
 };
 Api g_api;
 std::mutex g_mutex;
-std::map<std::string, void*> g_cache;  // key (device, kind, F, minCtas, cats) -> CUfunction; modules live for the process
 
 void* openFirst(const std::vector<std::string>& names, std::string* tried) {
     for (const std::string& n : names) {
@@ -113,14 +114,45 @@ void setErr(char* err, int errlen, const std::string& s) {
     if (err && errlen > 0) snprintf(err, (size_t)errlen, "%s", s.c_str());
 }
 
+
+struct Plan {
+    std::string key, src, head, cats, masks;
+    unsigned block = SAIL_JIT_CTA_THREADS;
+    int kind = 0, F = 0, n = 0;
+};
+
 }  // namespace
 
-// device < 0: compile only (no driver library, no GPU needed) -- sail_jit_compile_check.
-static int jitGetLocked(int device, int kind, int F, int minCtas, const SailSceneBlock* scene, SailJitKernel* out, char* err, int errlen) {
-    if (!loadApi()) { setErr(err, errlen, g_api.why); return 1; }
-    if (device >= 0 && !loadDriver()) { setErr(err, errlen, g_api.cuWhy); return 1; }
+struct SailJitJob {
+    Plan plan;
+    std::mutex m;
+    std::condition_variable cv;
+    bool done = false;
+    int rc = 0;  // 0 ok, else failure (message in err)
+    std::string err;
+    std::vector<char> cubin;
+    double secs = 0.0;
+    std::thread worker;
+    std::map<int, void*> fn;  // device -> CUfunction (guarded by g_mutex)
+};
+
+namespace {
+
+// Jobs live for the process: a scene structure is compiled once and its cubin is loaded on every device that asks.
+struct Registry {
+    std::map<std::string, SailJitJob*> jobs;
+    ~Registry() {
+        for (auto& kv : jobs)
+            if (kv.second->worker.joinable()) kv.second->worker.join();  // do not exit under a running compiler
+    }
+};
+Registry g_reg;
+
+// Fills the plan (cache key, generated source, launch shape) for `scene`; 0 or an error code with a message.
+int makePlan(int kind, int F, int minCtas, const SailSceneBlock* scene, Plan* plan, char* err, int errlen) {
     const int n = scene->n;
     if (n < 1) { setErr(err, errlen, "empty scene"); return 2; }
+    if (kind != 0 && kind != 1) { setErr(err, errlen, "unknown kernel kind"); return 2; }
     // runs of equal shape category in slot order
     std::string cats, runCat, runStart, runLen;
     int nruns = 0;
@@ -137,13 +169,11 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
     }
     if (nruns > SAIL_JIT_MAX_RUNS) { setErr(err, errlen, "more than 16 runs of distinct shapes"); return 2; }
     // which plugins the scene contains (category ids as bit positions; ids outside 0..31 select no arm anyway)
-    unsigned shapes = 0, mats = 0, texs = 0, lights = 0, glass = 0, matsBox = 0, matsOff = 0, matte = 0, tr = 0;
+    unsigned shapes = 0, mats = 0, texs = 0, lights = 0, glass = 0, matte = 0, tr = 0;
     auto bit = [](int c) { return (c >= 0 && c < 32) ? (1u << c) : 0u; };
     for (int i = 0; i < n; i++) {
         shapes |= bit(scene->shape[i].category);
         mats |= bit(scene->shape[i].matCategory) | bit(scene->surf[i].matCategory);
-        const bool box = scene->shape[i].category == SAIL_CUBE || scene->shape[i].category == SAIL_CORNELLBOX;
-        (box ? matsBox : matsOff) |= bit(scene->shape[i].matCategory) | bit(scene->surf[i].matCategory);
         texs |= bit(scene->surf[i].texCategory);
         if (scene->shape[i].matCategory == SAIL_MATTE || scene->surf[i].matCategory == SAIL_MATTE)
             matte |= (scene->surf[i].m[SM_MATTE_SIGMA] < 1e-5f) ? 1u : 2u;  // the shader's test, matte.glsl:13 / :30 (EPSILON)
@@ -156,6 +186,11 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
             tr |= (scene->surf[i].m[SM_METAL_UR] == scene->surf[i].m[SM_METAL_VR]) ? 1u : 2u;
     }
     for (int k = 0; scene->ln > 0 && k <= scene->ln; k++) lights |= bit(scene->light[k].category);
+    // an area light samples its geometry: the sampler arms of those shapes are part of the structure too
+    unsigned lightShapes = 0;
+    for (int k = 0; scene->ln > 0 && k <= scene->ln; k++)
+        if (scene->light[k].category == SAIL_AREA && scene->light[k].object >= 0 && scene->light[k].object < n)
+            lightShapes |= bit(scene->shape[scene->light[k].object].category);
     // SAIL_B200_JIT_DEFINES="NAME=VALUE,NAME2=VALUE2": extra #defines for A/B runs of experimental code paths
     std::string extraDefs;
     if (const char* e = getenv("SAIL_B200_JIT_DEFINES")) {
@@ -172,19 +207,9 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
         }
     }
     char masks[200];
-    snprintf(masks, sizeof(masks), " plugins=%x/%x/%x/%x/%x/%x/%x", shapes, mats, texs, lights, glass, matte, tr);
+    snprintf(masks, sizeof(masks), " plugins=%x/%x/%x/%x/%x/%x/%x/%x", shapes, mats, texs, lights, glass, matte, tr, lightShapes);
     if (const char* e = extraDefs.empty() ? nullptr : getenv("SAIL_B200_JIT_DEFINES")) snprintf(masks + strlen(masks), sizeof(masks) - strlen(masks), " -D%.60s", e);
-    // kind 2 (sail_server.cuh): path warps per CTA next to the one server warp; 64 registers per thread fill the SM
-    int pathWarps = 0;
     unsigned block = SAIL_JIT_CTA_THREADS;
-    if (kind == 2) {
-        pathWarps = 7;
-        if (const char* e = getenv("SAIL_B200_SRV_WARPS")) pathWarps = atoi(e);
-        if (pathWarps < 1 || pathWarps > 31) { setErr(err, errlen, "SAIL_B200_SRV_WARPS must be 1..31"); return 2; }
-        block = (unsigned)(pathWarps + 1) * 32u;
-        minCtas = (int)(65536u / (64u * block));
-        if (minCtas < 1) minCtas = 1;
-    }
     if (kind == 1) {  // wavefront: paths per CTA (sail_wavefront.cuh SAIL_WF_THREADS), 64 registers per thread fill the SM
         // measured (tools/wf_sweep.sh, Mpaths/s at 128 / 256 / 512 paths): config 3 (quadrics) 1744 / 2059 / 2269, config 5 1204 / 1303 / 1336,
         // config 2 3930 / 3956 / 3768
@@ -194,31 +219,18 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
         block = (unsigned)wf;
         if (wf != 128) minCtas = (int)(65536u / (64u * block));
     }
-    if (kind != 2) {
-        if (const char* e = getenv("SAIL_B200_MIN_CTAS")) {  // occupancy sweeps (tools/ab_defs.sh)
-            const int v = atoi(e);
-            if (v >= 1 && v <= 16) minCtas = v;
-        }
+    if (const char* e = getenv("SAIL_B200_MIN_CTAS")) {  // occupancy sweeps (tools/ab_defs.sh)
+        const int v = atoi(e);
+        if (v >= 1 && v <= 16) minCtas = v;
     }
-    const char* kindName = kind == 2 ? "server" : (kind ? "wavefront" : "mega");
     char head[96];
-    if (kind == 2) snprintf(head, sizeof(head), "jit server<F=%d,%d+1 warps> n=%d shapes=", F, pathWarps, n);
-    else if (kind == 1 && block != 128) snprintf(head, sizeof(head), "jit wavefront<F=%d,%u paths> n=%d shapes=", F, block, n);
-    else snprintf(head, sizeof(head), "jit %s<F=%d> n=%d shapes=", kindName, F, n);
+    if (kind == 1 && block != 128) snprintf(head, sizeof(head), "jit wavefront<F=%d,%u paths> n=%d shapes=", F, block, n);
+    else snprintf(head, sizeof(head), "jit %s<F=%d> n=%d shapes=", kind ? "wavefront" : "mega", F, n);
     // One shared sqrt instead of ~50 inlined copies: pays for quadric kernels that overflow the 32 KB instruction cache (megakernel,
     // 128-path wavefront: config 3 +5..16 %), costs 3.7 % once the 512-path wavefront has taken that pressure away (2318 vs 2404
     // Mpaths/s); metal/glass-only kernels are faster inlined.  SAIL_B200_INLINE_SQRT=0/1 overrides for A/B runs.
     bool outlineSqrt = (F & 1 /* SAIL_F_QUADRICS */) && !(kind == 1 && block >= 256);
     if (const char* e = getenv("SAIL_B200_INLINE_SQRT")) outlineSqrt = e[0] == '0';
-    const std::string key = extraDefs + (outlineSqrt ? "osqrt " : "") + "dev" + std::to_string(device) + " m" + std::to_string(minCtas) + " " + head + cats + masks;
-    auto it = g_cache.find(key);
-    out->block = block;
-    out->pathWarps = pathWarps;
-    if (it != g_cache.end()) {
-        out->fn = it->second;
-        snprintf(out->info, sizeof(out->info), "%s%s%s (cached)", head, cats.c_str(), masks);
-        return 0;
-    }
     std::string tuning = outlineSqrt ? "#define SAIL_OUTLINE_SQRT 1\n" : "#define SAIL_INLINE_TRANSCENDENTALS 1\n";
     // small scenes without quadrics: the nearest-hit scan inlined at both call sites (path ray, shadow ray) instead of one shared
     // out-of-line copy -- config 5 +2.8 %, config 2 +-0; with quadrics the scan is too large (config 3 -23 %)
@@ -227,70 +239,126 @@ static int jitGetLocked(int device, int kind, int F, int minCtas, const SailScen
     snprintf(src, sizeof(src),
              "%s#define SAIL_JIT_NRUNS %d\n#define SAIL_JIT_RUN_CATS %s\n#define SAIL_JIT_RUN_STARTS %s\n#define SAIL_JIT_RUN_LENS %s\n"
              "#define SAIL_JIT_SHAPES 0x%xu\n#define SAIL_JIT_MATS 0x%xu\n#define SAIL_JIT_TEXS 0x%xu\n#define SAIL_JIT_LIGHTS 0x%xu\n"
-             "#define SAIL_JIT_GLASS %u\n#define SAIL_JIT_MATTE %u\n#define SAIL_JIT_TR %u\n#define SAIL_JIT_MATS_BOX 0x%xu\n#define SAIL_JIT_MATS_OFF 0x%xu\n#define SAIL_SRV_PATH_WARPS %d\n#define SAIL_WF_THREADS %u\n%s"
-             "#include \"sail_mega.cuh\"\n#include \"sail_wavefront.cuh\"\n#include \"sail_server.cuh\"\n"
+             "#define SAIL_JIT_GLASS %u\n#define SAIL_JIT_MATTE %u\n#define SAIL_JIT_TR %u\n#define SAIL_JIT_LIGHT_SHAPES 0x%xu\n#define SAIL_WF_THREADS %u\n%s"
+             "#include \"sail_mega.cuh\"\n#include \"sail_wavefront.cuh\"\n"
              "extern \"C\" __global__ void __launch_bounds__(%u, %d) sail_jit_kernel(const __grid_constant__ SailLaunch L) "
              "{ %s<%d>(L); }\n",
-             extraDefs.c_str(), nruns, runCat.c_str(), runStart.c_str(), runLen.c_str(), shapes, mats, texs, lights, glass, matte, tr, matsBox, matsOff,
-             pathWarps ? pathWarps : 7, kind == 1 ? block : 128u,
+             extraDefs.c_str(), nruns, runCat.c_str(), runStart.c_str(), runLen.c_str(), shapes, mats, texs, lights, glass, matte, tr, lightShapes,
+             kind == 1 ? block : 128u,
              // kernels that are not instruction-cache bound also inline the sines of the RNG, the sampler's sincos and the sphere's
              // acos / sin (measured: config 2 +2.2 %, config 5 +2.9 %, config 3 +0.5 %)
-             tuning.c_str(), block, minCtas,
-             kind == 2 ? "sailServerBody" : (kind ? "sailWaveBody" : "sailMegaBody"), F);
-    void* prog = nullptr;
-    if (g_api.createProgram(&prog, src, "sail_jit.cu", kSailJitCount, kSailJitTexts, kSailJitNames) != 0) {
-        setErr(err, errlen, "nvrtcCreateProgram failed");
-        return 3;
-    }
-    const char* opts[] = {"--gpu-architecture=sm_100a", "--fmad=false", "-std=c++17", "-lineinfo"};
-    const auto t0 = std::chrono::steady_clock::now();
-    const int rc = g_api.compileProgram(prog, 4, opts);
-    const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-    if (rc != 0) {
-        size_t ls = 0;
-        g_api.logSize(prog, &ls);
-        std::string log(ls ? ls : 1, '\0');
-        if (ls) g_api.log(prog, &log[0]);
-        g_api.destroyProgram(&prog);
-        setErr(err, errlen, "nvrtcCompileProgram failed: " + log.substr(0, 400));
-        return 4;
-    }
-    size_t cs = 0;
-    g_api.cubinSize(prog, &cs);
-    std::vector<char> cubin(cs);
-    g_api.cubin(prog, cubin.data());
-    g_api.destroyProgram(&prog);
-    if (const char* dump = getenv("SAIL_B200_JIT_DUMP")) {  // keep the cubin for cuobjdump / nvdisasm / tools/sass_lines.py
-        std::string name = std::string(dump) + "/sail_jit_" + (kind == 2 ? "server" : (kind ? "wave" : "mega")) + "_F" + std::to_string(F) + "_n" + std::to_string(n) + ".cubin";
-        if (FILE* f = fopen(name.c_str(), "wb")) { fwrite(cubin.data(), 1, cubin.size(), f); fclose(f); }
-    }
-    if (device < 0) {
-        out->fn = nullptr;
-        snprintf(out->info, sizeof(out->info), "%s%s%s (nvrtc %d.%d, %.2f s, %zu byte cubin, not loaded)", head, cats.c_str(), masks,
-                 g_api.nvrtcMajor, g_api.nvrtcMinor, secs, cs);
-        return 0;
-    }
-    void *mod = nullptr, *fn = nullptr;
-    int cr = g_api.moduleLoadData(&mod, cubin.data());
-    if (cr == 0) cr = g_api.moduleGetFunction(&fn, mod, "sail_jit_kernel");
-    // A 512-path wavefront holds 45 KB of static shared memory (exchange slots); together with the scene block of a large
-    // scene (up to 17 KB, dynamic) that passes the 48 KB a kernel gets without opting in.
-    if (cr == 0 && block > 128) cr = g_api.funcSetAttribute(fn, 8 /* CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES */, (int)sizeof(SailSceneBlock));
-    if (cr != 0) {
-        const char* es = nullptr;
-        g_api.errorString(cr, &es);
-        setErr(err, errlen, std::string("loading the compiled kernel failed: ") + (es ? es : "?"));
-        return 5;
-    }
-    g_cache[key] = fn;
-    out->fn = fn;
-    snprintf(out->info, sizeof(out->info), "%s%s%s (nvrtc %d.%d, %.2f s)", head, cats.c_str(), masks, g_api.nvrtcMajor, g_api.nvrtcMinor, secs);
+             tuning.c_str(), block, minCtas, kind ? "sailWaveBody" : "sailMegaBody", F);
+    plan->src = src;
+    // The key is the generated source itself: whatever is baked into the kernel decides which cached kernel may be reused.
+    plan->key = plan->src;
+    plan->head = head;
+    plan->cats = cats;
+    plan->masks = masks;
+    plan->block = block;
+    plan->kind = kind;
+    plan->F = F;
+    plan->n = n;
     return 0;
 }
 
-int sail_jit_get(int device, int kind, int F, int minCtas, const SailSceneBlock* scene, SailJitKernel* out, char* err, int errlen) {
+void compileJob(SailJitJob* job) {
+    void* prog = nullptr;
+    int rc = 0;
+    std::string msg;
+    std::vector<char> cubin;
+    const auto t0 = std::chrono::steady_clock::now();
+    if (g_api.createProgram(&prog, job->plan.src.c_str(), "sail_jit.cu", kSailJitCount, kSailJitTexts, kSailJitNames) != 0) {
+        rc = 3;
+        msg = "nvrtcCreateProgram failed";
+    } else {
+        const char* opts[] = {"--gpu-architecture=sm_100a", "--fmad=false", "-std=c++17", "-lineinfo"};
+        if (g_api.compileProgram(prog, 4, opts) != 0) {
+            size_t ls = 0;
+            g_api.logSize(prog, &ls);
+            std::string log(ls ? ls : 1, '\0');
+            if (ls) g_api.log(prog, &log[0]);
+            rc = 4;
+            msg = "nvrtcCompileProgram failed: " + log.substr(0, 400);
+        } else {
+            size_t cs = 0;
+            g_api.cubinSize(prog, &cs);
+            cubin.resize(cs);
+            g_api.cubin(prog, cubin.data());
+        }
+        g_api.destroyProgram(&prog);
+    }
+    const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (rc == 0)
+        if (const char* dump = getenv("SAIL_B200_JIT_DUMP")) {  // keep the cubin for cuobjdump / nvdisasm / tools/sass_lines.py
+            std::string name = std::string(dump) + "/sail_jit_" + (job->plan.kind ? "wave" : "mega") + "_F" + std::to_string(job->plan.F) + "_n" + std::to_string(job->plan.n) + ".cubin";
+            if (FILE* f = fopen(name.c_str(), "wb")) { fwrite(cubin.data(), 1, cubin.size(), f); fclose(f); }
+        }
+    {
+        std::lock_guard<std::mutex> lk(job->m);
+        job->rc = rc;
+        job->err = msg;
+        job->cubin.swap(cubin);
+        job->secs = secs;
+        job->done = true;
+    }
+    job->cv.notify_all();
+}
+
+}  // namespace
+
+SailJitJob* sail_jit_request(int kind, int F, int minCtas, const SailSceneBlock* scene, char* err, int errlen) {
     std::lock_guard<std::mutex> lock(g_mutex);
-    return jitGetLocked(device, kind, F, minCtas, scene, out, err, errlen);
+    if (!loadApi()) { setErr(err, errlen, g_api.why); return nullptr; }
+    Plan plan;
+    if (makePlan(kind, F, minCtas, scene, &plan, err, errlen) != 0) return nullptr;
+    auto it = g_reg.jobs.find(plan.key);
+    if (it != g_reg.jobs.end()) return it->second;
+    SailJitJob* job = new SailJitJob;
+    job->plan = plan;
+    g_reg.jobs[plan.key] = job;
+    job->worker = std::thread(compileJob, job);
+    return job;
+}
+
+int sail_jit_poll(SailJitJob* job, int device, int wait, SailJitKernel* out, char* err, int errlen) {
+    if (!job) { setErr(err, errlen, "no job"); return -1; }
+    {
+        std::unique_lock<std::mutex> lk(job->m);
+        if (!job->done) {
+            if (!wait) return 1;
+            job->cv.wait(lk, [job] { return job->done; });
+        }
+        if (job->rc != 0) { setErr(err, errlen, job->err); return -job->rc; }
+    }
+    const Plan& p = job->plan;
+    out->block = p.block;
+    out->fn = nullptr;
+    if (device < 0) {
+        snprintf(out->info, sizeof(out->info), "%s%s%s (nvrtc %d.%d, %.2f s, %zu byte cubin, not loaded)", p.head.c_str(), p.cats.c_str(), p.masks.c_str(),
+                 g_api.nvrtcMajor, g_api.nvrtcMinor, job->secs, job->cubin.size());
+        return 0;
+    }
+    std::lock_guard<std::mutex> lock(g_mutex);
+    if (!loadDriver()) { setErr(err, errlen, g_api.cuWhy); return -1; }
+    auto it = job->fn.find(device);
+    if (it == job->fn.end()) {
+        void *mod = nullptr, *fn = nullptr;
+        int cr = g_api.moduleLoadData(&mod, job->cubin.data());
+        if (cr == 0) cr = g_api.moduleGetFunction(&fn, mod, "sail_jit_kernel");
+        // A 512-path wavefront holds 45 KB of static shared memory (exchange slots); together with the scene block of a large
+        // scene (up to 17 KB, dynamic) that passes the 48 KB a kernel gets without opting in.
+        if (cr == 0 && p.block > 128) cr = g_api.funcSetAttribute(fn, 8 /* CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES */, (int)sizeof(SailSceneBlock));
+        if (cr != 0) {
+            const char* es = nullptr;
+            g_api.errorString(cr, &es);
+            setErr(err, errlen, std::string("loading the compiled kernel failed: ") + (es ? es : "?"));
+            return -5;
+        }
+        it = job->fn.emplace(device, fn).first;
+    }
+    out->fn = it->second;
+    snprintf(out->info, sizeof(out->info), "%s%s%s (nvrtc %d.%d, %.2f s)", p.head.c_str(), p.cats.c_str(), p.masks.c_str(), g_api.nvrtcMajor, g_api.nvrtcMinor, job->secs);
+    return 0;
 }
 
 int sail_jit_launch(void* fn, const void* launch, unsigned gridX, unsigned gridY, unsigned block, unsigned smemBytes, void* stream,

@@ -44,8 +44,8 @@ SD V2 sinPair(float a, float b) {
     float va = (qa & 1) ? ca : sa, vb = (qb & 1) ? cb : sb;
     va = (qa & 2) ? -va : va;
     vb = (qb & 2) ? -vb : vb;
-    if (!(dm_abs(a) < 4194304.0f)) va = dm_sub(a, a);
-    if (!(dm_abs(b) < 4194304.0f)) vb = dm_sub(b, b);
+    if (!(dm_abs(a) < 4194304.0f)) va = dm_sin_large(a);  // Payne-Hanek (detmath.h): hours into a session, rare and warp-uniform in practice
+    if (!(dm_abs(b) < 4194304.0f)) vb = dm_sin_large(b);
     return mk2(va, vb);
 }
 static __device__ __noinline__ float2 sail_sin2(float a, float b) { V2 v = sinPair(a, b); return make_float2(v.x, v.y); }
@@ -276,10 +276,9 @@ SD V3 orenNayar_f(V3 R, float A, float B, V3 wo, V3 wi) {
 
 // ---- material(): shader.material.js:21-29 + matte/mirror/metal/glass.glsl ---------------------------
 // Returns fpdf (unclamped); writes wi (local frame) and, for matte only, f = matte_f().
-// matMask: material categories the caller can meet (bit = category id); arms outside it are not compiled.
-#define SAIL_MAT_ARM(c) (SAIL_HAS_MAT(c) && ((matMask >> (c)) & 1u))
+#define SAIL_MAT_ARM(c) SAIL_HAS_MAT(c)
 template <int F>
-SD V3 material(const SailSurface& su, int matCategory, V3 sc, bool into, V2 u, V3 wo, V3& wi, V3& f, const unsigned matMask = 0xffffffffu) {
+SD V3 material(const SailSurface& su, int matCategory, V3 sc, bool into, V2 u, V3 wo, V3& wi, V3& f) {
     const float* m = su.m;
     wi = splat3(0.0f);
     f = splat3(0.0f);
@@ -374,7 +373,7 @@ static __device__ __noinline__ V3 stubShapeNormal(const SailShape& s) {
     switch (s.category) {
         case SAIL_CUBE: return boxFaceNormal(hit, loOf(s), hiOf(s), s.rev);       // cube.glsl:25-38
         case SAIL_CORNELLBOX: return boxFaceNormal(hit, loOf(s), hiOf(s), 1.0f);  // cornellbox.glsl:39-51
-        case SAIL_CONE: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_CONE)) {  // cone.glsl:38-46
+        case SAIL_CONE: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_LIGHT_SHAPE(SAIL_CONE)) {  // cone.glsl:38-46
             V3 hh = hit - ld3(q + SQ_CONE_P);
             float d = dm_sqrt(hh.x * hh.x + hh.y * hh.y);
             float x1 = d * q[SQ_CONE_INVTANA];
@@ -382,9 +381,9 @@ static __device__ __noinline__ V3 stubShapeNormal(const SailShape& s) {
             V3 no = mk3(0.0f, 0.0f, q[SQ_CONE_H] - x1 - x2);
             return s.rev * normalize3(hh - no);
         }
-        case SAIL_CYLINDER: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_CYLINDER))  // cylinder.glsl:36-38
+        case SAIL_CYLINDER: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_LIGHT_SHAPE(SAIL_CYLINDER))  // cylinder.glsl:36-38
             return s.rev * normalize3(mk3(hit.x - q[SQ_CYL_P], hit.y - q[SQ_CYL_P + 1], 0.0f));
-        case SAIL_HYPERBOLOID: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_HYPERBOLOID)) {  // hyperboloid.glsl:48-58
+        case SAIL_HYPERBOLOID: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_LIGHT_SHAPE(SAIL_HYPERBOLOID)) {  // hyperboloid.glsl:48-58
             V3 p1 = ld3(q + SQ_HYP_P1), p2 = ld3(q + SQ_HYP_P2);
             float v = (hit.z - p1.z) * q[SQ_HYP_INVDZ];
             V3 pr = (1.0f - v) * p1 + v * p2;
@@ -396,7 +395,7 @@ static __device__ __noinline__ V3 stubShapeNormal(const SailShape& s) {
             V3 dpdv = mk3((p2.x - p1.x) * cp - (p2.y - p1.y) * sp, (p2.x - p1.x) * sp + (p2.y - p1.y) * cp, p2.z - p1.z);
             return s.rev * objToWorld(normalize3(cross3(dpdu, dpdv)));
         }
-        case SAIL_PARABOLOID: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_PARABOLOID)) {  // paraboloid.glsl:42-49
+        case SAIL_PARABOLOID: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_LIGHT_SHAPE(SAIL_PARABOLOID)) {  // paraboloid.glsl:42-49
             V3 dpdu = dpduAround(hit.x, hit.y);
             float inv = dm_rcp(2.0f * hit.z);
             V3 dpdv = q[SQ_PAR_DZ] * mk3(hit.x * inv, hit.y * inv, 1.0f);
@@ -413,20 +412,20 @@ SD V3 sampleGeometry(const SceneView& sc, V2 u, int i, V3& normal, float& pdf) {
     const SailShape& s = sc.shape[i];
     const float* q = s.q;
     switch (s.category) {
-        case SAIL_SPHERE: if (SAIL_HAS_SHAPE(SAIL_SPHERE)) {  // sphere.glsl:29-31,88-92
+        case SAIL_SPHERE: if (SAIL_HAS_LIGHT_SHAPE(SAIL_SPHERE)) {  // sphere.glsl:29-31,88-92
             V3 c = ld3(q + SQ_SPH_C);
             V3 p = uniformSampleSphere(u) * q[SQ_SPH_R] + c;
             pdf = q[SQ_SPH_PDF];
             normal = (s.rev * (p - c)) * q[SQ_SPH_INVR];
             return p;
         }
-        case SAIL_RECTANGLE: if (SAIL_HAS_SHAPE(SAIL_RECTANGLE)) {  // rectangle.glsl:25-30,65-70
+        case SAIL_RECTANGLE: if (SAIL_HAS_LIGHT_SHAPE(SAIL_RECTANGLE)) {  // rectangle.glsl:25-30,65-70
             V3 p = loOf(s) + ld3(q + SQ_RECT_DPDU) * u.x + ld3(q + SQ_RECT_DPDV) * u.y;
             pdf = q[SQ_RECT_PDF];
             normal = s.rev * ld3(q + SQ_RECT_N);
             return p;
         }
-        case SAIL_DISK: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_SHAPE(SAIL_DISK)) {  // disk.glsl:32-34,77-83
+        case SAIL_DISK: if ((F & SAIL_F_QUADRICS) && SAIL_HAS_LIGHT_SHAPE(SAIL_DISK)) {  // disk.glsl:32-34,77-83
             V2 pd = concentricSampleDisk(u);
             V3 p = mk3(pd.x * q[SQ_DISK_R] + q[SQ_DISK_P], q[SQ_DISK_P + 1], pd.y * q[SQ_DISK_R] + q[SQ_DISK_P + 2]);
             pdf = q[SQ_DISK_PDF];
@@ -434,7 +433,7 @@ SD V3 sampleGeometry(const SceneView& sc, V2 u, int i, V3& normal, float& pdf) {
             return p;
         }
     }
-    normal = stubShapeNormal<F>(s);
+    if (SAIL_HAS_STUB_LIGHT_SHAPE) normal = stubShapeNormal<F>(s);
     return splat3(0.0f);
 }
 
@@ -485,12 +484,12 @@ SD V3 light_sample(const SceneView& sc, V2 u, V3 hit, V3 insNormal) {
 
 // ---- shade(), path.glsl:1-14 ----------------------------------------------------------------------------
 template <int F>
-SD V3 shade(const SceneView& sc, const Hit& h, V2 u, V3 wo, V3& wi, V3& fpdf, const unsigned matMask = 0xffffffffu) {
+SD V3 shade(const SceneView& sc, const Hit& h, V2 u, V3 wo, V3& wi, V3& fpdf) {
     V3 f;
     // box faces: |dpdu| is exactly 1 (components 0 / +-1), so normalize() multiplies by rcp(sqrt(1)) = 1
     V3 ss = h.unitDpdu ? h.dpdu : normalize3(h.dpdu), ts = cross3(h.n, ss);
     wo = worldToLocal(wo, h.n, ss, ts);
-    fpdf = vclamp01(material<F>(sc.surf[h.index], h.matCategory, h.sc, h.into, u, wo, wi, f, matMask));
+    fpdf = vclamp01(material<F>(sc.surf[h.index], h.matCategory, h.sc, h.into, u, wo, wi, f));
     wi = localToWorld(wi, h.n, ss, ts);
     V3 direct = splat3(0.0f);
     if ((F & SAIL_F_NEE) && isblack(h.emission) && h.matCategory == SAIL_MATTE) direct = direct + light_sample<F>(sc, u, h.p, h.n) * f;

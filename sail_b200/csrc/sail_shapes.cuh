@@ -71,6 +71,9 @@ enum { SAIL_F_QUADRICS = 1,  // cone, cylinder, disk, hyperboloid, paraboloid pr
 #define SAIL_HAS_MAT(c) ((((unsigned)(SAIL_JIT_MATS)) >> (c)) & 1u)
 #define SAIL_HAS_TEX(c) ((((unsigned)(SAIL_JIT_TEXS)) >> (c)) & 1u)
 #define SAIL_HAS_LIGHT(c) ((((unsigned)(SAIL_JIT_LIGHTS)) >> (c)) & 1u)
+// shapes that are the geometry of an area light: only their samplers (sampleX / the stub + normalForX) are compiled
+#define SAIL_HAS_LIGHT_SHAPE(c) ((((unsigned)(SAIL_JIT_LIGHT_SHAPES)) >> (c)) & 1u)
+#define SAIL_HAS_STUB_LIGHT_SHAPE ((((unsigned)(SAIL_JIT_LIGHT_SHAPES)) & ~((1u << SAIL_SPHERE) | (1u << SAIL_RECTANGLE) | (1u << SAIL_DISK))) != 0u)
 #define SAIL_HAS_SMOOTH_GLASS ((SAIL_JIT_GLASS) & 1)
 #define SAIL_HAS_ROUGH_GLASS ((SAIL_JIT_GLASS) & 2)
 #define SAIL_HAS_LAMBERT ((SAIL_JIT_MATTE) & 1)
@@ -86,6 +89,8 @@ enum { SAIL_F_QUADRICS = 1,  // cone, cylinder, disk, hyperboloid, paraboloid pr
 #define SAIL_HAS_MAT(c) 1
 #define SAIL_HAS_TEX(c) 1
 #define SAIL_HAS_LIGHT(c) 1
+#define SAIL_HAS_LIGHT_SHAPE(c) 1
+#define SAIL_HAS_STUB_LIGHT_SHAPE 1
 #define SAIL_HAS_SMOOTH_GLASS 1
 #define SAIL_HAS_ROUGH_GLASS 1
 #endif
@@ -488,9 +493,7 @@ SD V3 boxDpdu(V3 normal) {  // cube.glsl:40-48
 
 // Phase 2: the full hit record of object `i` at distance `t` (the body of intersectX() after the hit
 // test, the per-arm emission mask of shader.shape.js:47-49 and the tail of :38-40).
-// MODE 0: any shape.  MODE 1: the caller knows object i is a cube / Cornell box, MODE 2: that it is not (the
-// path-warp and server-warp halves of sail_server.cuh); the arms of the other kind are not compiled.
-template <int F, int MODE = 0>
+template <int F>
 SD void hitRecord(const SceneView& sc, int i, float t, const Ray& ray, Hit& h) {
     const SailShape& s = sc.shape[i];
     const SailSurface& u = sc.surf[i];
@@ -500,11 +503,11 @@ SD void hitRecord(const SceneView& sc, int i, float t, const Ray& ray, Hit& h) {
     V2 uv = mk2(0.0f, 0.0f);
     h.d = t;
     h.index = i;
-    h.unitDpdu = MODE == 1 ? true : (MODE == 2 ? false : (s.category == SAIL_CUBE || s.category == SAIL_CORNELLBOX));
-    const int cat = MODE == 1 ? (s.category == SAIL_CORNELLBOX ? SAIL_CORNELLBOX : SAIL_CUBE) : s.category;
+    h.unitDpdu = s.category == SAIL_CUBE || s.category == SAIL_CORNELLBOX;
+    const int cat = s.category;
     switch (cat) {
         case SAIL_CUBE:          // cube.glsl:25-48,79-85
-        case SAIL_CORNELLBOX: if (MODE != 2) {  // cornellbox.glsl:23-51,81-88
+        case SAIL_CORNELLBOX: {  // cornellbox.glsl:23-51,81-88
             // One branch-free path for both boxes: the face is picked with the shader's comparison chain
             // (x-, x+, y-, y+, z-, z+), its normal and dpdu come from the per-face table built at upload.
             V3 mn = loOf(s), mx = hiOf(s);

@@ -59,16 +59,26 @@ class Tracer:
 
 
 class Renderer:
-    """renderer.js:8-73.  ``canvas`` is ``(width, height)`` or an object with ``width``/``height``."""
+    """renderer.js:8-73.  ``canvas`` is ``(width, height)`` or an object with ``width``/``height``.
 
-    def __init__(self, canvas, device=0, rows=None, schedule=None):
+    Multi-GPU (the reference has one GL context): ``devices=[0, 1, ...]`` makes one renderer over several
+    GPUs of this process, ``group=(nranks, rank, group_id)`` makes this renderer one member of a group with one GPU per
+    process (every member then issues the same calls; images arrive on rank 0).  ``shard`` = capi.SHARD_SAMPLE or
+    capi.SHARD_TILE; the split, the collective and the combined image all live behind the C ABI."""
+
+    def __init__(self, canvas, device=0, rows=None, schedule=None, devices=None, shard=capi.SHARD_SAMPLE, band_rows=0,
+                 combine=capi.COMBINE_AUTO, group=None):
         if isinstance(canvas, (tuple, list)):
             width, height = canvas
         elif isinstance(canvas, dict):
             width, height = canvas["width"], canvas["height"]
         else:
             width, height = canvas.width, canvas.height
-        self.ctx = capi.Context(width, height, device=device, rows=rows)
+        self.ctx = capi.Context(width, height, device=device, rows=rows, devices=devices, shard=shard, band_rows=band_rows,
+                                combine=combine)
+        if group is not None:
+            nranks, rank, group_id = group
+            self.ctx.group_join(nranks, rank, group_id, shard=shard, band_rows=band_rows, combine=combine)
         self.tracer = Tracer(self.ctx, schedule)
         self._filter = None
 
@@ -113,16 +123,17 @@ class Renderer:
         self.trace(scene, frames)
         prev = self.flush()
         self._slot = 1 - getattr(self, "_slot", 1)
-        self._inflight = self.ctx.present_begin(self._slot)
+        self._inflight = self.ctx.present_begin(self._slot)  # None on the non-root members of a group
+        self._pending = True
         return prev
 
     def flush(self):
         """Wait for the image queued by the last ``render_pipelined`` and return it (``None`` if there is none)."""
-        buf = getattr(self, "_inflight", None)
-        if buf is None:
+        if not getattr(self, "_pending", False):
             return None
         self.ctx.present_end()
-        self._inflight = None
+        self._pending = False
+        buf, self._inflight = self._inflight, None
         return buf
 
     def save(self, path, img=None):

@@ -9,6 +9,12 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
+# SAIL_SPECIALISE_AUTO compiles the scene's kernel on a worker thread and serves the first frames with the ahead-of-time
+# variant; the suite is about the specialised kernels as much as about those, so here AUTO waits for the compiler
+# (tests of the asynchronous hand-over remove the variable themselves).
+os.environ.setdefault("SAIL_B200_JIT_SYNC", "1")
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a real B200 (run with -m gpu on the GPU box)")
 

@@ -38,7 +38,7 @@ def test_header_declares_and_library_exports(capi):
 
 
 def test_struct_layouts(capi):
-    assert ctypes.sizeof(capi.CreateInfo) == 32
+    assert ctypes.sizeof(capi.CreateInfo) == 5 * 4 + 3 * 4 + 8 * 4 + 4 + 3 * 4 and capi.CreateInfo.device_ids.offset == 32
     assert ctypes.sizeof(capi.Config) == 4 * 4 + 5 * 4 + 4 + 8 + 64 + 16
     assert ctypes.sizeof(capi.Frame) == 84
     assert capi.Frame.eye.offset == 64 and capi.Frame.textureWeight.offset == 76
@@ -47,7 +47,7 @@ def test_struct_layouts(capi):
 
 def test_version_and_defaults(capi):
     lib = capi.load()
-    assert lib.sail_abi_version() == 1
+    assert lib.sail_abi_version() == capi.ABI_VERSION == 2
     assert b"sm_100a" in lib.sail_version()
     cfg = capi.Config()
     lib.sail_default_config(ctypes.byref(cfg))
@@ -113,7 +113,7 @@ def test_scene_specialised_kernels_compile_without_a_gpu(capi, cfg):
     """The kernels that NVRTC builds per scene structure at run time must compile for every
     BASELINE config -- checked here with sail_jit_compile_check, which needs NVRTC but no device."""
     _, o, t, l, _ = scene_tables(cfg, 64, 64)
-    for kernel in (capi.KERNEL_MEGA, capi.KERNEL_WAVEFRONT, capi.KERNEL_SERVER):
+    for kernel in (capi.KERNEL_MEGA, capi.KERNEL_WAVEFRONT):
         try:
             info = capi.jit_compile_check(o, t, l, kernel)
         except capi.SailError as e:
@@ -125,7 +125,7 @@ def test_scene_specialised_kernels_compile_without_a_gpu(capi, cfg):
 
 def test_kernel_build_knobs_compile(capi, monkeypatch):
     """The knobs sail_jit.cpp reads from the environment when it builds a kernel: extra #defines (the literal last bounce
-    that bench.py reports next to the default), the wavefront's paths per CTA, the server kernel's path warps."""
+    that bench.py reports next to the default), the wavefront's paths per CTA."""
     _, o, t, l, _ = scene_tables(3, 64, 64)
     try:
         monkeypatch.setenv("SAIL_B200_JIT_DEFINES", "SAIL_LITERAL_LAST_BOUNCE")
@@ -137,8 +137,6 @@ def test_kernel_build_knobs_compile(capi, monkeypatch):
         monkeypatch.setenv("SAIL_B200_WF_THREADS", "100")
         with pytest.raises(capi.SailError):
             capi.jit_compile_check(o, t, l, capi.KERNEL_WAVEFRONT)
-        monkeypatch.setenv("SAIL_B200_SRV_WARPS", "3")
-        assert "3+1 warps" in capi.jit_compile_check(o, t, l, capi.KERNEL_SERVER)
     except capi.SailError as e:
         if "NVRTC not found" in str(e):
             pytest.skip("no NVRTC on this machine")

@@ -57,20 +57,6 @@ def test_frames_bit_exact(capi, oracle, cfg, kernel, specialise):
         assert bits_equal(out[name], ref[name]), mismatch_report(out[name], ref[name], "cfg%d %s" % (cfg, name))
 
 
-@pytest.mark.parametrize("warps", [7, 3, 1])
-@pytest.mark.parametrize("cfg", [1, 2, 3, 5])
-def test_server_kernel_bit_exact(capi, oracle, cfg, warps, monkeypatch):
-    """The server-warp kernel (sail_server.cuh; run-time compiled only): non-box hits of all path warps of a CTA are
-    evaluated together by one server warp -- same bits as the oracle, for every CTA shape."""
-    monkeypatch.setenv("SAIL_B200_SRV_WARPS", str(warps))
-    for batch in (False, True):
-        out, ref = _render_both(capi, oracle, cfg, 4, kernel=capi.KERNEL_SERVER, batch=batch, specialise=2)
-        assert out["kernel_info"].startswith("jit server<"), out["kernel_info"]
-        assert np.array_equal(out["hit_id"], ref["hit_id"]), "primary hit ids differ"
-        for name in ("depth", "normal", "position", "color"):
-            assert bits_equal(out[name], ref[name]), mismatch_report(out[name], ref[name], "cfg%d %s" % (cfg, name))
-
-
 def _render_tables(capi, oracle, o, t, l, scene, W, H, nframes, bounces, kernel, specialise=0):
     oracle.set_scene(o, t, l)
     acc = np.zeros((H, W, 3), np.float32)
@@ -95,7 +81,7 @@ def _assert_same(out, ref, what):
         assert bits_equal(out[name], ref[name]), mismatch_report(out[name], ref[name], "%s %s" % (what, name))
 
 
-@pytest.mark.parametrize("kernel", [0, 1, 3], ids=["mega", "wavefront", "server"])
+@pytest.mark.parametrize("kernel", [0, 1], ids=["mega", "wavefront"])
 @pytest.mark.parametrize("bounces", [1, 2, 3])
 @pytest.mark.parametrize("cfg", [1, 2])
 def test_short_paths_bit_exact(capi, oracle, cfg, bounces, kernel):
@@ -108,7 +94,7 @@ def test_short_paths_bit_exact(capi, oracle, cfg, bounces, kernel):
     _assert_same(out, ref, "cfg%d bounces=%d" % (cfg, bounces))
 
 
-@pytest.mark.parametrize("kernel", [0, 1, 3], ids=["mega", "wavefront", "server"])
+@pytest.mark.parametrize("kernel", [0, 1], ids=["mega", "wavefront"])
 def test_emissive_mask_edge_cases(capi, oracle, kernel):
     """Emission that is negative, NaN-free but signed-zero, on a sphere and on objects past index 31 (the emissive
     mask of the scene header covers 32 objects; later ones always count as emissive)."""
@@ -288,7 +274,7 @@ def test_present_filters(capi, oracle, name, params):
     assert np.array_equal(g8, r8)
 
 
-@pytest.mark.parametrize("kernel", [2, 3], ids=["auto", "server"])
+@pytest.mark.parametrize("kernel", [2, 1], ids=["auto", "wavefront"])
 def test_tile_rows_and_sum_mode(capi, oracle, kernel):
     """Row-sharded contexts reproduce the full frame; SUM accumulation equals the mean within rounding."""
     W, H = SIZES[2]
@@ -399,7 +385,7 @@ def test_cuda_matches_golden_fixture(capi, cfg):
         assert bits_equal(ctx.read_accum(), gold["c%d_color" % cfg])
 
 
-@pytest.mark.parametrize("kernel", [2, 3], ids=["auto", "server"])
+@pytest.mark.parametrize("kernel", [2, 1], ids=["auto", "wavefront"])
 def test_interleaved_row_bands(capi, kernel):
     """sail_set_row_bands(): 3 contexts with interleaved 8-row bands reproduce the full frame bit for bit."""
     W, H = 128, 72

@@ -1,4 +1,4 @@
-"""Device-free NVRTC build of a BASELINE config's kernel: python tools/jit_check.py <config 1|2|3|5> <kernel 0 mega|1 wavefront|3 server>
+"""Device-free NVRTC build of a BASELINE config's kernel: python tools/jit_check.py <config 1|2|3|5> <kernel 0 mega|1 wavefront>
 (SAIL_B200_JIT_DUMP=<dir> keeps the cubin; SAIL_B200_JIT_DEFINES adds #defines)."""
 import os
 import sys
