@@ -40,8 +40,9 @@ struct SailMember {
     float *accum = nullptr, *normal = nullptr, *position = nullptr, *depth = nullptr;
     int* hitId = nullptr;
     bool timed = false;
-    void* jitFn[2] = {nullptr, nullptr};  // kind 0 mega, 1 wavefront: the scene-specialised kernel loaded on this device
-    unsigned jitBlock[2] = {0, 0};
+    // the scene-specialised kernels loaded on this device: [kind 0 mega, 1 wavefront][0 full-range RNG sine, 1 |arg| < 2^22 only]
+    void* jitFn[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
+    unsigned jitBlock[2][2] = {{0, 0}, {0, 0}};
     sailNcclComm_t comm = nullptr;
 };
 
@@ -75,13 +76,13 @@ struct sail_ctx {
     SailSceneBlock hostScene;
     uint64_t launches = 0;
     // scene-specialised kernels (sail_jit.cpp): requested per kernel kind after an upload, compiled on a worker thread
-    SailJitJob* jitJob[2] = {nullptr, nullptr};
-    bool jitRequested[2] = {false, false}, jitFailed[2] = {false, false};
-    char jitNote[2][320];
+    SailJitJob* jitJob[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
+    bool jitRequested[2][2] = {{false, false}, {false, false}}, jitFailed[2][2] = {{false, false}, {false, false}};
+    char jitNote[2][2][320];
     char kernelInfo[400];
     char err[512];
     sail_ctx() {
-        err[0] = 0; kernelInfo[0] = 0; jitNote[0][0] = jitNote[1][0] = 0; combineInfo[0] = 0;
+        err[0] = 0; kernelInfo[0] = 0; memset(jitNote, 0, sizeof(jitNote)); combineInfo[0] = 0;
         memset(&lastFrame, 0, sizeof(lastFrame));
     }
     bool grouped() const { return groupSize > 1; }
@@ -183,13 +184,13 @@ int uploadBlock(sail_ctx* ctx, const SailSceneBlock& blk) {
     for (int i = 0; i < ctx->nlocal; i++) {
         CU(cudaSetDevice(ctx->mem[i].device));
         CU(cudaStreamSynchronize(ctx->mem[i].stream));  // hostScene may be rewritten by the next upload
-        ctx->mem[i].jitFn[0] = ctx->mem[i].jitFn[1] = nullptr;
+        memset(ctx->mem[i].jitFn, 0, sizeof(ctx->mem[i].jitFn));
     }
     ctx->sceneLoaded = true;
     // the structure may have changed: look the specialised kernels up again
-    ctx->jitRequested[0] = ctx->jitRequested[1] = false;
-    ctx->jitFailed[0] = ctx->jitFailed[1] = false;
-    ctx->jitJob[0] = ctx->jitJob[1] = nullptr;
+    memset(ctx->jitRequested, 0, sizeof(ctx->jitRequested));
+    memset(ctx->jitFailed, 0, sizeof(ctx->jitFailed));
+    memset(ctx->jitJob, 0, sizeof(ctx->jitJob));
     ctx->aovValid = false;
     return SAIL_OK;
 }
@@ -448,46 +449,61 @@ int kernelKind(const sail_ctx* ctx, int F, bool jit) {
 
 // Looks after the scene-specialised kernel of `kind`: requests its compilation once per upload and, when the cubin is
 // there, loads it on every local member.  Returns true when all members have it.  `wait` blocks on the compiler.
-bool specialisedReady(sail_ctx* ctx, int kind, int F, bool wait) {
-    if (ctx->jitFailed[kind]) return false;
+bool specialisedReady(sail_ctx* ctx, int kind, int small, int F, bool wait) {
+    if (ctx->jitFailed[kind][small]) return false;
     // SAIL_B200_JIT_SYNC=1: SAIL_SPECIALISE_AUTO waits for the compiler too (test suites that must exercise the specialised kernels)
     const char* sync = getenv("SAIL_B200_JIT_SYNC");
     const bool alwaysWait = sync && sync[0] == '1';
     wait = wait || alwaysWait;
-    if (!ctx->jitRequested[kind]) {
-        ctx->jitRequested[kind] = true;
+    char* note = ctx->jitNote[kind][small];
+    const size_t noteLen = sizeof(ctx->jitNote[kind][small]);
+    if (!ctx->jitRequested[kind][small]) {
+        ctx->jitRequested[kind][small] = true;
         char why[300];
         why[0] = 0;
-        ctx->jitJob[kind] = sail_jit_request(kind, F, SAIL_MIN_CTAS(F), &ctx->hostScene, why, sizeof(why));
-        if (!ctx->jitJob[kind]) {
-            ctx->jitFailed[kind] = true;
-            snprintf(ctx->jitNote[kind], sizeof(ctx->jitNote[kind]), "jit: %s", why);
+        ctx->jitJob[kind][small] = sail_jit_request(kind, F, SAIL_MIN_CTAS(F), small, &ctx->hostScene, why, sizeof(why));
+        if (!ctx->jitJob[kind][small]) {
+            ctx->jitFailed[kind][small] = true;
+            snprintf(note, noteLen, "jit: %s", why);
             return false;
         }
-        snprintf(ctx->jitNote[kind], sizeof(ctx->jitNote[kind]), "jit: compiling");
+        snprintf(note, noteLen, "jit: compiling");
     }
     bool all = true;
     for (int i = 0; i < ctx->nlocal; i++) {
         SailMember& m = ctx->mem[i];
-        if (m.jitFn[kind]) continue;
+        if (m.jitFn[kind][small]) continue;
         SailJitKernel k;
         char why[300];
         why[0] = 0;
         if (cudaSetDevice(m.device) != cudaSuccess) { cudaGetLastError(); all = false; continue; }
-        const int rc = sail_jit_poll(ctx->jitJob[kind], m.device, wait ? 1 : 0, &k, why, sizeof(why));
+        const int rc = sail_jit_poll(ctx->jitJob[kind][small], m.device, wait ? 1 : 0, &k, why, sizeof(why));
         if (rc == 0) {
-            m.jitFn[kind] = k.fn;
-            m.jitBlock[kind] = k.block;
-            snprintf(ctx->jitNote[kind], sizeof(ctx->jitNote[kind]), "%s", k.info);
+            m.jitFn[kind][small] = k.fn;
+            m.jitBlock[kind][small] = k.block;
+            snprintf(note, noteLen, "%s", k.info);
         } else if (rc < 0) {
-            ctx->jitFailed[kind] = true;
-            snprintf(ctx->jitNote[kind], sizeof(ctx->jitNote[kind]), "jit: %s", why);
+            ctx->jitFailed[kind][small] = true;
+            snprintf(note, noteLen, "jit: %s", why);
             return false;
         } else {
             all = false;
         }
     }
     return all;
+}
+
+// The hash RNG takes sin(dot(gl_FragCoord.xyz + seed, K)) with seed = timeSinceStart + bounce (src/shader/util/random.glsl:1-18,
+// src/shader/trace/path.glsl:21).  True when that argument stays below 2^22 -- the range of the fast reduction in detmath.h --
+// for every pixel, bounce and frame of the call: all terms are positive, so the corner pixel with the largest seed bounds it.
+// (About the first 95 minutes of a session at 4K; afterwards the kernel with the full-range sine runs.)
+bool rngArgsSmall(const sail_ctx* ctx, const sail_frame* frames, int count) {
+    float tmax = 0.0f;
+    for (int k = 0; k < count; k++) tmax = frames[k].timeSinceStart > tmax ? frames[k].timeSinceStart : tmax;
+    const double seed = (double)tmax + (double)(ctx->cfg.max_bounces > 1 ? ctx->cfg.max_bounces : 1);
+    const double ax = (double)ctx->W + seed, ay = (double)ctx->H + seed, az = 0.5 + seed;
+    const double d1 = ax * 12.9898 + ay * 78.233 + az * 151.7182, d2 = ax * 63.7264 + ay * 10.873 + az * 623.6736;
+    return (d1 > d2 ? d1 : d2) * 1.001 < 4194304.0;
 }
 
 }  // namespace
@@ -741,7 +757,7 @@ int sail_jit_compile_check(const float* objects, int32_t n, const float* texpara
         char why[400];
         why[0] = 0;
         const int F = blk->features & SAIL_F_ALL;
-        SailJitJob* job = sail_jit_request(kernel == SAIL_KERNEL_WAVEFRONT ? 1 : 0, F, SAIL_MIN_CTAS(F), blk, why, sizeof(why));
+        SailJitJob* job = sail_jit_request(kernel == SAIL_KERNEL_WAVEFRONT ? 1 : 0, F, SAIL_MIN_CTAS(F), 1, blk, why, sizeof(why));
         if (job && sail_jit_poll(job, -1, 1, &k, why, sizeof(why)) == 0) {
             if (info && infolen > 0) snprintf(info, (size_t)infolen, "%s", k.info);
         } else {
@@ -797,14 +813,15 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
     const int F = ctx->hostScene.features & SAIL_F_ALL;
     const bool tryJit = ctx->cfg.specialise != SAIL_SPECIALISE_OFF;
     int kind = kernelKind(ctx, F, tryJit);
+    const int small = rngArgsSmall(ctx, frames, count) ? 1 : 0;
     bool jit = false;
     if (tryJit) {
-        jit = specialisedReady(ctx, kind, F, ctx->cfg.specialise == SAIL_SPECIALISE_REQUIRE);
+        jit = specialisedReady(ctx, kind, small, F, ctx->cfg.specialise == SAIL_SPECIALISE_REQUIRE);
         if (!jit && ctx->cfg.specialise == SAIL_SPECIALISE_REQUIRE)
-            return setErr(ctx, SAIL_ERR_STATE, "scene-specialised kernel unavailable: %s", ctx->jitNote[kind]);
-        if (jit) snprintf(ctx->kernelInfo, sizeof(ctx->kernelInfo), "%s", ctx->jitNote[kind]);
+            return setErr(ctx, SAIL_ERR_STATE, "scene-specialised kernel unavailable: %s", ctx->jitNote[kind][small]);
+        if (jit) snprintf(ctx->kernelInfo, sizeof(ctx->kernelInfo), "%s", ctx->jitNote[kind][small]);
         else {
-            const char* note = ctx->jitNote[kind];
+            const char* note = ctx->jitNote[kind][small];
             kind = kernelKind(ctx, F, false);  // the ahead-of-time variants have their own measured policy
             snprintf(ctx->kernelInfo, sizeof(ctx->kernelInfo), "aot %s<F=%d> (%s)", kind ? "wavefront" : "mega", F, note);
         }
@@ -846,8 +863,8 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
             if (jit) {
                 char why[200];
                 unsigned gx = grid.x;
-                if (kind == 1) gx = ((unsigned)ctx->W + m.jitBlock[1] / 8u - 1u) / (m.jitBlock[1] / 8u);  // tile = (threads / 8) x 8
-                if (sail_jit_launch(m.jitFn[kind], &L, gx, grid.y, m.jitBlock[kind], L.sceneSmem, m.stream, why, sizeof(why)) != 0)
+                if (kind == 1) gx = ((unsigned)ctx->W + m.jitBlock[1][small] / 8u - 1u) / (m.jitBlock[1][small] / 8u);  // tile = (threads / 8) x 8
+                if (sail_jit_launch(m.jitFn[kind][small], &L, gx, grid.y, m.jitBlock[kind][small], L.sceneSmem, m.stream, why, sizeof(why)) != 0)
                     return setErr(ctx, SAIL_ERR_CUDA, "%s", why);
             } else if (kind == 1) CU(launchWave(F, L, grid, m.stream));
             else CU(launchMega(F, L, grid, m.stream));
@@ -880,7 +897,9 @@ int sail_specialise_wait(sail_ctx* ctx) {
     if (ctx->cfg.specialise == SAIL_SPECIALISE_OFF) return 1;
     const int F = ctx->hostScene.features & SAIL_F_ALL;
     const int kind = kernelKind(ctx, F, true);
-    return specialisedReady(ctx, kind, F, true) ? 0 : 1;
+    // the variant the last frames asked for (a fresh context: the one a session starts with)
+    const int small = ctx->haveLastFrame ? (rngArgsSmall(ctx, &ctx->lastFrame, 1) ? 1 : 0) : 1;
+    return specialisedReady(ctx, kind, small, F, true) ? 0 : 1;
 }
 
 int sail_synchronize(sail_ctx* ctx) {

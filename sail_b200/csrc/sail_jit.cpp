@@ -149,7 +149,7 @@ struct Registry {
 Registry g_reg;
 
 // Fills the plan (cache key, generated source, launch shape) for `scene`; 0 or an error code with a message.
-int makePlan(int kind, int F, int minCtas, const SailSceneBlock* scene, Plan* plan, char* err, int errlen) {
+int makePlan(int kind, int F, int minCtas, int rngSmall, const SailSceneBlock* scene, Plan* plan, char* err, int errlen) {
     const int n = scene->n;
     if (n < 1) { setErr(err, errlen, "empty scene"); return 2; }
     if (kind != 0 && kind != 1) { setErr(err, errlen, "unknown kernel kind"); return 2; }
@@ -208,6 +208,7 @@ int makePlan(int kind, int F, int minCtas, const SailSceneBlock* scene, Plan* pl
     }
     char masks[200];
     snprintf(masks, sizeof(masks), " plugins=%x/%x/%x/%x/%x/%x/%x/%x", shapes, mats, texs, lights, glass, matte, tr, lightShapes);
+    if (!rngSmall) snprintf(masks + strlen(masks), sizeof(masks) - strlen(masks), " rng=full-range");
     if (const char* e = extraDefs.empty() ? nullptr : getenv("SAIL_B200_JIT_DEFINES")) snprintf(masks + strlen(masks), sizeof(masks) - strlen(masks), " -D%.60s", e);
     unsigned block = SAIL_JIT_CTA_THREADS;
     if (kind == 1) {  // wavefront: paths per CTA (sail_wavefront.cuh SAIL_WF_THREADS), 64 registers per thread fill the SM
@@ -235,6 +236,7 @@ int makePlan(int kind, int F, int minCtas, const SailSceneBlock* scene, Plan* pl
     // small scenes without quadrics: the nearest-hit scan inlined at both call sites (path ray, shadow ray) instead of one shared
     // out-of-line copy -- config 5 +2.8 %, config 2 +-0; with quadrics the scan is too large (config 3 -23 %)
     if (!(F & 1 /* SAIL_F_QUADRICS */) && n <= 8) tuning += "#define SAIL_INLINE_SCAN 1\n";
+    if (rngSmall) tuning += "#define SAIL_RNG_SMALL_ARGS 1\n";
     char src[4096];
     snprintf(src, sizeof(src),
              "%s#define SAIL_JIT_NRUNS %d\n#define SAIL_JIT_RUN_CATS %s\n#define SAIL_JIT_RUN_STARTS %s\n#define SAIL_JIT_RUN_LENS %s\n"
@@ -306,11 +308,11 @@ void compileJob(SailJitJob* job) {
 
 }  // namespace
 
-SailJitJob* sail_jit_request(int kind, int F, int minCtas, const SailSceneBlock* scene, char* err, int errlen) {
+SailJitJob* sail_jit_request(int kind, int F, int minCtas, int rngSmall, const SailSceneBlock* scene, char* err, int errlen) {
     std::lock_guard<std::mutex> lock(g_mutex);
     if (!loadApi()) { setErr(err, errlen, g_api.why); return nullptr; }
     Plan plan;
-    if (makePlan(kind, F, minCtas, scene, &plan, err, errlen) != 0) return nullptr;
+    if (makePlan(kind, F, minCtas, rngSmall, scene, &plan, err, errlen) != 0) return nullptr;
     auto it = g_reg.jobs.find(plan.key);
     if (it != g_reg.jobs.end()) return it->second;
     SailJitJob* job = new SailJitJob;

@@ -44,8 +44,12 @@ SD V2 sinPair(float a, float b) {
     float va = (qa & 1) ? ca : sa, vb = (qb & 1) ? cb : sb;
     va = (qa & 2) ? -va : va;
     vb = (qb & 2) ? -vb : vb;
-    if (!(dm_abs(a) < 4194304.0f)) va = dm_sin_large(a);  // Payne-Hanek (detmath.h): hours into a session, rare and warp-uniform in practice
+#ifndef SAIL_RNG_SMALL_ARGS
+    // Payne-Hanek (detmath.h): hours into a session.  A scene-specialised kernel is built without this arm while the host can
+    // prove |argument| < 2^22 for every pixel, bounce and frame of the launch (sail_api.cu rngArgsSmall), and rebuilt with it after.
+    if (!(dm_abs(a) < 4194304.0f)) va = dm_sin_large(a);
     if (!(dm_abs(b) < 4194304.0f)) vb = dm_sin_large(b);
+#endif
     return mk2(va, vb);
 }
 static __device__ __noinline__ float2 sail_sin2(float a, float b) { V2 v = sinPair(a, b); return make_float2(v.x, v.y); }
