@@ -28,8 +28,10 @@ def _opt(arr):
 class Oracle:
     """One loaded copy of the oracle library (``count_ops=True`` loads the op-counting build)."""
 
-    def __init__(self, count_ops=False):
-        name = "liboracle_ops.so" if count_ops else "liboracle.so"
+    def __init__(self, count_ops=False, ieee_div=False):
+        """``ieee_div=True`` loads the build whose '/' is IEEE division and whose normalize() divides by the length
+        (oracle/glsl.h SAIL_ORACLE_IEEE_DIV) -- for measuring the distance between the two arithmetic models only."""
+        name = "liboracle_ieee.so" if ieee_div else ("liboracle_ops.so" if count_ops else "liboracle.so")
         path = os.path.join(_HERE, name)
         if not os.path.exists(path):
             build()

@@ -41,7 +41,14 @@ struct real {
 static inline real operator+(real a, real b) { SAIL_OP(1); return real(a.v + b.v); }
 static inline real operator-(real a, real b) { SAIL_OP(1); return real(a.v - b.v); }
 static inline real operator*(real a, real b) { SAIL_OP(1); return real(a.v * b.v); }
+#ifdef SAIL_ORACLE_IEEE_DIV
+// The other defensible reading of GLSL's '/' (SURVEY.md 8(c) first wrote "correctly rounded"): IEEE-754 division, and
+// normalize(v) = v / length(v).  Built as liboracle_ieee.so ONLY to measure how far the two arithmetic models are apart
+// (tests/test_cpu_model_sensitivity.py); parity tests use the a * rcp(b) model above.
+static inline real operator/(real a, real b) { SAIL_OP(1); return real(a.v / b.v); }
+#else
 static inline real operator/(real a, real b) { SAIL_OP(1); return real(dm_div(a.v, b.v)); }
+#endif
 static inline real operator-(real a) { return real(-a.v); }
 static inline real& operator+=(real& a, real b) { a = a + b; return a; }
 static inline real& operator-=(real& a, real b) { a = a - b; return a; }
@@ -136,7 +143,11 @@ static inline vec3 cross(vec3 x, vec3 y) {
     return vec3(x.y * y.z - y.y * x.z, x.z * y.x - y.z * x.x, x.x * y.y - y.x * x.y);
 }
 static inline real length(vec3 a) { return sqrt(dot(a, a)); }
+#ifdef SAIL_ORACLE_IEEE_DIV
+static inline vec3 normalize(vec3 a) { return a / sqrt(dot(a, a)); }
+#else
 static inline vec3 normalize(vec3 a) { return a * (real(1.0f) / sqrt(dot(a, a))); }
+#endif
 static inline vec3 reflect(vec3 I, vec3 N) { return I - (real(2.0f) * dot(N, I)) * N; }
 static inline vec3 refract(vec3 I, vec3 N, real eta) {
     real d = dot(N, I);

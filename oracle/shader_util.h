@@ -82,8 +82,13 @@ static thread_local vec3 gl_FragCoord;
 
 // Row coordinate helpers: `float(i)/float(n-1)` (shader.shape.js:34,44,56; shader.light.js:20) and
 // `value/float(tn-1)` (cube.glsl:19-20 ...).  Pure table addressing: not counted as arithmetic.
+#ifdef SAIL_ORACLE_IEEE_DIV
+static inline real rowCoord(int i, int count) { return real((float)i / (float)(count - 1)); }
+static inline real rowCoordF(real v, int count) { return real(v.v / (float)(count - 1)); }
+#else
 static inline real rowCoord(int i, int count) { return real(dm_div((float)i, (float)(count - 1))); }
 static inline real rowCoordF(real v, int count) { return real(dm_div(v.v, (float)(count - 1))); }
+#endif
 
 // ---- util/texhelper.glsl:1-36 ----------------------------------------------------------------
 static inline vec2 convert(vec2 pos, float width) {

@@ -442,6 +442,11 @@ SD V3 sampleGeometry(const SceneView& sc, V2 u, int i, V3& normal, float& pdf) {
 }
 
 // ---- light_sample(), shader.light.js:12-22 + area/point/spot.glsl -----------------------------------
+// Three steps instead of the shader's one arm per light kind: (1) the point on the light (per kind, cheap), (2) ONE shadow
+// ray for all lanes of the warp whatever kind of light each lane drew, (3) the radiance formula of the kind.  The shader
+// calls testShadow() inside each arm (area.glsl:20, point.glsl:17, spot.glsl:27); with several kinds of light in a scene that
+// would run the nearest-hit scan -- the most expensive function of the path -- once per kind with a third of the lanes each.
+// Every value is computed by the same operations on the same operands; only the order of independent steps differs.
 template <int F>
 SD V3 light_sample(const SceneView& sc, V2 u, V3 hit, V3 insNormal) {
     const int ln = sc.ln;
@@ -449,25 +454,29 @@ SD V3 light_sample(const SceneView& sc, V2 u, V3 hit, V3 insNormal) {
     int index = toInt(u.x * (float)ln);  // randomInt(seed, 0, ln): same hash value as u.x
     if (index > ln) index = ln;
     const SailLight& l = sc.light[index];
-    switch (l.category) {
-        case SAIL_AREA: if (SAIL_HAS_LIGHT(SAIL_AREA)) {  // area.glsl:13-23
-            V3 normal;
-            float pdf;
-            V3 p = sampleGeometry<F>(sc, u, l.object, normal, pdf);
-            V3 toLight = p - hit;
+    const int cat = l.category;
+    V3 toLight = splat3(0.0f), normal = splat3(0.0f);
+    float pdf = 0.0f;
+    if (cat == SAIL_AREA && SAIL_HAS_LIGHT(SAIL_AREA)) {  // area.glsl:16-17
+        V3 p = sampleGeometry<F>(sc, u, l.object, normal, pdf);
+        toLight = p - hit;
+    } else if (cat == SAIL_POINT && SAIL_HAS_LIGHT(SAIL_POINT)) {  // point.glsl:14-15
+        V3 p = ld3(l.from) + uniformSampleSphere(u) * 0.1f;
+        toLight = p - hit;
+    } else if (cat == SAIL_SPOT && SAIL_HAS_LIGHT(SAIL_SPOT)) {  // spot.glsl:25
+        toLight = ld3(l.from) - hit;
+    } else {
+        return splat3(0.0f);  // no arm for this category
+    }
+    if (testShadow<F>(sc, hit, toLight)) return splat3(0.0f);
+    switch (cat) {
+        case SAIL_AREA: if (SAIL_HAS_LIGHT(SAIL_AREA)) {  // area.glsl:18-22
             V3 normToLight = normalize3(toLight);
-            if (testShadow<F>(sc, hit, toLight)) return splat3(0.0f);
             return vdivs(ld3(l.emission) * fmax2(0.0f, dot3(normal, -normToLight)) * fmax2(0.0f, dot3(normToLight, insNormal)), pdf);
         }
-        case SAIL_POINT: if (SAIL_HAS_LIGHT(SAIL_POINT)) {  // point.glsl:13-20
-            V3 p = ld3(l.from) + uniformSampleSphere(u) * 0.1f;
-            V3 toLight = p - hit;
-            if (testShadow<F>(sc, hit, toLight)) return splat3(0.0f);
+        case SAIL_POINT: if (SAIL_HAS_LIGHT(SAIL_POINT))  // point.glsl:18-19
             return ld3(l.emission) * fmax2(0.0f, dot3(normalize3(toLight), insNormal));
-        }
         case SAIL_SPOT: if (SAIL_HAS_LIGHT(SAIL_SPOT)) {  // spot.glsl:17-39 (axis fixed to -y)
-            V3 toLight = ld3(l.from) - hit;
-            if (testShadow<F>(sc, hit, toLight)) return splat3(0.0f);
             V3 normToLight = normalize3(toLight);
             float d = length3(toLight);
             V3 w = -normToLight;

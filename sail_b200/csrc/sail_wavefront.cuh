@@ -86,7 +86,15 @@ SD void sailWaveBody(const SailLaunch& L) {
                 // ---- stage 2: counting sort by hit object ----
                 const int key = alive ? nr.id : n;
                 int* hcur = hist[hsel];
-                const int rank = atomicAdd(&hcur[key], 1);
+                // one shared-memory atomic per (warp, object) instead of one per lane: lanes that hit the same object find each
+                // other with match.any, the first of them reserves the whole group's ranks (same-address atomics of a warp are
+                // serialised by the hardware -- 4.3e8 bank conflicts per launch in the round-1 capture)
+                const unsigned peers = __match_any_sync(0xffffffffu, key);
+                const int leader = __ffs(peers) - 1;
+                int base = 0;
+                if (lane == leader) base = atomicAdd(&hcur[key], __popc(peers));
+                base = __shfl_sync(0xffffffffu, base, leader);
+                const int rank = base + __popc(peers & ((1u << lane) - 1u));
                 __syncthreads();
                 int pos = rank;
                 for (int j = 0; j < key; j++) pos += hcur[j];
