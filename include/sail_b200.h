@@ -240,6 +240,16 @@ void* sail_stream(sail_ctx* ctx);
  * normal count x 3 (flipped toward the ray), mat_category. */
 int sail_intersect_rays(sail_ctx* ctx, const float* rays, int32_t count, int32_t* hit_id, float* t, float* normal,
                         int32_t* mat_category);
+/* sail_intersect_rays() for callers that must not allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same
+ * arguments, same results; the device copies of the rays and outputs live in a fixed array inside the library instead of
+ * per-call cudaMalloc / cudaFree, so count <= SAIL_NOALLOC_MAX_RAYS (more: SAIL_ERR_INVALID, nothing is launched).  The call
+ * makes no cudaMalloc / cudaFree and calls no allocating library routine.  The array (3 MiB per GPU that loads the library,
+ * held until exit) is shared by every call on a device and keeps the last call's contents: calls that overlap on the GPU --
+ * two contexts on one device driven from two threads -- race on it; calls on one context are ordered by its stream. */
+#define SAIL_NOALLOC_MAX_RAYS 65536
+int sail_intersect_rays_noalloc(sail_ctx* ctx, const float* rays, int32_t count, int32_t* hit_id, float* t, float* normal,
+                                int32_t* mat_category);
 /* One frame with per-bounce records (no accumulation): hit_id/t are W*H*max_bounces (unreached = -2),
  * rays W*H*max_bounces*6, radiance W*H*3 (the raw sample e).  Each may be NULL. */
 int sail_trace_dump(sail_ctx* ctx, const sail_frame* frame, int32_t* hit_id, float* t, float* rays, float* radiance);

@@ -24,6 +24,7 @@ COMBINE_AUTO, COMBINE_NCCL, COMBINE_P2P = 0, 1, 2
 MAX_DEVICES = 8
 GROUP_ID_BYTES = 128
 ABI_VERSION = 2
+NOALLOC_MAX_RAYS = 65536
 
 
 class SailError(RuntimeError):
@@ -86,6 +87,7 @@ _SIGNATURES = {
     "sail_device_ptr": (_P, [_P, ctypes.c_int32]),
     "sail_stream": (_P, [_P]),
     "sail_intersect_rays": (ctypes.c_int, [_P, _P, ctypes.c_int32, _P, _P, _P, _P]),
+    "sail_intersect_rays_noalloc": (ctypes.c_int, [_P, _P, ctypes.c_int32, _P, _P, _P, _P]),
     "sail_trace_dump": (ctypes.c_int, [_P, ctypes.POINTER(Frame), _P, _P, _P, _P]),
     "sail_eval_math": (ctypes.c_int, [_P, ctypes.c_int32, _P, _P, _P, ctypes.c_int32]),
     "sail_selftest_math": (ctypes.c_int, [_P, ctypes.POINTER(ctypes.c_uint64)]),
@@ -374,6 +376,15 @@ class Context:
         ids, t = np.empty(n, np.int32), np.empty(n, np.float32)
         normal, mat = np.empty((n, 3), np.float32), np.empty(n, np.int32)
         self._check(self.lib.sail_intersect_rays(self._h, _ptr(r), n, _ptr(ids), _ptr(t), _ptr(normal), _ptr(mat)))
+        return ids, t, normal, mat
+
+    def intersect_rays_noalloc(self, rays):
+        """``intersect_rays`` through sail_intersect_rays_noalloc: fixed in-library scratch, at most NOALLOC_MAX_RAYS rays."""
+        r = _f32(rays).reshape(-1, 6)
+        n = r.shape[0]
+        ids, t = np.empty(n, np.int32), np.empty(n, np.float32)
+        normal, mat = np.empty((n, 3), np.float32), np.empty(n, np.int32)
+        self._check(self.lib.sail_intersect_rays_noalloc(self._h, _ptr(r), n, _ptr(ids), _ptr(t), _ptr(normal), _ptr(mat)))
         return ids, t, normal, mat
 
     def trace_dump(self, frame):

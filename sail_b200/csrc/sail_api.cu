@@ -17,6 +17,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -1081,6 +1082,63 @@ int sail_intersect_rays(sail_ctx* ctx, const float* rays, int32_t count, int32_t
     if (mat_category) CU(cudaMemcpyAsync(mat_category, dM, c * sizeof(int), cudaMemcpyDeviceToHost, m.stream));
     CU(cudaStreamSynchronize(m.stream));
     cudaFree(dR); cudaFree(dT); cudaFree(dN); cudaFree(dI); cudaFree(dM);
+    return SAIL_OK;
+}
+
+// ---- sail_intersect_rays_noalloc -------------------------------------------------------------------------------------
+// The scratch of sail_intersect_rays() (device copies of the rays and of the four outputs, cudaMalloc'ed and freed per call)
+// as ONE file-scope device array, for callers that must not allocate: 12 words per ray.  Every GPU that loads the library
+// holds these SAIL_NOALLOC_MAX_RAYS * 48 bytes (3 MiB) until the process exits.  All calls on a device share the array and it
+// keeps the last call's contents; nothing in it has to start at zero (the kernel writes every output element below `count`
+// before the copies read it), but two calls that overlap on the GPU (different contexts / streams) race on it.
+static __device__ __align__(256) float sail_noalloc_scratch[(size_t)SAIL_NOALLOC_MAX_RAYS * 12];
+
+namespace {
+// In host code `sail_noalloc_scratch` is only a handle for the runtime, not a device address: the address is asked for
+// once per device, with that device current.
+float* noallocScratch(int device, cudaError_t* e) {
+    static float* ptr[64] = {nullptr};
+    static std::mutex m;
+    std::lock_guard<std::mutex> lock(m);
+    *e = cudaSuccess;
+    if (device < 0 || device >= 64) { *e = cudaErrorInvalidDevice; return nullptr; }
+    if (!ptr[device]) {
+        void* p = nullptr;
+        *e = cudaGetSymbolAddress(&p, sail_noalloc_scratch);  // the caller has made `device` current
+        if (*e != cudaSuccess) return nullptr;
+        ptr[device] = static_cast<float*>(p);
+    }
+    return ptr[device];
+}
+}  // namespace
+
+int sail_intersect_rays_noalloc(sail_ctx* ctx, const float* rays, int32_t count, int32_t* hit_id, float* t, float* normal, int32_t* mat_category) {
+    if (!ctx || !rays || count < 0) return SAIL_ERR_INVALID;
+    if (!ctx->sceneLoaded) return setErr(ctx, SAIL_ERR_STATE, "sail_intersect_rays_noalloc before sail_upload_scene");
+    if (count > SAIL_NOALLOC_MAX_RAYS)
+        return setErr(ctx, SAIL_ERR_INVALID, "sail_intersect_rays_noalloc: %d rays exceed the fixed scratch of SAIL_NOALLOC_MAX_RAYS = %d; split the batch or use sail_intersect_rays",
+                      count, SAIL_NOALLOC_MAX_RAYS);
+    if (count == 0) return SAIL_OK;
+    SailMember& m = ctx->root();
+    CU(cudaSetDevice(m.device));
+    cudaError_t se;
+    float* base = noallocScratch(m.device, &se);
+    if (!base) return setErr(ctx, SAIL_ERR_CUDA, "cudaGetSymbolAddress(sail_noalloc_scratch) failed: %s", cudaGetErrorString(se));
+    const size_t c = (size_t)count, cap = (size_t)SAIL_NOALLOC_MAX_RAYS;
+    float* dR = base;                                         // cap x 6
+    float* dT = base + cap * 6;                               // cap
+    float* dN = base + cap * 7;                               // cap x 3
+    int* dI = reinterpret_cast<int*>(base + cap * 10);        // cap
+    int* dM = reinterpret_cast<int*>(base + cap * 11);        // cap
+    CU(cudaMemcpyAsync(dR, rays, c * 6 * sizeof(float), cudaMemcpyHostToDevice, m.stream));
+    sail_intersect_kernel<<<(unsigned)((c + SAIL_CTA_THREADS - 1) / SAIL_CTA_THREADS), SAIL_CTA_THREADS, sailSceneSmemBytes(ctx->hostScene.n, ctx->hostScene.ln), m.stream>>>(m.dScene, dR, count, dI, dT, dN, dM);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    if (hit_id) CU(cudaMemcpyAsync(hit_id, dI, c * sizeof(int), cudaMemcpyDeviceToHost, m.stream));
+    if (t) CU(cudaMemcpyAsync(t, dT, c * sizeof(float), cudaMemcpyDeviceToHost, m.stream));
+    if (normal) CU(cudaMemcpyAsync(normal, dN, c * 3 * sizeof(float), cudaMemcpyDeviceToHost, m.stream));
+    if (mat_category) CU(cudaMemcpyAsync(mat_category, dM, c * sizeof(int), cudaMemcpyDeviceToHost, m.stream));
+    CU(cudaStreamSynchronize(m.stream));
     return SAIL_OK;
 }
 
