@@ -446,7 +446,7 @@ def run_ours(args, rank, world, local_rank):
             "data": "synthetic",
             "config": {"workload": WORKLOADS[_workload][1], "spp_per_step": SPP_PER_STEP, "paths_per_step": paths_per_step,
                        "kernel": args.kernel, "kernel_used": kernel_used, "arithmetic": "strict (bit-exact vs oracle)",
-                       "sharding": ("interleaved %d-row bands mod N (tile)" % (args.band_rows or 16)) if tile else "sample index mod N",
+                       "sharding": ("interleaved %d-row bands mod N (tile)" % (args.band_rows or 8)) if tile else "sample index mod N",
                        "group": group_info,
                        "l2": "flushed between steps (256 MiB memset outside the per-step events)"},
             "spp_per_s": value * 1e6 / (W * H),
@@ -512,7 +512,7 @@ def main():
     ap.add_argument("--no-jit", action="store_true", help="ahead-of-time kernel variants only (no per-scene NVRTC build)")
     ap.add_argument("--workload", default="cornell", choices=sorted(WORKLOADS), help="cornell = the headline; others are extra")
     ap.add_argument("--sharding", default="sample", choices=["sample", "tile"], help="N > 1: sample index mod N (config 4) or row bands (config 5)")
-    ap.add_argument("--band-rows", type=int, default=0, help="tile sharding: rows per interleaved band (multiple of 8; 0 = 16)")
+    ap.add_argument("--band-rows", type=int, default=0, help="tile sharding: rows per interleaved band (multiple of 8; 0 = 8)")
     ap.add_argument("--filters", default="box,sinc,gaussian", help="tile sharding: display filters applied to the gathered image each step")
     args = ap.parse_args()
     global _workload

@@ -130,7 +130,7 @@ def rank_main(args):
 
     def make(shard):
         token = gid[:128] if shard == capi.SHARD_SAMPLE else gid[128:]
-        return Renderer((args.width, args.height), device=rank, group=(n, rank, token), shard=shard)
+        return Renderer((args.width, args.height), device=rank, group=(n, rank, token), shard=shard, band_rows=16)
 
     run_group(args, make, n, res, "", is_root=(rank == 0))
     if rank == 0:
@@ -173,7 +173,7 @@ def main():
     ok = True
     for combine, tag in ((capi.COMBINE_P2P, "p2p_"), (capi.COMBINE_NCCL, "nccl_")):
         def make(shard, combine=combine):
-            return Renderer((args.width, args.height), devices=list(range(n)), shard=shard, combine=combine)
+            return Renderer((args.width, args.height), devices=list(range(n)), shard=shard, combine=combine, band_rows=16)
         try:
             run_group(args, make, n, res, tag)
             ok = ok and res[tag + "sample_ok"] and res[tag + "tile_ok"]
