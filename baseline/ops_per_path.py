@@ -1,6 +1,7 @@
 """Counts OPS_alg: FP32 arithmetic operations the literal oracle executes per path,
 averaged over the frame and over frames k = 0..F-1, with the op-counting oracle build
 (oracle/liboracle_ops.so, -DSAIL_COUNT_OPS).  Writes baseline/ops_per_path.json.
+Every config over frames k = 0..15, as SURVEY.md 8(d) defines it.
 Usage: python baseline/ops_per_path.py [frames]"""
 import json
 import os
@@ -35,10 +36,10 @@ if __name__ == "__main__":
                          "and each transcendental = 1; addressing, conversions and loads = 0 (SURVEY.md 8(d))",
            "cornell_1080p": count(configs.cornell_1080p, frames),
            "config1_512": count(configs.config1, frames),
-           "config2_1080p": count(configs.config2, max(1, frames // 4)),
-           "config3_1080p": count(configs.config3, max(1, frames // 4)),
-           "config5_1080p": count(configs.config5, max(1, frames // 8)),
-           "config4_2160p": count(configs.config4, max(1, frames // 8))}
+           "config2_1080p": count(configs.config2, frames),
+           "config3_1080p": count(configs.config3, frames),
+           "config5_1080p": count(configs.config5, frames),
+           "config4_2160p": count(configs.config4, frames)}
     with open(os.path.join(ROOT, "baseline", "ops_per_path.json"), "w") as f:
         json.dump(out, f, indent=1)
     print(json.dumps(out, indent=1))

@@ -1,9 +1,12 @@
 // Renderer on libsail_b200.so: the reference's src/core/renderer.js:8-73 with the canvas replaced by a size and
 // the display pass returning pixels (Uint8ClampedArray, W*H*4, bottom row first) instead of drawing them.
-import native from '../../napi/build/Release/sail_napi.node';
+import native from './native';
 import {Tracer} from './tracer';
 
 class Renderer {
+    // device: a CUDA ordinal, or {devices: [0, 1, ...], shard: 1 (sample index mod N) | 2 (row bands), bandRows, combine} for one
+    // renderer over several GPUs (include/sail_b200.h sail_create_info.ndev; the split, the collective and the combined image
+    // live behind the C ABI)
     constructor(canvas, device = 0) {
         this.ctx = native.create(canvas.width, canvas.height, device);
         this.tracer = new Tracer(this.ctx);

@@ -1,6 +1,6 @@
 // Tracer on libsail_b200.so: same fields and methods as the reference's src/core/tracer.js:8-101, the WebGL
 // texture/uniform plumbing replaced by calls into the N-API addon (napi/sail_napi.cc).
-import native from '../../napi/build/Release/sail_napi.node';
+import native from './native';
 import {Matrix, Vector} from '../utils/matrix';
 import {lowerConfig} from './config';
 

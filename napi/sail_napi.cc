@@ -41,14 +41,32 @@ static void floatArrayProp(napi_env env, napi_value obj, const char* name, float
     for (uint32_t i = 0; i < n; i++) { double d = 0; napi_get_element(env, arr, i, &e); napi_get_value_double(env, e, &d); out[i] = (float)d; }
 }
 
-// create(width, height, device) -> {handle, width, height}        [new Sail.Renderer(canvas)]
+// create(width, height, device | {devices: [0, 1, ...], shard: 1 | 2, bandRows, combine}) -> {handle, width, height}
+// [new Sail.Renderer(canvas)].  With a device list the context is sharded over those GPUs behind the C ABI
+// (sail_create_info.ndev / device_ids / shard_mode): sample index mod N (shard 1) or interleaved row bands (shard 2).
 static napi_value Create(napi_env env, napi_callback_info info) {
     size_t argc = 3; napi_value a[3];
     NAPI_OK(napi_get_cb_info(env, info, &argc, a, nullptr, nullptr));
     sail_create_info ci; memset(&ci, 0, sizeof(ci));
     napi_get_value_int32(env, a[0], &ci.width);
     napi_get_value_int32(env, a[1], &ci.height);
-    if (argc > 2) napi_get_value_int32(env, a[2], &ci.device);
+    if (argc > 2) {
+        napi_valuetype vt;
+        napi_typeof(env, a[2], &vt);
+        if (vt == napi_object) {
+            napi_value devs; uint32_t n = 0;
+            napi_get_named_property(env, a[2], "devices", &devs);
+            napi_get_array_length(env, devs, &n);
+            if (n > SAIL_MAX_DEVICES) { napi_throw_range_error(env, nullptr, "too many devices"); return nullptr; }
+            ci.ndev = (int32_t)n;
+            for (uint32_t i = 0; i < n; i++) { napi_value e; napi_get_element(env, devs, i, &e); napi_get_value_int32(env, e, &ci.device_ids[i]); }
+            ci.shard_mode = (int32_t)numberProp(env, a[2], "shard");
+            ci.band_rows = (int32_t)numberProp(env, a[2], "bandRows");
+            ci.combine = (int32_t)numberProp(env, a[2], "combine");
+        } else {
+            napi_get_value_int32(env, a[2], &ci.device);
+        }
+    }
     sail_ctx* ctx = nullptr;
     int rc = sail_create(&ci, &ctx);
     if (rc != SAIL_OK) { napi_throw_error(env, nullptr, ctx ? sail_last_error(ctx) : "sail_create failed"); sail_destroy(ctx); return nullptr; }
@@ -167,6 +185,85 @@ static napi_value ReadAov(napi_env env, napi_callback_info info) {
     return nullptr;
 }
 
+// renderN(handle, Float32Array frames /* count x 21: matrix16, eye3, textureWeight, timeSinceStart */)   [k x Tracer.render]
+static napi_value RenderN(napi_env env, napi_callback_info info) {
+    size_t argc = 2; napi_value a[2];
+    NAPI_OK(napi_get_cb_info(env, info, &argc, a, nullptr, nullptr));
+    sail_ctx* ctx = handle(env, a[0]);
+    size_t n = 0;
+    float* f = f32(env, a[1], &n);
+    static_assert(sizeof(sail_frame) == 21 * sizeof(float), "sail_frame is 21 consecutive floats");
+    if (!f || n == 0 || n % 21) { napi_throw_range_error(env, nullptr, "frames must hold 21 floats per frame"); return nullptr; }
+    check(env, ctx, sail_render_n(ctx, (const sail_frame*)f, (int32_t)(n / 21)));
+    return nullptr;
+}
+// reset(handle)        [a fresh frameCache]
+static napi_value Reset(napi_env env, napi_callback_info info) {
+    size_t argc = 1; napi_value a[1];
+    NAPI_OK(napi_get_cb_info(env, info, &argc, a, nullptr, nullptr));
+    check(env, handle(env, a[0]), sail_reset(handle(env, a[0])));
+    return nullptr;
+}
+// specialiseWait(handle) -> true when the scene-specialised kernel is in place (false: ahead-of-time variant keeps running)
+static napi_value SpecialiseWait(napi_env env, napi_callback_info info) {
+    size_t argc = 1; napi_value a[1];
+    NAPI_OK(napi_get_cb_info(env, info, &argc, a, nullptr, nullptr));
+    sail_ctx* ctx = handle(env, a[0]);
+    int rc = sail_specialise_wait(ctx);
+    if (rc < 0) { check(env, ctx, rc); return nullptr; }
+    napi_value out;
+    napi_get_boolean(env, rc == 0, &out);
+    return out;
+}
+// kernelInfo(handle) -> string
+static napi_value KernelInfo(napi_env env, napi_callback_info info) {
+    size_t argc = 1; napi_value a[1];
+    NAPI_OK(napi_get_cb_info(env, info, &argc, a, nullptr, nullptr));
+    char buf[400];
+    int n = sail_kernel_info(handle(env, a[0]), buf, sizeof(buf));
+    napi_value out;
+    napi_create_string_utf8(env, n < 0 ? "" : buf, NAPI_AUTO_LENGTH, &out);
+    return out;
+}
+// intersectRays(handle, Float32Array rays /* count x 6 */, Int32Array hitId, Float32Array t)        [Pickup.pick, pickup.js:46-63]
+static napi_value IntersectRays(napi_env env, napi_callback_info info) {
+    size_t argc = 4; napi_value a[4];
+    NAPI_OK(napi_get_cb_info(env, info, &argc, a, nullptr, nullptr));
+    sail_ctx* ctx = handle(env, a[0]);
+    size_t nr = 0, nt = 0;
+    float* rays = f32(env, a[1], &nr);
+    napi_typedarray_type type; napi_value buf; size_t off, ni = 0; void* ids = nullptr;
+    NAPI_OK(napi_get_typedarray_info(env, a[2], &type, &ni, &ids, &buf, &off));
+    float* t = f32(env, a[3], &nt);
+    if (!rays || nr % 6 || type != napi_int32_array || ni != nr / 6 || nt != nr / 6) { napi_throw_range_error(env, nullptr, "rays: 6 floats each; hitId (Int32Array), t: one element per ray"); return nullptr; }
+    check(env, ctx, sail_intersect_rays(ctx, rays, (int32_t)(nr / 6), (int32_t*)ids, t, nullptr, nullptr));
+    return nullptr;
+}
+// groupId() -> Uint8Array(128); groupJoin(handle, nranks, rank, id, shard, bandRows): one GPU per process (a cluster of Node
+// workers), images arrive on rank 0 (include/sail_b200.h sail_group_join)
+static napi_value GroupId(napi_env env, napi_callback_info info) {
+    void* data = nullptr; napi_value buf, out;
+    NAPI_OK(napi_create_arraybuffer(env, SAIL_GROUP_ID_BYTES, &data, &buf));
+    if (sail_group_id((uint8_t*)data) != SAIL_OK) { napi_throw_error(env, nullptr, "sail_group_id failed (NCCL not available?)"); return nullptr; }
+    NAPI_OK(napi_create_typedarray(env, napi_uint8_array, SAIL_GROUP_ID_BYTES, buf, 0, &out));
+    return out;
+}
+static napi_value GroupJoin(napi_env env, napi_callback_info info) {
+    size_t argc = 6; napi_value a[6];
+    NAPI_OK(napi_get_cb_info(env, info, &argc, a, nullptr, nullptr));
+    sail_ctx* ctx = handle(env, a[0]);
+    int32_t nranks = 0, rank = 0, shard = 0, band = 0;
+    napi_get_value_int32(env, a[1], &nranks);
+    napi_get_value_int32(env, a[2], &rank);
+    napi_typedarray_type type; napi_value buf; size_t off, len = 0; void* id = nullptr;
+    NAPI_OK(napi_get_typedarray_info(env, a[3], &type, &len, &id, &buf, &off));
+    napi_get_value_int32(env, a[4], &shard);
+    if (argc > 5) napi_get_value_int32(env, a[5], &band);
+    if (type != napi_uint8_array || len != SAIL_GROUP_ID_BYTES) { napi_throw_range_error(env, nullptr, "group id: the Uint8Array(128) of groupId()"); return nullptr; }
+    check(env, ctx, sail_group_join(ctx, nranks, rank, (const uint8_t*)id, shard, band, SAIL_COMBINE_AUTO));
+    return nullptr;
+}
+
 static napi_value Init(napi_env env, napi_value exports) {
     napi_property_descriptor d[] = {
         {"create", nullptr, Create, nullptr, nullptr, nullptr, napi_default, nullptr},
@@ -175,10 +272,17 @@ static napi_value Init(napi_env env, napi_value exports) {
         {"uploadScene", nullptr, UploadScene, nullptr, nullptr, nullptr, napi_default, nullptr},
         {"uploadObjects", nullptr, UploadObjects, nullptr, nullptr, nullptr, napi_default, nullptr},
         {"render", nullptr, Render, nullptr, nullptr, nullptr, napi_default, nullptr},
+        {"renderN", nullptr, RenderN, nullptr, nullptr, nullptr, napi_default, nullptr},
+        {"reset", nullptr, Reset, nullptr, nullptr, nullptr, napi_default, nullptr},
         {"present", nullptr, Present, nullptr, nullptr, nullptr, napi_default, nullptr},
         {"presentBegin", nullptr, PresentBegin, nullptr, nullptr, nullptr, napi_default, nullptr},
         {"presentEnd", nullptr, PresentEnd, nullptr, nullptr, nullptr, napi_default, nullptr},
         {"readAov", nullptr, ReadAov, nullptr, nullptr, nullptr, napi_default, nullptr},
+        {"specialiseWait", nullptr, SpecialiseWait, nullptr, nullptr, nullptr, napi_default, nullptr},
+        {"kernelInfo", nullptr, KernelInfo, nullptr, nullptr, nullptr, napi_default, nullptr},
+        {"intersectRays", nullptr, IntersectRays, nullptr, nullptr, nullptr, napi_default, nullptr},
+        {"groupId", nullptr, GroupId, nullptr, nullptr, nullptr, napi_default, nullptr},
+        {"groupJoin", nullptr, GroupJoin, nullptr, nullptr, nullptr, napi_default, nullptr},
     };
     napi_define_properties(env, exports, sizeof(d) / sizeof(d[0]), d);
     return exports;

@@ -108,6 +108,47 @@ def test_napi_addon_source_compiles_against_the_header():
     assert r.returncode == 0, r.stderr
 
 
+def test_js_host_is_complete_on_paper():
+    """The JS host cannot run here (no Node.js).  What can be checked: every `native.<name>` the files under js/ use is a
+    function napi/sail_napi.cc registers; the addon is loaded from exactly one place (js/native.js); every relative import
+    resolves to a file under js/ or -- for `../x/y` -- to a module of the reference tree the host is dropped into
+    (js/ -> <sail>/src/native/); js/index.js exports the thirty names of the reference's namespace
+    (/root/reference/index.js:15-45) without `window`."""
+    js_dir = os.path.join(ROOT, "js")
+    napi = open(os.path.join(ROOT, "napi", "sail_napi.cc")).read()
+    registered = set(re.findall(r'\{"(\w+)", nullptr, \w+, nullptr', napi))
+    assert len(registered) >= 15
+    used, loaders = set(), []
+    ref_modules = {"../scene/scene", "../scene/geometry", "../scene/light", "../scene/camera", "../scene/material", "../scene/texture",
+                   "../utils/matrix", "../core/color", "../core/pickup", "../shader/filter/box", "../shader/filter/gaussian",
+                   "../shader/filter/mitchell", "../shader/filter/sinc", "../shader/filter/triangle"}
+    for f in sorted(os.listdir(js_dir)):
+        txt = open(os.path.join(js_dir, f)).read()
+        used |= set(re.findall(r"\bnative\.(\w+)\(", txt))
+        if "sail_napi.node" in txt:
+            loaders.append(f)
+        assert not re.search(r"\bwindow\b", re.sub(r"//.*", "", txt)), f
+        for mod in re.findall(r"from '([^']+)'", re.sub(r"//.*", "", txt)):
+            if mod.startswith("./"):
+                assert os.path.exists(os.path.join(js_dir, mod[2:] + ".js")), "%s imports %s" % (f, mod)
+            elif mod.startswith("../"):
+                assert mod in ref_modules, "%s imports %s, not a module of the reference tree" % (f, mod)
+            else:
+                assert mod == "module", (f, mod)
+    assert loaders == ["native.js"], loaders
+    assert used and used <= registered, "used but not registered in napi/sail_napi.cc: %s" % sorted(used - registered)
+    index = open(os.path.join(js_dir, "index.js")).read()
+    names = ["Renderer", "Scene", "Cube", "Sphere", "Rectangle", "Cone", "Cylinder", "Disk", "Hyperboloid", "Paraboloid", "AreaLight",
+             "PointLight", "SpotLight", "Cornellbox", "Camera", "Control", "Matte", "Mirror", "Metal", "Glass", "UniformColor",
+             "Checkerboard", "Checkerboard2", "Bilerp", "Mix", "Scale", "UV", "Color", "Matrix", "Vector"]
+    body = index[index.index("const Sail = {"):index.index("};")]
+    for n in names:
+        assert re.search(r"\b%s\b" % n, body), n
+    if os.path.isdir("/root/reference/src"):  # in the build container: the reference modules really exist
+        for mod in ref_modules:
+            assert os.path.exists(os.path.join("/root/reference/src", mod[3:] + ".js")), mod
+
+
 @pytest.mark.parametrize("cfg", [1, 2, 3, 5])
 def test_scene_specialised_kernels_compile_without_a_gpu(capi, cfg):
     """The kernels that NVRTC builds per scene structure at run time must compile for every
