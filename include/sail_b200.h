@@ -231,7 +231,8 @@ int sail_present_begin(sail_ctx* ctx, uint8_t* rgba8);
 int sail_present_end(sail_ctx* ctx);
 
 /* Device-side handles for hosts that combine buffers across GPUs themselves (torch.distributed / NCCL on
- * the host side): raw device pointers of the full-image buffers and the CUDA stream (cudaStream_t). */
+ * the host side): raw device pointers of the full-image buffers and the CUDA stream (cudaStream_t).  The normal / position /
+ * hit-id / depth buffers are filled on demand (by this call, sail_read_aov and the filters that sample them), on that stream. */
 void* sail_device_ptr(sail_ctx* ctx, int32_t which);
 void* sail_stream(sail_ctx* ctx);
 

@@ -175,7 +175,11 @@ void lowerFrame(const sail_frame& f, SailFrameDev& o) {
 
 // Commits a packed scene: only called with a block that sail_pack_scene() accepted, so a failed upload leaves the
 // context (host block, device blocks, cached kernels) exactly as it was.
+int uploadBlock(sail_ctx* ctx, const SailSceneBlock& blk);
+int ensureAovs(sail_ctx* ctx);
 int uploadBlock(sail_ctx* ctx, const SailSceneBlock& blk) {
+    int arc = ensureAovs(ctx);  // the AOVs of the frames rendered so far belong to the scene that is about to be replaced
+    if (arc) return arc;
     ctx->hostScene = blk;
     for (int i = 0; i < ctx->nlocal; i++) {
         SailMember& m = ctx->mem[i];
@@ -397,9 +401,11 @@ int ensureCombined(sail_ctx* ctx, const float** img) {
     return SAIL_OK;
 }
 
-// Sharded contexts: the first-hit AOVs of the last frame, computed on the root (whichever member traced that frame).
+// The first-hit AOVs of the last frame (fstrace.glsl:15-16), computed when somebody asks for them -- a reader, a filter that
+// samples them, or an upload that is about to replace the scene they belong to -- instead of on every launch (32 B per pixel).
+// Sharded contexts: on the root, whichever member traced that frame.
 int ensureAovs(sail_ctx* ctx) {
-    if (!ctx->grouped() || ctx->aovValid || !ctx->isRoot() || !ctx->haveLastFrame || !ctx->sceneLoaded) return SAIL_OK;
+    if (ctx->aovValid || !ctx->isRoot() || !ctx->haveLastFrame || !ctx->sceneLoaded) return SAIL_OK;
     SailMember& r = ctx->root();
     CU(cudaSetDevice(r.device));
     SailAovLaunch L;
@@ -698,7 +704,11 @@ int sail_configure(sail_ctx* ctx, const sail_config* cfg) {
     if (cfg->accum_mode != SAIL_ACCUM_MEAN && cfg->accum_mode != SAIL_ACCUM_SUM) return setErr(ctx, SAIL_ERR_INVALID, "unknown accum_mode %d", cfg->accum_mode);
     if (cfg->kernel < SAIL_KERNEL_MEGA || cfg->kernel > SAIL_KERNEL_AUTO) return setErr(ctx, SAIL_ERR_INVALID, "unknown kernel %d", cfg->kernel);
     if (cfg->specialise < SAIL_SPECIALISE_AUTO || cfg->specialise > SAIL_SPECIALISE_REQUIRE) return setErr(ctx, SAIL_ERR_INVALID, "unknown specialise mode %d", cfg->specialise);
-    if (ctx->grouped() && (cfg->accum_mode != ctx->cfg.accum_mode || cfg->max_bounces != ctx->cfg.max_bounces)) { ctx->combinedValid = false; ctx->aovValid = false; }
+    if (cfg->max_bounces != ctx->cfg.max_bounces) {  // the pending AOVs are those of the old setting (max_bounces < 1: no hit at all)
+        int rc = ensureAovs(ctx);
+        if (rc) return rc;
+    }
+    if (ctx->grouped() && cfg->accum_mode != ctx->cfg.accum_mode) ctx->combinedValid = false;
     ctx->cfg = *cfg;
     return SAIL_OK;
 }
@@ -845,10 +855,10 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
         }
         L.maxBounces = ctx->cfg.max_bounces;
         L.accumMode = sample ? SAIL_ACCUM_SUM : ctx->cfg.accum_mode;
-        L.writeAov = ctx->grouped() ? 0 : 1;  // a sharded context computes them on its root (ensureAovs)
+        L.pad0 = 0;
         L.rcpW = dm_rcp((float)ctx->W);
         L.rcpH = dm_rcp((float)ctx->H);
-        L.accum = m.accum; L.normal = m.normal; L.position = m.position; L.hitId = m.hitId; L.depth = m.depth;
+        L.accum = m.accum;
         L.scene = m.dScene;
         L.sceneSmem = (unsigned)sailSceneSmemBytes(ctx->hostScene.n, ctx->hostScene.ln);
         L.nframes = 0;
@@ -912,8 +922,7 @@ int sail_synchronize(sail_ctx* ctx) {
     return SAIL_OK;
 }
 
-void* sail_device_ptr(sail_ctx* ctx, int32_t which) {
-    if (!ctx) return nullptr;
+static void* rawBuffer(sail_ctx* ctx, int32_t which) {
     SailMember& r = ctx->root();
     switch (which) {
         case SAIL_AOV_COLOR: return r.accum;
@@ -924,11 +933,16 @@ void* sail_device_ptr(sail_ctx* ctx, int32_t which) {
     }
     return nullptr;
 }
+void* sail_device_ptr(sail_ctx* ctx, int32_t which) {
+    if (!ctx) return nullptr;
+    if (which != SAIL_AOV_COLOR && ensureAovs(ctx) != SAIL_OK) return nullptr;  // queued on the context's stream
+    return rawBuffer(ctx, which);
+}
 void* sail_stream(sail_ctx* ctx) { return ctx ? (void*)ctx->root().stream : nullptr; }
 
 int sail_read_aov(sail_ctx* ctx, int32_t which, void* out, size_t out_bytes) {
     if (!ctx) return SAIL_ERR_INVALID;
-    const void* src = sail_device_ptr(ctx, which);
+    const void* src = rawBuffer(ctx, which);
     if (!src) return setErr(ctx, SAIL_ERR_INVALID, "unknown AOV %d", which);
     size_t bytes = npix(ctx) * ((which == SAIL_AOV_HIT_ID || which == SAIL_AOV_DEPTH) ? 4 : 12);
     if (which == SAIL_AOV_COLOR) {

@@ -48,13 +48,9 @@ struct SailLaunch {
     int maxBounces;
     int nframes;
     int accumMode;       // SAIL_ACCUM_*
-    int writeAov;
+    int pad0;
     float rcpW, rcpH;
     float* accum;        // W*H*3
-    float* normal;       // W*H*3
-    float* position;     // W*H*3
-    int* hitId;          // W*H
-    float* depth;        // W*H
     const SailSceneBlock* scene;
     unsigned sceneSmem;  // dynamic shared memory bytes (sailSceneSmemBytes)
     SailFrameDev frames[SAIL_MAX_BATCH];
@@ -135,20 +131,16 @@ SD void sailMegaBody(const SailLaunch& L) {
     const float a = fx * L.rcpW, b = fy * L.rcpH;
 
     V3 c = mk3(L.accum[3 * pix], L.accum[3 * pix + 1], L.accum[3 * pix + 2]);
-    AovSink aov;
-    aov.normal = L.normal; aov.position = L.position; aov.hitId = L.hitId; aov.depth = L.depth;
-    aov.pix = pix;
     for (int k = 0; k < L.nframes; k++) {
         const SailFrameDev& f = L.frames[k];
         Ray ray;
         ray.o = ld3(f.eye);
         ray.d = primaryDir(f, a, b);
-        aov.on = L.writeAov && k == L.nframes - 1;  // the AOVs of a launch are those of its last frame
         float tss = f.timeSinceStart;
 #ifndef SAIL_RELOAD_TIME
         asm volatile("" : "+f"(tss));  // one register instead of three uniform-path instructions per bounce to re-read it
 #endif
-        V3 e = tracePath<F>(sc, ray, L.maxBounces, fx, fy, fz, tss, aov);
+        V3 e = tracePath<F>(sc, ray, L.maxBounces, fx, fy, fz, tss);
         e = mk3(nanToZero(e.x), nanToZero(e.y), nanToZero(e.z));
         if (L.accumMode == 0) c = mix3(e, c, f.textureWeight);  // fstrace.glsl:14
         else c = c + e;

@@ -509,9 +509,10 @@ SD V3 shade(const SceneView& sc, const Hit& h, V2 u, V3 wo, V3& wi, V3& fpdf) {
     return h.emission + direct;
 }
 
-// First-hit AOVs of one path (fstrace.glsl:8,15-16 plus the hit id / depth this library adds).  They are
-// written straight to memory from inside the bounce loop of the frame that wants them (the last of a launch)
-// instead of being carried in eight registers through every frame.
+// First-hit AOVs of one path (fstrace.glsl:8,15-16 plus the hit id / depth this library adds).  The trace kernels do not
+// write them: the reference overwrites its normal / position attachments every frame (webgl.js:65-73), which here would be
+// 32 B per pixel per launch that nobody reads on most frames.  sail_aov_kernel (sail_combine.cuh) computes them from the last
+// frame's uniforms when a reader or a filter asks (sail_api.cu ensureAovs).
 struct AovSink {
     float* normal;
     float* position;
@@ -555,26 +556,20 @@ SD bool lastBounceNeedsRecord(const SailShape& s) {
 // ---- trace(), path.glsl:16-38 -----------------------------------------------------------------------------
 // fx, fy, fz = gl_FragCoord.xyz.  Returns the radiance sample e.
 template <int F>
-SD V3 tracePath(const SceneView& sc, Ray ray, int maxBounces, float fx, float fy, float fz, float timeSinceStart,
-                const AovSink& aov) {
+SD V3 tracePath(const SceneView& sc, Ray ray, int maxBounces, float fx, float fy, float fz, float timeSinceStart) {
     V3 fpdf = splat3(1.0f), e = splat3(0.0f);
     int deepth = 0;
-    if (aov.on && maxBounces < 1) writeAov(aov, splat3(0.0f), splat3(0.0f), -1, SAIL_MAX_DISTANCE);
     while (deepth++ < maxBounces) {
         // Last bounce without NEE: only a hit on an emissive object adds anything (below).  If the ray does not even
         // touch one, the nearest-hit scan over the other objects is dead code as well.
-        if (!(F & SAIL_F_NEE) && SAIL_IS_LAST_BOUNCE(deepth, maxBounces) && !(deepth == 1 && aov.on) && !touchesMasked<F>(sc, ray, sc.emissive)) break;
+        if (!(F & SAIL_F_NEE) && SAIL_IS_LAST_BOUNCE(deepth, maxBounces) && !touchesMasked<F>(sc, ray, sc.emissive)) break;
         const Nearest nr = nearestObject<F>(sc, ray);
-        if (nr.id < 0) {
-            if (deepth == 1 && aov.on) writeAov(aov, splat3(0.0f), splat3(0.0f), nr.id, nr.t);
-            break;
-        }
+        if (nr.id < 0) break;
         // Last bounce, object without emission (and no NEE for it): the hit adds (BLACK + BLACK) * fpdf = +0 to `e`
         // (fpdf is a product of values clamped to [0, 1]; `e` is never -0), so not even its hit record is needed.
-        if (SAIL_IS_LAST_BOUNCE(deepth, maxBounces) && !(deepth == 1 && aov.on) && !lastBounceNeedsRecord<F>(sc.shape[nr.id])) break;
+        if (SAIL_IS_LAST_BOUNCE(deepth, maxBounces) && !lastBounceNeedsRecord<F>(sc.shape[nr.id])) break;
         Hit h;
         hitRecord<F>(sc, nr.id, nr.t, ray, h);
-        if (deepth == 1 && aov.on) writeAov(aov, h.n, h.p, h.index, h.d);
         // The last bounce only contributes `shade() * fpdf` (path.glsl:27): the sampled direction, the BSDF weight and the
         // respawned ray it also produces are never read again.  shade() = emission + direct, and direct is non-zero only
         // for non-emissive matte hits with lights present (path.glsl:10), so everywhere else the RNG pair, the shading

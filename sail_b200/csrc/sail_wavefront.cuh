@@ -31,7 +31,6 @@
 template <int F>
 SD void sailWaveBody(const SailLaunch& L) {
     __shared__ float slot[SAIL_WF_STATE][SAIL_WF_THREADS];  // SoA: lane-consecutive words, conflict free
-    __shared__ float firstHit[6][SAIL_WF_THREADS];          // n, p of the primary hit, indexed by home lane
     __shared__ int hist[2][SAIL_MAX_OBJECTS + 2];  // double buffered: the next bounce's counters are cleared while this one scatters
     const SceneView sc = stageScene(L.scene);
 
@@ -53,8 +52,6 @@ SD void sailWaveBody(const SailLaunch& L) {
     __syncthreads();  // this one publishes the cleared counters
 
     V3 c = inside ? mk3(L.accum[3 * pix], L.accum[3 * pix + 1], L.accum[3 * pix + 2]) : splat3(0.0f);
-    int firstId = -1;
-    float firstT = SAIL_MAX_DISTANCE;
 
     for (int k = 0; k < L.nframes; k++) {
         const SailFrameDev& f = L.frames[k];
@@ -66,8 +63,6 @@ SD void sailWaveBody(const SailLaunch& L) {
         float fx = hx, fy = hy;  // RNG key of the path's pixel
         int home = tid;
         bool alive = inside;
-        firstHit[0][tid] = 0.0f; firstHit[1][tid] = 0.0f; firstHit[2][tid] = 0.0f;
-        firstHit[3][tid] = 0.0f; firstHit[4][tid] = 0.0f; firstHit[5][tid] = 0.0f;
 
         for (int deepth = 1; deepth <= L.maxBounces; deepth++) {
             // ---- stage 1: nearest-hit scan (uniform) ----
@@ -75,10 +70,9 @@ SD void sailWaveBody(const SailLaunch& L) {
             nr.t = SAIL_MAX_DISTANCE;
             nr.id = -1;
             if (alive) nr = nearestObject<F>(sc, ray);
-            if (deepth == 1) { firstId = nr.id; firstT = nr.t; }  // still on the home lane
             if (nr.id < 0) alive = false;                          // path.glsl:22 `break`
             // last bounce on an object that neither emits nor gets NEE: adds +0 to e (see tracePath()), the path is done
-            if (alive && SAIL_IS_LAST_BOUNCE(deepth, L.maxBounces) && deepth > 1 && !lastBounceNeedsRecord<F>(sc.shape[nr.id])) alive = false;
+            if (alive && SAIL_IS_LAST_BOUNCE(deepth, L.maxBounces) && !lastBounceNeedsRecord<F>(sc.shape[nr.id])) alive = false;
             float t = nr.t;
             int id = alive ? nr.id : -1;
             // Primary rays of a tile are coherent already; regroup from the second bounce on.
@@ -124,10 +118,6 @@ SD void sailWaveBody(const SailLaunch& L) {
             if (alive) {
                 Hit h;
                 hitRecord<F>(sc, id, t, ray, h);
-                if (deepth == 1) {
-                    firstHit[0][home] = h.n.x; firstHit[1][home] = h.n.y; firstHit[2][home] = h.n.z;
-                    firstHit[3][home] = h.p.x; firstHit[4][home] = h.p.y; firstHit[5][home] = h.p.z;
-                }
                 if (SAIL_IS_LAST_BOUNCE(deepth, L.maxBounces) && lastBounceIsEmissionOnly<F>(h)) {  // see tracePath(): dead BSDF sample
                     e = e + (h.emission + splat3(0.0f)) * fpdf;
                 } else {
@@ -149,22 +139,12 @@ SD void sailWaveBody(const SailLaunch& L) {
         V3 es = mk3(nanToZero(slot[0][tid]), nanToZero(slot[1][tid]), nanToZero(slot[2][tid]));
         if (L.accumMode == 0) c = mix3(es, c, f.textureWeight);  // fstrace.glsl:14
         else c = c + es;
-        if (k + 1 < L.nframes) __syncthreads();  // slot[] / firstHit[] are rewritten by the next frame
+        if (k + 1 < L.nframes) __syncthreads();  // slot[] is rewritten by the next frame
     }
     if (!inside) return;
     L.accum[3 * pix] = c.x;
     L.accum[3 * pix + 1] = c.y;
     L.accum[3 * pix + 2] = c.z;
-    if (L.writeAov) {
-        V3 fn = mk3(firstHit[0][tid], firstHit[1][tid], firstHit[2][tid]);
-        V3 fp = mk3(firstHit[3][tid], firstHit[4][tid], firstHit[5][tid]);
-        V3 on = vdivs(fn, 2.0f) + 0.5f;
-        V3 op = normalize3(fp);
-        L.normal[3 * pix] = on.x; L.normal[3 * pix + 1] = on.y; L.normal[3 * pix + 2] = on.z;
-        L.position[3 * pix] = op.x; L.position[3 * pix + 1] = op.y; L.position[3 * pix + 2] = op.z;
-        L.hitId[pix] = firstId;
-        L.depth[pix] = firstT;
-    }
 }
 
 template <int F>
