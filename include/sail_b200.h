@@ -131,7 +131,11 @@ typedef struct sail_config {
     float filter_radius[2];   /* FILTER_WINDOW_RADIUS / FILTER_WAVELET_R */
     float filter_weights[16]; /* windowWeightTable built by filter/{box,gaussian,mitchell,sinc,triangle}.js */
     int32_t specialise;       /* SAIL_SPECIALISE_* (was reserved: 0 keeps the default) */
-    int32_t reserved[3];
+    int32_t rr_start_bounce;  /* Russian roulette from this bounce on: a path survives bounce d >= rr_start_bounce with probability
+                                 q = clamp(max(throughput), 0.05, 1) and is scaled by 1/q.  0 = off (default).  NOT in the reference
+                                 (fixed MAXBOUNCES, const/define.glsl:6): an opt-in extension; images then differ from the
+                                 reference estimator's by noise, not in expectation. */
+    int32_t reserved[2];
 } sail_config;
 
 /* One frame's uniforms: Tracer.render(), src/core/tracer.js:92-101 / src/core/shader.js:41-49. */

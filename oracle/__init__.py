@@ -51,6 +51,10 @@ class Oracle:
         lib.oracle_present.argtypes = [ctypes.c_int, ctypes.c_int, _f32p, _f32p, _f32p, ctypes.c_int, ctypes.c_float,
                                        _f32p, _f32p, ctypes.c_void_p, ctypes.c_void_p]
 
+    def set_russian_roulette(self, start_bounce):
+        """Opt-in extension (not in the reference): Russian roulette from bounce ``start_bounce`` on; 0 = off."""
+        self.lib.oracle_set_russian_roulette(int(start_bounce))
+
     def set_scene(self, objects, texparams, lights):
         o = np.ascontiguousarray(objects, dtype=np.float32).reshape(-1)
         t = np.ascontiguousarray(texparams, dtype=np.float32).reshape(-1)

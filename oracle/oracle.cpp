@@ -24,8 +24,11 @@ thread_local uint64_t g_sail_ops = 0;
 #include "oracle_filters.h"
 
 static std::vector<float> g_objects, g_texparams, g_lights;
+static int g_rr_start = 0;  // Russian roulette start bounce for the following frames (0 = off)
 
 extern "C" {
+
+void oracle_set_russian_roulette(int start_bounce) { g_rr_start = start_bounce > 0 ? start_bounce : 0; }
 
 int oracle_set_scene(const float* objs, int n, const float* texparams, int tn, const float* lts, int ln) {
     if (n < 0 || tn < 0 || ln < 0) return -1;
@@ -47,6 +50,7 @@ static void set_frame(const float* matrix, const float* eye, float textureWeight
     U.textureWeight = real(textureWeight);
     U.timeSinceStart_ = real(time);
     U.maxBounces = maxBounces;
+    U.rrStart = g_rr_start;
 }
 
 // One progressive frame (Tracer.render, src/core/tracer.js:92-101 + fstrace.glsl:6-17).

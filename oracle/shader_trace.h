@@ -153,6 +153,16 @@ static inline void trace(Ray ray, int maxDeepth, vec3& e, vec3& n, vec3& p, int*
         vec3 _fpdf;
         e += shade(ins, -ray.dir, wi, _fpdf) * fpdf;
         fpdf *= _fpdf;
+        // Russian roulette -- NOT in the reference (fixed MAXBOUNCES, define.glsl:6); an opt-in extension the build's brief names
+        // (BASELINE.json north_star), off unless rrStart > 0.  From bounce rrStart on a path survives with probability
+        // q = clamp(max(fpdf), 0.05, 1) and its throughput is divided by q; the decision draws one more number from the
+        // shader's own hash (random(), util/random.glsl:1-4) with a third scale vector.
+        if (U.rrStart > 0 && deepth >= U.rrStart && deepth < maxDeepth) {
+            real q = clamp(max(fpdf.x, max(fpdf.y, fpdf.z)), real(0.05f), real(1.0f));
+            real u = random(vec3(37.1234f, 91.4567f, 231.9876f), ins.seed);
+            if (!(u < q)) break;
+            fpdf = fpdf * (real(1.0f) / q);
+        }
         real outdot = dot(ins.normal, wi);
         ray.origin = ins.hit + ins.normal * (outdot > real(EPSILON) ? real(0.0001f) : real(-0.0001f));
         ray.dir = wi;

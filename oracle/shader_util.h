@@ -69,6 +69,7 @@ struct Uniforms {
     vec3 eye;
     sampler2D objects_{nullptr, 18, 0}, texParams_{nullptr, 16, 0}, lights_{nullptr, 18, 0};
     int maxBounces = MAXBOUNCES;  // define.glsl:6; config 5 of BASELINE.json raises it to 16
+    int rrStart = 0;              // Russian roulette from this bounce on (0 = off, the reference's behaviour): see trace()
 };
 static Uniforms U;
 static thread_local vec3 gl_FragCoord;

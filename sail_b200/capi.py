@@ -45,7 +45,8 @@ class Config(ctypes.Structure):
                 ("light_mask", ctypes.c_uint32), ("trace_id", ctypes.c_int32), ("max_bounces", ctypes.c_int32),
                 ("accum_mode", ctypes.c_int32), ("kernel", ctypes.c_int32), ("filter_id", ctypes.c_int32),
                 ("filter_gamma_c", ctypes.c_float), ("filter_radius", ctypes.c_float * 2),
-                ("filter_weights", ctypes.c_float * 16), ("specialise", ctypes.c_int32), ("reserved", ctypes.c_int32 * 3)]
+                ("filter_weights", ctypes.c_float * 16), ("specialise", ctypes.c_int32), ("rr_start_bounce", ctypes.c_int32),
+                ("reserved", ctypes.c_int32 * 2)]
 
 
 class Frame(ctypes.Structure):

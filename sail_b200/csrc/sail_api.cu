@@ -41,9 +41,9 @@ struct SailMember {
     float *accum = nullptr, *normal = nullptr, *position = nullptr, *depth = nullptr;
     int* hitId = nullptr;
     bool timed = false;
-    // the scene-specialised kernels loaded on this device: [kind 0 mega, 1 wavefront][0 full-range RNG sine, 1 |arg| < 2^22 only]
-    void* jitFn[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
-    unsigned jitBlock[2][2] = {{0, 0}, {0, 0}};
+    // the scene-specialised kernels loaded on this device: [kind 0 mega, 1 wavefront][variant: bit 0 = RNG sine for |arg| < 2^22 only, bit 1 = with Russian roulette]
+    void* jitFn[2][4] = {{nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr}};
+    unsigned jitBlock[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
     sailNcclComm_t comm = nullptr;
 };
 
@@ -77,13 +77,14 @@ struct sail_ctx {
     SailSceneBlock hostScene;
     uint64_t launches = 0;
     // scene-specialised kernels (sail_jit.cpp): requested per kernel kind after an upload, compiled on a worker thread
-    SailJitJob* jitJob[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
-    bool jitRequested[2][2] = {{false, false}, {false, false}}, jitFailed[2][2] = {{false, false}, {false, false}};
-    char jitNote[2][2][320];
+    SailJitJob* jitJob[2][4];
+    bool jitRequested[2][4], jitFailed[2][4];
+    char jitNote[2][4][320];
     char kernelInfo[400];
     char err[512];
     sail_ctx() {
         err[0] = 0; kernelInfo[0] = 0; memset(jitNote, 0, sizeof(jitNote)); combineInfo[0] = 0;
+        memset(jitJob, 0, sizeof(jitJob)); memset(jitRequested, 0, sizeof(jitRequested)); memset(jitFailed, 0, sizeof(jitFailed));
         memset(&lastFrame, 0, sizeof(lastFrame));
     }
     bool grouped() const { return groupSize > 1; }
@@ -456,6 +457,7 @@ int kernelKind(const sail_ctx* ctx, int F, bool jit) {
 
 // Looks after the scene-specialised kernel of `kind`: requests its compilation once per upload and, when the cubin is
 // there, loads it on every local member.  Returns true when all members have it.  `wait` blocks on the compiler.
+// `small`: the kernel variant, bit 0 = RNG arguments proven < 2^22, bit 1 = Russian roulette compiled in
 bool specialisedReady(sail_ctx* ctx, int kind, int small, int F, bool wait) {
     if (ctx->jitFailed[kind][small]) return false;
     // SAIL_B200_JIT_SYNC=1: SAIL_SPECIALISE_AUTO waits for the compiler too (test suites that must exercise the specialised kernels)
@@ -703,6 +705,7 @@ int sail_configure(sail_ctx* ctx, const sail_config* cfg) {
     if (cfg->filter_id < 0 || cfg->filter_id > SAIL_FILTER_TONEMAPPING) return setErr(ctx, SAIL_ERR_INVALID, "unknown filter id %d", cfg->filter_id);
     if (cfg->accum_mode != SAIL_ACCUM_MEAN && cfg->accum_mode != SAIL_ACCUM_SUM) return setErr(ctx, SAIL_ERR_INVALID, "unknown accum_mode %d", cfg->accum_mode);
     if (cfg->kernel < SAIL_KERNEL_MEGA || cfg->kernel > SAIL_KERNEL_AUTO) return setErr(ctx, SAIL_ERR_INVALID, "unknown kernel %d", cfg->kernel);
+    if (cfg->rr_start_bounce < 0 || cfg->rr_start_bounce > 1024) return setErr(ctx, SAIL_ERR_INVALID, "rr_start_bounce %d out of range", cfg->rr_start_bounce);
     if (cfg->specialise < SAIL_SPECIALISE_AUTO || cfg->specialise > SAIL_SPECIALISE_REQUIRE) return setErr(ctx, SAIL_ERR_INVALID, "unknown specialise mode %d", cfg->specialise);
     if (cfg->max_bounces != ctx->cfg.max_bounces) {  // the pending AOVs are those of the old setting (max_bounces < 1: no hit at all)
         int rc = ensureAovs(ctx);
@@ -824,7 +827,7 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
     const int F = ctx->hostScene.features & SAIL_F_ALL;
     const bool tryJit = ctx->cfg.specialise != SAIL_SPECIALISE_OFF;
     int kind = kernelKind(ctx, F, tryJit);
-    const int small = rngArgsSmall(ctx, frames, count) ? 1 : 0;
+    const int small = (rngArgsSmall(ctx, frames, count) ? 1 : 0) | (ctx->cfg.rr_start_bounce > 0 ? 2 : 0);
     bool jit = false;
     if (tryJit) {
         jit = specialisedReady(ctx, kind, small, F, ctx->cfg.specialise == SAIL_SPECIALISE_REQUIRE);
@@ -855,7 +858,7 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
         }
         L.maxBounces = ctx->cfg.max_bounces;
         L.accumMode = sample ? SAIL_ACCUM_SUM : ctx->cfg.accum_mode;
-        L.pad0 = 0;
+        L.rrStart = ctx->cfg.rr_start_bounce;
         L.rcpW = dm_rcp((float)ctx->W);
         L.rcpH = dm_rcp((float)ctx->H);
         L.accum = m.accum;
@@ -909,7 +912,7 @@ int sail_specialise_wait(sail_ctx* ctx) {
     const int F = ctx->hostScene.features & SAIL_F_ALL;
     const int kind = kernelKind(ctx, F, true);
     // the variant the last frames asked for (a fresh context: the one a session starts with)
-    const int small = ctx->haveLastFrame ? (rngArgsSmall(ctx, &ctx->lastFrame, 1) ? 1 : 0) : 1;
+    const int small = (ctx->haveLastFrame ? (rngArgsSmall(ctx, &ctx->lastFrame, 1) ? 1 : 0) : 1) | (ctx->cfg.rr_start_bounce > 0 ? 2 : 0);
     return specialisedReady(ctx, kind, small, F, true) ? 0 : 1;
 }
 
@@ -1164,7 +1167,7 @@ int sail_trace_dump(sail_ctx* ctx, const sail_frame* frame, int32_t* hit_id, flo
     size_t n = npix(ctx), B = (size_t)ctx->cfg.max_bounces;
     if (B == 0) return setErr(ctx, SAIL_ERR_INVALID, "max_bounces is 0");
     SailDumpLaunch L;
-    L.W = ctx->W; L.H = ctx->H; L.maxBounces = (int)B;
+    L.W = ctx->W; L.H = ctx->H; L.maxBounces = (int)B; L.rrStart = ctx->cfg.rr_start_bounce;
     L.rcpW = dm_rcp((float)ctx->W); L.rcpH = dm_rcp((float)ctx->H);
     L.scene = m.dScene;
     L.hitId = nullptr; L.t = nullptr; L.rays = nullptr; L.radiance = nullptr;

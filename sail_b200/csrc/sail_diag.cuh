@@ -25,7 +25,7 @@ __global__ void __launch_bounds__(SAIL_CTA_THREADS) sail_intersect_kernel(const 
 }
 
 struct SailDumpLaunch {
-    int W, H, maxBounces;
+    int W, H, maxBounces, rrStart;
     float rcpW, rcpH;
     const SailSceneBlock* scene;
     int* hitId;
@@ -70,6 +70,7 @@ __global__ void __launch_bounds__(SAIL_CTA_THREADS) sail_trace_dump_kernel(const
         V3 wi, _fpdf;
         e = e + shade<SAIL_F_ALL>(sc, h, u, -ray.d, wi, _fpdf) * fpdf;
         fpdf = fpdf * _fpdf;
+        if (!russianRoulette<SAIL_F_ALL>(L.rrStart, deepth, B, fx, fy, fz, seed, fpdf)) break;
         float outdot = dot3(h.n, wi);
         ray.o = h.p + h.n * (outdot > SAIL_EPSILON ? 0.0001f : -0.0001f);
         ray.d = wi;

@@ -208,7 +208,8 @@ int makePlan(int kind, int F, int minCtas, int rngSmall, const SailSceneBlock* s
     }
     char masks[200];
     snprintf(masks, sizeof(masks), " plugins=%x/%x/%x/%x/%x/%x/%x/%x", shapes, mats, texs, lights, glass, matte, tr, lightShapes);
-    if (!rngSmall) snprintf(masks + strlen(masks), sizeof(masks) - strlen(masks), " rng=full-range");
+    if (!(rngSmall & 1)) snprintf(masks + strlen(masks), sizeof(masks) - strlen(masks), " rng=full-range");
+    if (rngSmall & 2) snprintf(masks + strlen(masks), sizeof(masks) - strlen(masks), " +rr");
     if (const char* e = extraDefs.empty() ? nullptr : getenv("SAIL_B200_JIT_DEFINES")) snprintf(masks + strlen(masks), sizeof(masks) - strlen(masks), " -D%.60s", e);
     unsigned block = SAIL_JIT_CTA_THREADS;
     if (kind == 1) {  // wavefront: paths per CTA (sail_wavefront.cuh SAIL_WF_THREADS), 64 registers per thread fill the SM
@@ -216,7 +217,7 @@ int makePlan(int kind, int F, int minCtas, int rngSmall, const SailSceneBlock* s
         // config 2 3930 / 3956 / 3768
         int wf = (F & 1 /* SAIL_F_QUADRICS */) ? 512 : ((F & 2 /* SAIL_F_GLOSSY */) ? 256 : SAIL_JIT_WF_THREADS_DEFAULT);
         if (const char* e = getenv("SAIL_B200_WF_THREADS")) wf = atoi(e);
-        if (wf != 128 && wf != 256 && wf != 512) { setErr(err, errlen, "SAIL_B200_WF_THREADS must be 128, 256 or 512"); return 2; }
+        if (wf != 128 && wf != 256 && wf != 384 && wf != 512) { setErr(err, errlen, "SAIL_B200_WF_THREADS must be 128, 256, 384 or 512"); return 2; }
         block = (unsigned)wf;
         if (wf != 128) minCtas = (int)(65536u / (64u * block));
     }
@@ -236,7 +237,8 @@ int makePlan(int kind, int F, int minCtas, int rngSmall, const SailSceneBlock* s
     // small scenes without quadrics: the nearest-hit scan inlined at both call sites (path ray, shadow ray) instead of one shared
     // out-of-line copy -- config 5 +2.8 %, config 2 +-0; with quadrics the scan is too large (config 3 -23 %)
     if (!(F & 1 /* SAIL_F_QUADRICS */) && n <= 8) tuning += "#define SAIL_INLINE_SCAN 1\n";
-    if (rngSmall) tuning += "#define SAIL_RNG_SMALL_ARGS 1\n";
+    if (rngSmall & 1) tuning += "#define SAIL_RNG_SMALL_ARGS 1\n";
+    tuning += (rngSmall & 2) ? "#define SAIL_JIT_RR 1\n" : "#define SAIL_JIT_RR 0\n";
     char src[4096];
     snprintf(src, sizeof(src),
              "%s#define SAIL_JIT_NRUNS %d\n#define SAIL_JIT_RUN_CATS %s\n#define SAIL_JIT_RUN_STARTS %s\n#define SAIL_JIT_RUN_LENS %s\n"

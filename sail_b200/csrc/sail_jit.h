@@ -19,7 +19,7 @@ struct SailJitJob;
 // kind: 0 megakernel, 1 wavefront.  Starts (or finds) the NVRTC compilation of the kernel specialised for `scene`'s structure on a
 // worker thread and returns its job, or null with a message in `err` (NVRTC missing, scene not specialisable ...): the caller then
 // keeps using the ahead-of-time variant.  Never blocks on the compiler.
-// rngSmall != 0: the caller guarantees |argument| < 2^22 for every sine of the hash RNG (sail_shade.cuh sinPair), so the
+// rngSmall bit 1: Russian roulette compiled in (sail_config.rr_start_bounce > 0).  rngSmall bit 0: the caller guarantees |argument| < 2^22 for every sine of the hash RNG (sail_shade.cuh sinPair), so the
 // large-argument reduction is not compiled.
 SailJitJob* sail_jit_request(int kind, int F, int minCtas, int rngSmall, const SailSceneBlock* scene, char* err, int errlen);
 // 0: compiled, module loaded on `device` (the current device), `out` filled.  1: still compiling (only when wait == 0).

@@ -48,7 +48,7 @@ struct SailLaunch {
     int maxBounces;
     int nframes;
     int accumMode;       // SAIL_ACCUM_*
-    int pad0;
+    int rrStart;         // Russian roulette from this bounce on; 0 = off (sail_config.rr_start_bounce)
     float rcpW, rcpH;
     float* accum;        // W*H*3
     const SailSceneBlock* scene;
@@ -140,7 +140,7 @@ SD void sailMegaBody(const SailLaunch& L) {
 #ifndef SAIL_RELOAD_TIME
         asm volatile("" : "+f"(tss));  // one register instead of three uniform-path instructions per bounce to re-read it
 #endif
-        V3 e = tracePath<F>(sc, ray, L.maxBounces, fx, fy, fz, tss);
+        V3 e = tracePath<F>(sc, ray, L.maxBounces, fx, fy, fz, tss, L.rrStart);
         e = mk3(nanToZero(e.x), nanToZero(e.y), nanToZero(e.z));
         if (L.accumMode == 0) c = mix3(e, c, f.textureWeight);  // fstrace.glsl:14
         else c = c + e;

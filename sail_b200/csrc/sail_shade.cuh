@@ -64,6 +64,28 @@ SD V2 random2(float fx, float fy, float fz, float seed) {
     return mk2(ffract(s2.x * 43758.5453f + seed), ffract(s2.y * 43758.5453f + seed));
 }
 
+// Russian roulette -- no counterpart in the reference (fixed MAXBOUNCES, const/define.glsl:6); the opt-in extension the brief
+// names, off unless sail_config.rr_start_bounce > 0 (SailLaunch::rrStart) and then defined by the oracle's trace()
+// (oracle/shader_trace.h): from bounce rrStart on a path survives with probability q = clamp(max(fpdf), 0.05, 1), decided by one
+// more draw of the shader's hash, random(scale, seed) of util/random.glsl:1-4 with a third scale vector; survivors are scaled
+// by 1 / q.  Returns false when the path ends.  SAIL_HAS_RR: a scene-specialised kernel is built with or without it.
+#ifdef SAIL_JIT_NRUNS
+#define SAIL_HAS_RR (SAIL_JIT_RR)
+#else
+#define SAIL_HAS_RR 1
+#endif
+template <int F>
+SD bool russianRoulette(int rrStart, int deepth, int maxBounces, float fx, float fy, float fz, float seed, V3& fpdf) {
+    if (!SAIL_HAS_RR || rrStart <= 0 || deepth < rrStart || deepth >= maxBounces) return true;
+    const float q = fclamp(fmax2(fpdf.x, fmax2(fpdf.y, fpdf.z)), 0.05f, 1.0f);
+    const float ax = fx + seed, ay = fy + seed, az = fz + seed;
+    const float d = ax * 37.1234f + ay * 91.4567f + az * 231.9876f;
+    const float u = ffract(sail_sin(d) * 43758.5453f + seed);
+    if (!(u < q)) return false;
+    fpdf = fpdf * dm_rcp(q);
+    return true;
+}
+
 // ---- util/sampler.glsl ---------------------------------------------------------------------------
 SD V3 uniformSampleSphere(V2 u) {
     float z = 1.0f - 2.0f * u.x;
@@ -556,7 +578,7 @@ SD bool lastBounceNeedsRecord(const SailShape& s) {
 // ---- trace(), path.glsl:16-38 -----------------------------------------------------------------------------
 // fx, fy, fz = gl_FragCoord.xyz.  Returns the radiance sample e.
 template <int F>
-SD V3 tracePath(const SceneView& sc, Ray ray, int maxBounces, float fx, float fy, float fz, float timeSinceStart) {
+SD V3 tracePath(const SceneView& sc, Ray ray, int maxBounces, float fx, float fy, float fz, float timeSinceStart, int rrStart = 0) {
     V3 fpdf = splat3(1.0f), e = splat3(0.0f);
     int deepth = 0;
     while (deepth++ < maxBounces) {
@@ -585,6 +607,7 @@ SD V3 tracePath(const SceneView& sc, Ray ray, int maxBounces, float fx, float fy
         e = e + shade<F>(sc, h, u, -ray.d, wi, _fpdf) * fpdf;
         if (SAIL_IS_LAST_BOUNCE(deepth, maxBounces)) break;
         fpdf = fpdf * _fpdf;
+        if (!russianRoulette<F>(rrStart, deepth, maxBounces, fx, fy, fz, seed, fpdf)) break;
         float outdot = dot3(h.n, wi);
         ray.o = h.p + h.n * (outdot > SAIL_EPSILON ? 0.0001f : -0.0001f);
         ray.d = wi;

@@ -126,6 +126,7 @@ SD void sailWaveBody(const SailLaunch& L) {
                     V3 wi, _fpdf;
                     e = e + shade<F>(sc, h, u, -ray.d, wi, _fpdf) * fpdf;
                     fpdf = fpdf * _fpdf;
+                    if (!russianRoulette<F>(L.rrStart, deepth, L.maxBounces, fx, fy, 0.5f, seed, fpdf)) alive = false;
                     const float outdot = dot3(h.n, wi);
                     ray.o = h.p + h.n * (outdot > SAIL_EPSILON ? 0.0001f : -0.0001f);
                     ray.d = wi;

@@ -298,3 +298,35 @@ def test_oracle_matches_golden_v2_bounce_dump(oracle):
         assert bits_equal(d[k], gold["c2_bounce_" + k]), k
     assert gold["c1_converged"].shape == (64, 64, 3) and np.isfinite(gold["c1_converged"]).all()
     assert 0.05 < float(gold["c1_converged"].mean()) < 1.0
+
+
+def test_oracle_reproduces_golden_v3(oracle):
+    """The oracle against its committed round-2 fixture (tests/golden/oracle_v3.npz): plugin-matrix scenes (Oren-Nayar, rough
+    glass, Bilerp / Scale, sphere / disk / stub area lights, reverseNormal, single-row tables) and the opt-in Russian roulette.
+    Guards the oracle -- and the shared detmath.h -- against silent changes; the full-size digests are checked on the GPU box."""
+    import os
+    import matrix_scenes
+    from conftest import ROOT, frame_uniforms, scene_tables
+    from sail_b200 import wire
+    gold = np.load(os.path.join(ROOT, "tests", "golden", "oracle_v3.npz"))
+    W, H = 48, 32
+    for name, fn in sorted(matrix_scenes.MATRIX.items()):
+        scene = fn(W, H)
+        oracle.set_scene(*wire.serialize_scene(scene))
+        acc = np.zeros((H, W, 3), np.float32)
+        for k in range(3):
+            m, eye, w, tm = frame_uniforms(scene, k, W, H)
+            r = oracle.render_frame(W, H, m, eye, w, tm, acc, max_bounces=5, aovs=True)
+        assert np.array_equal(acc.view(np.uint32), gold["m_%s_color" % name].view(np.uint32)), name
+        assert np.array_equal(r["hit_id"], gold["m_%s_hit_id" % name].astype(np.int32)), name
+    scene, o, t, l, bounces = scene_tables(2, W, H)
+    oracle.set_scene(o, t, l)
+    oracle.set_russian_roulette(2)
+    try:
+        acc = np.zeros((H, W, 3), np.float32)
+        for k in range(4):
+            m, eye, w, tm = frame_uniforms(scene, k, W, H)
+            oracle.render_frame(W, H, m, eye, w, tm, acc, max_bounces=bounces)
+    finally:
+        oracle.set_russian_roulette(0)
+    assert np.array_equal(acc.view(np.uint32), gold["rr2_c2_color"].view(np.uint32))

@@ -26,8 +26,9 @@ def capi():
     return c
 
 
-def _compare(capi, oracle, scene, o, t, l, W, H, frames_k, bounces, kernel, specialise, what, tms=None):
+def _compare(capi, oracle, scene, o, t, l, W, H, frames_k, bounces, kernel, specialise, what, tms=None, rr=0):
     oracle.set_scene(o, t, l)
+    oracle.set_russian_roulette(rr)
     acc = np.zeros((H, W, 3), np.float32)
     frames, ref = [], None
     for i, k in enumerate(frames_k):
@@ -36,8 +37,9 @@ def _compare(capi, oracle, scene, o, t, l, W, H, frames_k, bounces, kernel, spec
             tm = tms[i]
         ref = oracle.render_frame(W, H, m, eye, w, tm, acc, max_bounces=bounces, aovs=True)
         frames.append(capi.make_frame(m, eye, w, tm))
+    oracle.set_russian_roulette(0)
     with capi.Context(W, H) as ctx:
-        ctx.configure(max_bounces=bounces, kernel=kernel, specialise=specialise)
+        ctx.configure(max_bounces=bounces, kernel=kernel, specialise=specialise, rr_start_bounce=rr)
         ctx.upload_scene(o, t, l)
         ctx.render_n(frames)
         info = ctx.kernel_info()
@@ -208,3 +210,73 @@ def test_specialisation_is_compiled_off_the_render_path(capi, oracle, monkeypatc
         assert ctx.kernel_info().startswith("jit "), ctx.kernel_info()
         got = ctx.read_accum()
     assert bits_equal(got, acc), mismatch_report(got, acc, "across the kernel swap")
+
+
+@pytest.mark.parametrize("specialise", [2, 1], ids=["jit", "aot"])
+@pytest.mark.parametrize("kernel", [0, 1], ids=["mega", "wavefront"])
+@pytest.mark.parametrize("cfg,rr", [(1, 2), (2, 3), (3, 2), (5, 4)])
+def test_russian_roulette_bit_exact(capi, oracle, cfg, rr, kernel, specialise):
+    """The opt-in Russian roulette (sail_config.rr_start_bounce; no counterpart in the reference, off by default): the kernels
+    end the same paths at the same bounces as the oracle's trace() -- colour, AOVs and hit ids bit for bit."""
+    W, H = 128, 72
+    scene, o, t, l, bounces = scene_tables(cfg, W, H)
+    info = _compare(capi, oracle, scene, o, t, l, W, H, [0, 1, 2], bounces, kernel, specialise, "config %d rr from bounce %d" % (cfg, rr), rr=rr)
+    assert specialise != 2 or "+rr" in info, info
+    # and it really changes the estimator's samples (paths end early) without changing what an image converges to
+    oracle.set_scene(o, t, l)
+    acc = {}
+    for start in (0, rr):
+        oracle.set_russian_roulette(start)
+        a = np.zeros((H, W, 3), np.float32)
+        for k in range(8):
+            m, eye, w, tm = frame_uniforms(scene, k, W, H)
+            oracle.render_frame(W, H, m, eye, w, tm, a, max_bounces=bounces)
+        acc[start] = a
+    oracle.set_russian_roulette(0)
+    assert not np.array_equal(acc[0], acc[rr])
+    assert abs(float(acc[0].mean()) - float(acc[rr].mean())) < 0.05 * float(acc[0].mean()) + 1e-3
+
+
+def _sha(a):
+    import hashlib
+    a = np.ascontiguousarray(a)
+    if a.dtype == np.float32:
+        bits = a.view(np.uint32).copy()
+        bits[np.isnan(a)] = 0x7FC00000
+        a = bits
+    return np.frombuffer(hashlib.sha256(a.tobytes()).digest(), np.uint8)
+
+
+def test_cuda_matches_golden_v3_no_oracle_in_the_loop(capi):
+    """tests/golden/oracle_v3.npz (made by tests/golden/make_golden_v3.py): the plugin-matrix scenes and the Russian roulette at
+    48x32, and SHA-256 digests of frame 2 of every BASELINE config at its stated size -- the CUDA path against the committed
+    fixture alone."""
+    import os
+    from conftest import ROOT
+    from sail_b200 import wire
+    gold = np.load(os.path.join(ROOT, "tests", "golden", "oracle_v3.npz"))
+    W, H = 48, 32
+    for name, fn in sorted(matrix_scenes.MATRIX.items()):
+        scene = fn(W, H)
+        o, t, l = wire.serialize_scene(scene)
+        with capi.Context(W, H) as ctx:
+            ctx.upload_scene(o, t, l)
+            ctx.render_n([capi.make_frame(*frame_uniforms(scene, k, W, H)) for k in range(3)])
+            got = ctx.read_accum()
+            assert bits_equal(got, gold["m_%s_color" % name]), mismatch_report(got, gold["m_%s_color" % name], name)
+            assert np.array_equal(ctx.read_aov(capi.AOV_HIT_ID), gold["m_%s_hit_id" % name].astype(np.int32)), name
+    scene, o, t, l, bounces = scene_tables(2, W, H)
+    with capi.Context(W, H) as ctx:
+        ctx.configure(max_bounces=bounces, rr_start_bounce=2)
+        ctx.upload_scene(o, t, l)
+        ctx.render_n([capi.make_frame(*frame_uniforms(scene, k, W, H)) for k in range(4)])
+        assert bits_equal(ctx.read_accum(), gold["rr2_c2_color"])
+    for cfg, (FW, FH) in FULL_SIZES.items():
+        scene, o, t, l, bounces = scene_tables(cfg, FW, FH)
+        with capi.Context(FW, FH) as ctx:
+            ctx.configure(max_bounces=bounces)
+            ctx.upload_scene(o, t, l)
+            ctx.render_n([capi.make_frame(*frame_uniforms(scene, 2, FW, FH))])
+            assert np.array_equal(_sha(ctx.read_accum()), gold["full_c%d_color_sha256" % cfg]), "config %d colour" % cfg
+            assert np.array_equal(_sha(ctx.read_aov(capi.AOV_HIT_ID)), gold["full_c%d_hit_id_sha256" % cfg]), "config %d hit ids" % cfg
+            assert np.array_equal(_sha(ctx.read_aov(capi.AOV_DEPTH)), gold["full_c%d_depth_sha256" % cfg]), "config %d depth" % cfg
