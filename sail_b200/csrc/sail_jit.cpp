@@ -70,6 +70,8 @@ void* openFirst(const std::vector<std::string>& names, std::string* tried) {
     return nullptr;
 }
 
+void waitForCompilersAtExit();
+
 bool loadApi() {
     if (g_api.tried) return g_api.ok;
     g_api.tried = true;
@@ -89,6 +91,9 @@ bool loadApi() {
     SYM(nv, destroyProgram, "nvrtcDestroyProgram", nvrtcDestroyProgram_t)
 #undef SYM
     if (nvrtcVersion_t ver = (nvrtcVersion_t)dlsym(nv, "nvrtcVersion")) ver(&g_api.nvrtcMajor, &g_api.nvrtcMinor);
+    // Registered AFTER libnvrtc was loaded, so at exit it runs BEFORE libnvrtc's own finalisers: a compilation still in flight is
+    // given a bounded time to finish instead of racing the teardown of the compiler it is running in.
+    atexit(waitForCompilersAtExit);
     g_api.ok = true;
     return true;
 }
@@ -132,21 +137,22 @@ struct SailJitJob {
     std::string err;
     std::vector<char> cubin;
     double secs = 0.0;
-    std::thread worker;
     std::map<int, void*> fn;  // device -> CUfunction (guarded by g_mutex)
 };
 
 namespace {
 
-// Jobs live for the process: a scene structure is compiled once and its cubin is loaded on every device that asks.
+// Jobs live for the process: a scene structure is compiled once and its cubin is loaded on every device that asks.  The
+// registry and the jobs are never destroyed and the compiler threads are detached: a host that exits while NVRTC is still
+// working must not wait for it -- joining from a static destructor deadlocks, because libnvrtc (opened later, so finalised
+// earlier) has already torn down the state its compiler thread is using.  Process exit ends the thread.
 struct Registry {
     std::map<std::string, SailJitJob*> jobs;
-    ~Registry() {
-        for (auto& kv : jobs)
-            if (kv.second->worker.joinable()) kv.second->worker.join();  // do not exit under a running compiler
-    }
 };
-Registry g_reg;
+Registry& registry() {
+    static Registry* r = new Registry;  // intentionally leaked
+    return *r;
+}
 
 // Fills the plan (cache key, generated source, launch shape) for `scene`; 0 or an error code with a message.
 int makePlan(int kind, int F, int minCtas, int rngSmall, const SailSceneBlock* scene, Plan* plan, char* err, int errlen) {
@@ -308,6 +314,19 @@ void compileJob(SailJitJob* job) {
     job->cv.notify_all();
 }
 
+void waitForCompilersAtExit() {
+    std::vector<SailJitJob*> jobs;
+    {
+        std::lock_guard<std::mutex> lock(g_mutex);
+        for (auto& kv : registry().jobs) jobs.push_back(kv.second);
+    }
+    const auto deadline = std::chrono::steady_clock::now() + std::chrono::seconds(20);
+    for (SailJitJob* job : jobs) {
+        std::unique_lock<std::mutex> lk(job->m);
+        job->cv.wait_until(lk, deadline, [job] { return job->done; });
+    }
+}
+
 }  // namespace
 
 SailJitJob* sail_jit_request(int kind, int F, int minCtas, int rngSmall, const SailSceneBlock* scene, char* err, int errlen) {
@@ -315,12 +334,12 @@ SailJitJob* sail_jit_request(int kind, int F, int minCtas, int rngSmall, const S
     if (!loadApi()) { setErr(err, errlen, g_api.why); return nullptr; }
     Plan plan;
     if (makePlan(kind, F, minCtas, rngSmall, scene, &plan, err, errlen) != 0) return nullptr;
-    auto it = g_reg.jobs.find(plan.key);
-    if (it != g_reg.jobs.end()) return it->second;
+    auto it = registry().jobs.find(plan.key);
+    if (it != registry().jobs.end()) return it->second;
     SailJitJob* job = new SailJitJob;
     job->plan = plan;
-    g_reg.jobs[plan.key] = job;
-    job->worker = std::thread(compileJob, job);
+    registry().jobs[plan.key] = job;
+    std::thread(compileJob, job).detach();
     return job;
 }
 

@@ -210,3 +210,23 @@ def test_scene_specialisation_limits(capi):
     with pytest.raises(capi.SailError) as ei:
         capi.jit_compile_check(*tables(alternating))
     assert "16 runs" in str(ei.value)
+
+
+def test_host_may_exit_while_a_kernel_is_compiling(capi):
+    """SAIL_SPECIALISE_AUTO compiles on a worker thread; a host that exits before NVRTC is done must terminate promptly and
+    cleanly (round 2: a static destructor joining that thread deadlocked against libnvrtc's own teardown)."""
+    import subprocess
+    import sys
+    try:
+        _, o, t, l, _ = scene_tables(3, 64, 64)
+        capi.jit_compile_check(o, t, l)
+    except capi.SailError as e:
+        if "NVRTC not found" in str(e):
+            pytest.skip("no NVRTC on this machine")
+        raise
+    code = ("import os, sys; sys.path.insert(0, %r); sys.path.insert(0, %r); os.environ['SAIL_B200_JIT_CHECK_NOWAIT'] = '1'\n"
+            "from sail_b200 import capi; from conftest import scene_tables\n"
+            "_, o, t, l, _ = scene_tables(3, 64, 64)\n"
+            "print(capi.jit_compile_check(o, t, l, capi.KERNEL_WAVEFRONT))\n") % (ROOT, os.path.join(ROOT, "tests"))
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0 and "compiling" in r.stdout, (r.returncode, r.stdout, r.stderr[-500:])

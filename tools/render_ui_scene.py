@@ -61,8 +61,10 @@ def main():
     r = Renderer((512, 512))
     r.update(scene)
     img = None
-    for _ in range(args.spp // 32):
+    for i in range(args.spp // 32):
         img = np.array(r.render(scene, frames=32))
+        if i == 0:
+            r.ctx.specialise_wait()
     r.save(args.out, img)
     res = {"out": args.out, "spp": scene.sampleCount, "kernel": r.ctx.kernel_info(), "mean_rgb": [float(v) for v in img[..., :3].mean(axis=(0, 1))]}
     r.close()
