@@ -11,7 +11,7 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsail_b200.so")
+LIB_PATH = os.environ.get("SAIL_B200_LIB") or os.path.join(_HERE, "libsail_b200.so")  # SAIL_B200_LIB: A/B runs of two builds
 
 MAX_FRAMES_PER_CALL = 32
 AOV_COLOR, AOV_NORMAL, AOV_POSITION, AOV_HIT_ID, AOV_DEPTH = range(5)

@@ -1027,8 +1027,7 @@ int sail_present_begin(sail_ctx* ctx, uint8_t* rgba8) {
     P.out_u8 = ctx->presentU8;
     // the filter overwrites the device image: it must not overtake the previous copy (long finished in practice)
     if (ctx->copiedOnce) CU(cudaStreamWaitEvent(r.stream, ctx->evCopied, 0));
-    dim3 grid((ctx->W + 31) / 32, (ctx->H + 7) / 8);
-    sail_present_kernel<<<grid, 256, 0, r.stream>>>(P);
+    sailLaunchPresent(P, r.stream);
     ctx->launches++;
     CU(cudaGetLastError());
     CU(cudaEventRecord(ctx->evPresented, r.stream));
@@ -1068,8 +1067,7 @@ int sail_present(sail_ctx* ctx, float* rgba_f32, uint8_t* rgba8) {
     fillPresentParams(ctx, P, img);
     P.out_f32 = rgba_f32 ? ctx->presentF32 : nullptr;
     P.out_u8 = rgba8 ? ctx->presentU8 : nullptr;
-    dim3 grid((ctx->W + 31) / 32, (ctx->H + 7) / 8);
-    sail_present_kernel<<<grid, 256, 0, r.stream>>>(P);
+    sailLaunchPresent(P, r.stream);
     ctx->launches++;
     CU(cudaGetLastError());
     if ((rc = markConsumed(ctx)) != 0) return rc;

@@ -59,30 +59,65 @@ SD V4 textureLinear(const float* img, int W, int H, float u, float v) {
     return a * (1.0f - ty) + b * ty;
 }
 
-// window.glsl:1-8
-SD V3 windowSampler(const PresentParams& P, float cx, float cy, int& count) {
-    if (cx < 0.0f || cx > 1.0f || cy < 0.0f || cy > 1.0f) return splat3(0.0f);
+// window.glsl:1-8 windowSampler + the LINEAR fetch, split per axis.  The 64 taps of a window filter are the products of 8
+// x coordinates (tx +- 4 offsets) and 8 y coordinates: the bounds test, the texel pair, its wrap-around and the 8-bit blend
+// weight of a coordinate are computed once per axis value instead of once per tap (16 instead of 128 coordinate set-ups, 32
+// instead of 512 integer modulos per pixel).  Every tap still evaluates exactly the expressions of textureLinear().
+struct AxisTap {
+    int i0, i1;   // wrapped texel indices
+    float t, omt; // blend weight and 1 - t
+    bool ok;      // coordinate inside [0, 1] (windowSampler's test)
+};
+SD AxisTap axisTap(float c, int size) {
+    AxisTap a;
+    a.ok = !(c < 0.0f || c > 1.0f);
+    int i0;
+    linearCoord(c, size, i0, a.t);
+    a.omt = 1.0f - a.t;
+    a.i0 = wrapIndex(i0, size);
+    a.i1 = wrapIndex(i0 + 1, size);
+    return a;
+}
+SD V3 texel3(const float* img, int W, int x, int y) {
+    const float* p = img + 3 * ((size_t)y * W + x);
+    return mk3(__ldg(p), __ldg(p + 1), __ldg(p + 2));
+}
+SD V3 windowTap(const PresentParams& P, const AxisTap& X, const AxisTap& Y, int& count) {
+    if (!(X.ok && Y.ok)) return splat3(0.0f);
     count++;
-    V4 c = textureLinear(P.color, P.W, P.H, cx, cy);
-    return mk3(c.x, c.y, c.z);
+    const V3 c00 = texel3(P.color, P.W, X.i0, Y.i0), c10 = texel3(P.color, P.W, X.i1, Y.i0);
+    const V3 c01 = texel3(P.color, P.W, X.i0, Y.i1), c11 = texel3(P.color, P.W, X.i1, Y.i1);
+    // textureLinear(): a = c00*(1-tx) + c10*tx, b = c01*(1-tx) + c11*tx, a*(1-ty) + b*ty, per channel, plain scalar operations
+    const V3 a = mk3(c00.x * X.omt + c10.x * X.t, c00.y * X.omt + c10.y * X.t, c00.z * X.omt + c10.z * X.t);
+    const V3 b = mk3(c01.x * X.omt + c11.x * X.t, c01.y * X.omt + c11.y * X.t, c01.z * X.omt + c11.z * X.t);
+    return mk3(a.x * Y.omt + b.x * Y.t, a.y * Y.omt + b.y * Y.t, a.z * Y.omt + b.z * Y.t);
 }
 // window.glsl:26-44 (table lookup i*j+j as written)
 SD V4 filterWindow(const PresentParams& P, float tx, float ty) {
     V3 color = splat3(0.0f);
     float weightSum = 0.0f;
     const float rW = dm_rcp((float)P.W), rH = dm_rcp((float)P.H);
+    AxisTap Xp[4], Xm[4], Yp[4], Ym[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        // window.glsl:10-24: x = vec2(i/W, 0), y = vec2(0, j/H); the shader's `+ 0.0` / `- 0.0` terms leave the sums unchanged
+        const float xx = fdiv(((float)k + 0.5f) * P.radius[0], 4.0f) * rW;
+        const float yy = fdiv(((float)k + 0.5f) * P.radius[1], 4.0f) * rH;
+        Xp[k] = axisTap(tx + xx + 0.0f, P.W);
+        Xm[k] = axisTap(tx - xx + 0.0f, P.W);
+        Yp[k] = axisTap(ty + 0.0f + yy, P.H);
+        Ym[k] = axisTap(ty + 0.0f - yy, P.H);
+    }
+#pragma unroll
     for (int i = 0; i < 4; i++) {
+#pragma unroll
         for (int j = 0; j < 4; j++) {
-            float oi = fdiv(((float)j + 0.5f) * P.radius[0], 4.0f);
-            float oj = fdiv(((float)i + 0.5f) * P.radius[1], 4.0f);
-            // window.glsl:10-24: x = vec2(i/W, 0), y = vec2(0, j/H)
-            float xx = oi * rW, yy = oj * rH;
             int count = 0;
             V3 tmp = splat3(0.0f);
-            tmp = tmp + windowSampler(P, tx + xx + 0.0f, ty + 0.0f + yy, count);
-            tmp = tmp + windowSampler(P, tx + xx - 0.0f, ty + 0.0f - yy, count);
-            tmp = tmp + windowSampler(P, tx - xx + 0.0f, ty - 0.0f + yy, count);
-            tmp = tmp + windowSampler(P, tx - xx - 0.0f, ty - 0.0f - yy, count);
+            tmp = tmp + windowTap(P, Xp[j], Yp[i], count);
+            tmp = tmp + windowTap(P, Xp[j], Ym[i], count);
+            tmp = tmp + windowTap(P, Xm[j], Yp[i], count);
+            tmp = tmp + windowTap(P, Xm[j], Ym[i], count);
             float weight = P.weights[i * j + j];
             weightSum += weight * (float)count;
             color = color + tmp * weight;
@@ -139,13 +174,16 @@ SD float tonemap1(float c) {
     return fdiv(x * (6.2f * x + 0.5f), x * (6.2f * x + 1.7f) + 0.06f);
 }
 
+// KIND: 0 = the point filters (color / gamma / tonemapping / normal / position), 1 = window filters, 2 = wavelet -- three
+// instantiations, so the 64-tap window filter's registers (112) do not set the occupancy of the one-fetch filters.
+template <int KIND>
 __global__ void __launch_bounds__(256) sail_present_kernel(const __grid_constant__ PresentParams P) {
     int x = blockIdx.x * 32 + (threadIdx.x & 31);
     int y = blockIdx.y * 8 + (threadIdx.x >> 5);
     if (x >= P.W || y >= P.H) return;
     // vsrender.glsl:5: texCoord = vertex.xy*0.5+0.5 interpolated to the pixel centre
     float tx = fdiv((float)x + 0.5f, (float)P.W), ty = fdiv((float)y + 0.5f, (float)P.H);
-    V4 v;
+    V4 v = mk4(0.0f, 0.0f, 0.0f, 0.0f);
     switch (P.filter_id) {
         case 0: {  // color.glsl
             V4 c = textureLinear(P.color, P.W, P.H, tx, ty);
@@ -173,8 +211,8 @@ __global__ void __launch_bounds__(256) sail_present_kernel(const __grid_constant
             v = mk4(c.x, c.y, c.z, 1.0f);
             break;
         }
-        case 9: v = filterWavelet(P, tx, ty); break;
-        case 2: case 3: case 4: case 5: case 6: v = filterWindow(P, tx, ty); break;
+        case 9: if (KIND == 2) v = filterWavelet(P, tx, ty); break;
+        case 2: case 3: case 4: case 5: case 6: if (KIND == 1) v = filterWindow(P, tx, ty); break;
         default: v = mk4(0.0f, 0.0f, 0.0f, 0.0f);
     }
     size_t i = (size_t)y * P.W + x;
@@ -192,5 +230,14 @@ __global__ void __launch_bounds__(256) sail_present_kernel(const __grid_constant
         reinterpret_cast<uchar4*>(P.out_u8)[i] = make_uchar4(b[0], b[1], b[2], b[3]);
     }
 }
+
+#ifndef __CUDACC_RTC__
+static inline void sailLaunchPresent(const PresentParams& P, cudaStream_t stream) {
+    dim3 grid((P.W + 31) / 32, (P.H + 7) / 8);
+    if (P.filter_id == 9) sail_present_kernel<2><<<grid, 256, 0, stream>>>(P);
+    else if (P.filter_id >= 2 && P.filter_id <= 6) sail_present_kernel<1><<<grid, 256, 0, stream>>>(P);
+    else sail_present_kernel<0><<<grid, 256, 0, stream>>>(P);
+}
+#endif
 
 #endif
