@@ -20,6 +20,8 @@ d=dict(zip(h,v))
 for k in sorted(d):
     if k.startswith("smsp__pcsamp_warps_issue_stalled") and not k.endswith("not_issued") : 
         pass
+for k in ("sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active","sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active","sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active","sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active","sm__inst_executed_pipe_cbu.avg.pct_of_peak_sustained_active","sm__inst_executed_pipe_adu.avg.pct_of_peak_sustained_active","sm__inst_executed_pipe_fmaheavy.avg.pct_of_peak_sustained_active","sm__inst_executed_pipe_fmalite.avg.pct_of_peak_sustained_active","smsp__thread_inst_executed_per_inst_executed.ratio","dram__bytes.sum.per_second","sm__throughput.avg.pct_of_peak_sustained_elapsed"):
+    if k in d: print("pipe/ratio", k, d[k])
 want=["dram__bytes_read.sum","dram__bytes_write.sum","smsp__inst_executed.sum","sm__inst_executed_pipe_fma.sum","sm__inst_executed_pipe_alu.sum","sm__inst_executed_pipe_xu.sum","l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum","smsp__thread_inst_executed.sum"]
 for k in want:
     if k in d: print(k, d[k])
