@@ -25,6 +25,10 @@
 #ifndef SAIL_WF_THREADS
 #define SAIL_WF_THREADS SAIL_CTA_THREADS
 #endif
+// Bounces before which the paths are regrouped (bit d = bounce d; A/B knob, default: every bounce after the first).
+#ifndef SAIL_WF_REGROUP_MASK
+#define SAIL_WF_REGROUP_MASK 0xffffffffu
+#endif
 #define SAIL_WF_TILE_W (SAIL_WF_THREADS / 8)
 #define SAIL_WF_WARPS_X (SAIL_WF_TILE_W / 8)
 
@@ -76,7 +80,7 @@ SD void sailWaveBody(const SailLaunch& L) {
             float t = nr.t;
             int id = alive ? nr.id : -1;
             // Primary rays of a tile are coherent already; regroup from the second bounce on.
-            if (deepth > 1) {
+            if (deepth > 1 && ((SAIL_WF_REGROUP_MASK >> (deepth & 31)) & 1u)) {
                 // ---- stage 2: counting sort by hit object ----
                 const int key = alive ? nr.id : n;
                 int* hcur = hist[hsel];
