@@ -325,7 +325,7 @@ def run_ours(args, rank, world, local_rank):
                   specialise=capi.SPECIALISE_OFF if args.no_jit else capi.SPECIALISE_AUTO)
     r.update(scene)
     filters = []
-    if tile:  # BASELINE config 5: the filter sweep runs on the root after the gather
+    if args.sharding == "tile":  # BASELINE config 5: the filter sweep runs on the root after the gather (N = 1: same display work)
         for name in args.filters.split(","):
             pp = PluginParams(name)
             pp.addParam("r", "vec2(2.0,2.0)")

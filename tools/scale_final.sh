@@ -4,7 +4,7 @@ TAG=${TAG:-final}
 timeout 300 python -m pytest tests/test_gpu_multi.py -x -q -m gpu 2>&1 | tail -2
 run() {  # workload sharding n
   local out=gpurun_out/${TAG}_$1_$2_$3
-  if [ $3 = 1 ]; then timeout 200 python bench.py --gpus 1 --steps ${STEPS:-40} --warmup 5 --no-cpu --workload $1 > $out.json 2> $out.err
+  if [ $3 = 1 ]; then timeout 200 python bench.py --gpus 1 --steps ${STEPS:-40} --warmup 5 --no-cpu --workload $1 --sharding $2 > $out.json 2> $out.err
   else timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $3 --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $3 --steps ${STEPS:-40} --warmup 5 --no-cpu --workload $1 --sharding $2 > $out.json 2> $out.err; fi
   python - $out $1 $2 $3 <<'PY'
 import json, sys

@@ -6,7 +6,7 @@
 TAG=${TAG:-scale}
 run() {  # workload sharding band n
   local wl=$1 sh=$2 band=$3 n=$4 out=gpurun_out/${TAG}_$1_$2$([ $3 != 0 ] && echo _b$3)_$4
-  if [ $n = 1 ]; then timeout 300 python bench.py --gpus 1 --steps ${STEPS:-40} --warmup 5 --no-cpu --workload $wl > $out.json 2> $out.err
+  if [ $n = 1 ]; then timeout 300 python bench.py --gpus 1 --steps ${STEPS:-40} --warmup 5 --no-cpu --workload $wl --sharding $sh > $out.json 2> $out.err
   else timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $n --steps ${STEPS:-40} --warmup 5 --no-cpu --workload $wl --sharding $sh --band-rows $band > $out.json 2> $out.err; fi
   python - $out $wl $sh $band $n <<'PY'
 import json, sys
