@@ -112,7 +112,7 @@ typedef struct sail_create_info {
     int32_t ndev;           /* 0 or 1: single device.  2..SAIL_MAX_DEVICES: device_ids[0..ndev) */
     int32_t shard_mode;     /* SAIL_SHARD_SAMPLE or SAIL_SHARD_TILE when ndev > 1 */
     int32_t band_rows;      /* SAIL_SHARD_TILE: rows per interleaved band, a multiple of 8 (0 = 8, the measured best: profiles/r02f_scaling.json) */
-    int32_t device_ids[SAIL_MAX_DEVICES];
+    int32_t device_ids[SAIL_MAX_DEVICES];  /* a device may appear more than once: those members share the GPU (peer-memory combine only) */
     int32_t combine;        /* SAIL_COMBINE_* */
     int32_t reserved[3];
 } sail_create_info;

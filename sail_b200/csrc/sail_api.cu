@@ -255,14 +255,14 @@ int checkShard(sail_ctx* ctx, int shard_mode, int band_rows, int combine) {
 bool enablePeerAccess(sail_ctx* ctx) {
     for (int a = 0; a < ctx->nlocal; a++)
         for (int b = 0; b < ctx->nlocal; b++) {
-            if (a == b) continue;
+            if (a == b || ctx->mem[a].device == ctx->mem[b].device) continue;  // members sharing a GPU see each other's memory anyway
             int can = 0;
             if (cudaDeviceCanAccessPeer(&can, ctx->mem[a].device, ctx->mem[b].device) != cudaSuccess || !can) { cudaGetLastError(); return false; }
         }
     for (int a = 0; a < ctx->nlocal; a++) {
         if (cudaSetDevice(ctx->mem[a].device) != cudaSuccess) return false;
         for (int b = 0; b < ctx->nlocal; b++) {
-            if (a == b) continue;
+            if (a == b || ctx->mem[a].device == ctx->mem[b].device) continue;
             cudaError_t e = cudaDeviceEnablePeerAccess(ctx->mem[b].device, 0);
             if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); return false; }
             cudaGetLastError();
@@ -569,6 +569,7 @@ int sail_create(const sail_create_info* info, sail_ctx** out) {
     sail_default_config(&ctx->cfg);
     const int want = info->ndev <= 1 ? 1 : info->ndev;
     if (want > SAIL_MAX_DEVICES) return setErr(ctx, SAIL_ERR_INVALID, "ndev %d exceeds SAIL_MAX_DEVICES (%d)", want, SAIL_MAX_DEVICES);
+    bool shared = false;
     if (want > 1) {
         if (ctx->y0 != 0 || ctx->y1 != ctx->H) return setErr(ctx, SAIL_ERR_INVALID, "a multi-GPU context shards the image itself: row_begin / row_end must be 0");
         int rc = checkShard(ctx, info->shard_mode, info->band_rows, info->combine);
@@ -576,9 +577,14 @@ int sail_create(const sail_create_info* info, sail_ctx** out) {
         for (int i = 0; i < want; i++) {
             if (info->device_ids[i] < 0 || info->device_ids[i] >= ndev)
                 return setErr(ctx, SAIL_ERR_INVALID, "device_ids[%d] = %d out of range (%d devices)", i, info->device_ids[i], ndev);
+            // A device may be listed more than once: several members then share that GPU, each with its own stream and buffers
+            // (no speed-up -- it lets a one-GPU machine run, and test, the sharded path); they combine through peer memory, NCCL
+            // refuses two ranks on one device.
             for (int j = 0; j < i; j++)
-                if (info->device_ids[j] == info->device_ids[i]) return setErr(ctx, SAIL_ERR_INVALID, "device %d listed twice", info->device_ids[i]);
+                if (info->device_ids[j] == info->device_ids[i]) shared = true;
         }
+        if (shared && info->combine == SAIL_COMBINE_NCCL)
+            return setErr(ctx, SAIL_ERR_INVALID, "SAIL_COMBINE_NCCL needs distinct devices (a device is listed twice); use SAIL_COMBINE_AUTO / _P2P");
     } else if (info->device < 0 || info->device >= ndev) {
         return setErr(ctx, SAIL_ERR_INVALID, "device %d out of range (%d devices)", info->device, ndev);
     }
@@ -597,6 +603,7 @@ int sail_create(const sail_create_info* info, sail_ctx** out) {
         int combine = info->combine;
         if (combine == SAIL_COMBINE_P2P && !peers) return setErr(ctx, SAIL_ERR_CUDA, "SAIL_COMBINE_P2P: the devices cannot map each other's memory");
         if (combine == SAIL_COMBINE_AUTO) combine = peers ? SAIL_COMBINE_P2P : SAIL_COMBINE_NCCL;
+        if (combine == SAIL_COMBINE_NCCL && shared) return setErr(ctx, SAIL_ERR_CUDA, "members share a GPU and the other devices cannot map each other's memory: no combine path");
         if (combine == SAIL_COMBINE_NCCL) {
             const SailNccl* nc = sail_nccl();
             if (!nc->ok) return setErr(ctx, SAIL_ERR_CUDA, "%s", nc->why);
