@@ -121,3 +121,70 @@ MATRIX = {
     "single_rows": single_rows,
     "single_object_no_light": single_object_no_light,
 }
+
+
+def random_scene(seed, W, H):
+    """A seeded random scene over the whole plugin surface: 3-9 objects of random shape kind, material (incl. Oren-Nayar, rough and
+    smooth glass, isotropic / anisotropic metal), texture, emission and reverseNormal inside a Cornell box, 0-3 lights of random kind
+    (area lights over sphere / rectangle / disk / a stub shape).  Structure fuzz for the per-scene kernel specialisation."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+
+    def pos(lo=0.6, hi=4.8):
+        return [float(rng.uniform(lo, hi)), float(rng.uniform(0.0, 3.0)), float(rng.uniform(0.4, 4.8))]
+
+    def col():
+        return [float(v) for v in rng.uniform(0.1, 1.0, 3)]
+
+    def material():
+        k = int(rng.integers(0, 7))
+        return [Sail.Matte(0.7), Sail.Matte(0.8, float(rng.uniform(5, 60))), Sail.Mirror(float(rng.uniform(0.5, 1.0))),
+                Sail.Metal(0, float(rng.uniform(0.02, 0.3)), float(rng.uniform(0.02, 0.3))), Sail.Metal(float(rng.uniform(0.05, 0.2))),
+                Sail.Glass(1, 1, float(rng.uniform(1.2, 1.8))),
+                Sail.Glass(0.9, 0.9, 1.5, float(rng.uniform(0.05, 0.3)), float(rng.uniform(0.05, 0.3)))][k]
+
+    def texture():
+        k = int(rng.integers(0, 8))
+        return [Sail.UniformColor(col()), Sail.UniformColor(col()), Sail.Checkerboard(float(rng.uniform(0.05, 0.3)), 0.02),
+                Sail.Checkerboard2(col(), col(), float(rng.uniform(0.05, 0.3))), Sail.Bilerp(col(), col(), col(), col()),
+                Sail.Mix(col(), col(), float(rng.uniform(0, 1))), Sail.Scale(col(), col()), Sail.UV()][k]
+
+    def shape(mat, tex, emission=(0, 0, 0), rev=False):
+        k = int(rng.integers(0, 8))
+        p = pos()
+        if k == 0:
+            return Sail.Cube(p, [p[0] + float(rng.uniform(0.3, 1.2)), p[1] + float(rng.uniform(0.3, 1.2)), p[2] + float(rng.uniform(0.3, 1.2))], mat, tex, emission, rev)
+        if k == 1:
+            return Sail.Sphere(p, float(rng.uniform(0.3, 1.0)), mat, tex, emission, rev)
+        if k == 2:
+            return Sail.Rectangle(p, [p[0] + float(rng.uniform(0.5, 1.5)), p[1] + float(rng.uniform(0.0, 1.0)), p[2] + float(rng.uniform(0.2, 1.0))], mat, tex, emission, rev)
+        if k == 3:
+            return Sail.Cone(p, float(rng.uniform(0.5, 1.5)), float(rng.uniform(0.3, 0.8)), mat, tex, emission, rev)
+        if k == 4:
+            return Sail.Cylinder(p, float(rng.uniform(0.5, 1.5)), float(rng.uniform(0.3, 0.7)), mat, tex, emission, rev)
+        if k == 5:
+            return Sail.Disk(p, float(rng.uniform(0.4, 0.9)), float(rng.uniform(0.0, 0.3)), mat, tex, emission, rev)
+        if k == 6:
+            return Sail.Hyperboloid(p, [0.4, -0.3, -0.6], [float(rng.uniform(0.3, 0.6)), 0.3, float(rng.uniform(0.4, 0.8))], mat, tex, emission, rev)
+        return Sail.Paraboloid(p, 0, float(rng.uniform(0.5, 1.2)), float(rng.uniform(0.3, 0.7)), mat, tex, emission, rev)
+
+    s = Sail.Scene()
+    s.add(Sail.Cornellbox())
+    for _ in range(int(rng.integers(2, 9))):
+        emission = [float(v) for v in rng.uniform(0, 4, 3)] if rng.uniform() < 0.2 else (0, 0, 0)
+        s.add(shape(material(), texture(), emission, bool(rng.uniform() < 0.15)))
+    matte = Sail.Matte(0.7)
+    for _ in range(int(rng.integers(0, 4))):
+        k = int(rng.integers(0, 5))
+        e = [float(v) for v in rng.uniform(0.5, 6, 3)]
+        if k == 0:
+            s.add(Sail.AreaLight(Sail.Rectangle([2.13, 5.48, 2.27], [3.43, 5.48, 3.32], matte, Sail.Color.BLACK), e))
+        elif k == 1:
+            s.add(Sail.AreaLight(Sail.Sphere([float(rng.uniform(1, 4.5)), 4.3, float(rng.uniform(1, 4))], 0.4, matte, Sail.Color.BLACK), e))
+        elif k == 2:
+            s.add(Sail.PointLight([float(rng.uniform(0.5, 5)), 4.6, float(rng.uniform(0.5, 5))], e))
+        elif k == 3:
+            s.add(Sail.SpotLight([float(rng.uniform(1, 4.5)), 5.2, float(rng.uniform(1, 4))], float(rng.uniform(20, 50)), 10, [10 * v for v in e]))
+        else:
+            s.add(Sail.AreaLight(shape(matte, Sail.Color.BLACK), e))  # any shape kind: a real sampler or a stub (Q7)
+    return _finish(s, W, H)

@@ -280,3 +280,16 @@ def test_cuda_matches_golden_v3_no_oracle_in_the_loop(capi):
             assert np.array_equal(_sha(ctx.read_accum()), gold["full_c%d_color_sha256" % cfg]), "config %d colour" % cfg
             assert np.array_equal(_sha(ctx.read_aov(capi.AOV_HIT_ID)), gold["full_c%d_hit_id_sha256" % cfg]), "config %d hit ids" % cfg
             assert np.array_equal(_sha(ctx.read_aov(capi.AOV_DEPTH)), gold["full_c%d_depth_sha256" % cfg]), "config %d depth" % cfg
+
+
+@pytest.mark.parametrize("seed", range(10))
+def test_random_scenes_bit_exact(capi, oracle, seed):
+    """Structure fuzz (tests/matrix_scenes.py random_scene): random shapes / materials / textures / lights / emission /
+    reverseNormal -- every scene compiles its own kernel; the scene-specialised build of one kernel kind and the ahead-of-time
+    variant of the other must both equal the oracle bit for bit."""
+    from sail_b200 import wire
+    W, H = 64, 48
+    scene = matrix_scenes.random_scene(seed, W, H)
+    o, t, l = wire.serialize_scene(scene)
+    _compare(capi, oracle, scene, o, t, l, W, H, [0, 1], 5, seed % 2, 2, "random scene %d (jit)" % seed)
+    _compare(capi, oracle, scene, o, t, l, W, H, [0, 1], 5, 1 - seed % 2, 1, "random scene %d (aot)" % seed)
