@@ -53,14 +53,15 @@ def _compare(capi, oracle, scene, o, t, l, W, H, frames_k, bounces, kernel, spec
     return info
 
 
-@pytest.mark.parametrize("specialise", [2, 1], ids=["jit", "aot"])
+@pytest.mark.parametrize("kernel,specialise", [(2, 2), (2, 1), (0, 2), (1, 2)], ids=["auto-jit", "auto-aot", "mega-jit", "wavefront-jit"])
 @pytest.mark.parametrize("cfg", [1, 2, 3, 4, 5])
-def test_full_size_frame_bit_exact(capi, oracle, cfg, specialise):
-    """Frame k = 2 (non-zero jitter) of each BASELINE config at its stated size, the kernel SAIL_KERNEL_AUTO picks, as
-    the scene-specialised build and as the ahead-of-time variant: colour, AOVs and hit ids equal the oracle's bit for bit."""
+def test_full_size_frame_bit_exact(capi, oracle, cfg, kernel, specialise):
+    """Frame k = 2 (non-zero jitter) of each BASELINE config at its stated size -- the kernel SAIL_KERNEL_AUTO picks as the
+    scene-specialised build and as the ahead-of-time variant, and both kernel kinds explicitly: colour, AOVs and hit ids equal the
+    oracle's bit for bit."""
     W, H = FULL_SIZES[cfg]
     scene, o, t, l, bounces = scene_tables(cfg, W, H)
-    _compare(capi, oracle, scene, o, t, l, W, H, [2], bounces, capi.KERNEL_AUTO, specialise, "config %d at %dx%d" % (cfg, W, H))
+    _compare(capi, oracle, scene, o, t, l, W, H, [2], bounces, kernel, specialise, "config %d at %dx%d" % (cfg, W, H))
 
 
 @pytest.mark.parametrize("specialise", [2, 1], ids=["jit", "aot"])
