@@ -294,3 +294,24 @@ def test_random_scenes_bit_exact(capi, oracle, seed):
     o, t, l = wire.serialize_scene(scene)
     _compare(capi, oracle, scene, o, t, l, W, H, [0, 1], 5, seed % 2, 2, "random scene %d (jit)" % seed)
     _compare(capi, oracle, scene, o, t, l, W, H, [0, 1], 5, 1 - seed % 2, 1, "random scene %d (aot)" % seed)
+
+
+@pytest.mark.parametrize("size", [(1, 1), (37, 29), (130, 7), (8, 200)])
+@pytest.mark.parametrize("kernel", [0, 1], ids=["mega", "wavefront"])
+def test_odd_image_sizes_bit_exact(capi, oracle, size, kernel):
+    """Sizes that are not multiples of the 16x8 (megakernel) / 64x8 (512-path wavefront) CTA tiles, down to one pixel: edge tiles,
+    idle lanes taking part in the wavefront's barriers, the display pass at the borders."""
+    from sail_b200.filters import lower_filter
+    W, H = size
+    scene, o, t, l, bounces = scene_tables(3, W, H)
+    _compare(capi, oracle, scene, o, t, l, W, H, [0, 1], bounces, kernel, 2, "config 3 at %dx%d" % size)
+    f = lower_filter(scene.filter)
+    with capi.Context(W, H) as ctx:
+        ctx.configure(max_bounces=bounces, kernel=kernel, filter_id=f["filter_id"], filter_gamma_c=f["gamma_c"], filter_radius=f["radius"],
+                      filter_weights=f["weights"])
+        ctx.upload_scene(o, t, l)
+        ctx.render_n([capi.make_frame(*frame_uniforms(scene, k, W, H)) for k in range(2)])
+        color, normal, position = ctx.read_accum(), ctx.read_aov(capi.AOV_NORMAL), ctx.read_aov(capi.AOV_POSITION)
+        g32, g8 = ctx.present(both=True)
+    r32, r8 = oracle.present(color, normal, position, f, as_u8=True)
+    assert bits_equal(g32, r32) and np.array_equal(g8, r8)
