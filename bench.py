@@ -321,7 +321,7 @@ def run_ours(args, rank, world, local_rank):
     r = Renderer((W, H), device=local_rank, group=group, shard=shard, band_rows=args.band_rows)
     ctx = r.ctx
     ctx.configure(max_bounces=bounces,
-                  kernel={"wavefront": capi.KERNEL_WAVEFRONT, "mega": capi.KERNEL_MEGA, "auto": capi.KERNEL_AUTO}[args.kernel],
+                  kernel={"wavefront": capi.KERNEL_WAVEFRONT, "mega": capi.KERNEL_MEGA, "auto": capi.KERNEL_AUTO, "queue": capi.KERNEL_QUEUE}[args.kernel],
                   specialise=capi.SPECIALISE_OFF if args.no_jit else capi.SPECIALISE_AUTO)
     r.update(scene)
     filters = []
@@ -507,7 +507,7 @@ def main():
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--kernel", default="auto", choices=["auto", "mega", "wavefront"])
+    ap.add_argument("--kernel", default="auto", choices=["auto", "mega", "wavefront", "queue"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-jit", action="store_true", help="ahead-of-time kernel variants only (no per-scene NVRTC build)")
     ap.add_argument("--workload", default="cornell", choices=sorted(WORKLOADS), help="cornell = the headline; others are extra")

@@ -69,7 +69,11 @@ enum {
 enum {
     SAIL_KERNEL_MEGA = 0,       /* one thread traces a whole path */
     SAIL_KERNEL_WAVEFRONT = 1,  /* per-bounce stages over ray queues regrouped by hit object, queues in shared memory */
-    SAIL_KERNEL_AUTO = 2        /* default: chosen from the scene's content by the measured policy of DESIGN.md 4.2 */
+    SAIL_KERNEL_AUTO = 2,       /* default: chosen from the scene's content by the measured policy of DESIGN.md 4.2 */
+    SAIL_KERNEL_QUEUE = 3       /* wavefront with its ray queues in device memory: raygen / scan / sort / shade / accumulate as separate
+                                   kernels over batches of up to 4 M paths regrouped globally by hit object (sail_queue.cuh).  Exists
+                                   as a scene-specialised build only, for contexts that render whole images; otherwise the
+                                   shared-memory wavefront runs (sail_kernel_info() says so). */
 };
 
 enum {

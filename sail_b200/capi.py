@@ -16,7 +16,7 @@ LIB_PATH = os.environ.get("SAIL_B200_LIB") or os.path.join(_HERE, "libsail_b200.
 MAX_FRAMES_PER_CALL = 32
 AOV_COLOR, AOV_NORMAL, AOV_POSITION, AOV_HIT_ID, AOV_DEPTH = range(5)
 ACCUM_MEAN, ACCUM_SUM = 0, 1
-KERNEL_MEGA, KERNEL_WAVEFRONT, KERNEL_AUTO = 0, 1, 2
+KERNEL_MEGA, KERNEL_WAVEFRONT, KERNEL_AUTO, KERNEL_QUEUE = 0, 1, 2, 3
 SPECIALISE_AUTO, SPECIALISE_OFF, SPECIALISE_REQUIRE = 0, 1, 2
 ERR_CUDA, ERR_INVALID, ERR_STATE, ERR_NOMEM = -1, -2, -3, -4
 SHARD_NONE, SHARD_SAMPLE, SHARD_TILE = 0, 1, 2

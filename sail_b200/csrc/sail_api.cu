@@ -28,6 +28,7 @@
 #include "sail_jit.h"
 #include "sail_mega.cuh"
 #include "sail_present.cuh"
+#include "sail_queue.cuh"
 
 static_assert(SAIL_COMBINE_MAX == SAIL_MAX_DEVICES, "sail_combine.cuh and sail_b200.h disagree on the group size");
 
@@ -42,8 +43,14 @@ struct SailMember {
     int* hitId = nullptr;
     bool timed = false;
     // the scene-specialised kernels loaded on this device: [kind 0 mega, 1 wavefront][variant: bit 0 = RNG sine for |arg| < 2^22 only, bit 1 = with Russian roulette]
-    void* jitFn[2][4] = {{nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr}};
-    unsigned jitBlock[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
+    void* jitFn[3][4] = {};
+    unsigned jitBlock[3][4] = {};
+    void* jitStage[4][5] = {};  // kind 2 (queue wavefront): the five stage kernels per variant
+    // queue wavefront (sail_queue.cuh): path state, permutation, counters for one batch; allocated at first use
+    float4* qState = nullptr;
+    int* qPerm = nullptr;
+    int* qCounters = nullptr;
+    size_t qCapacity = 0;  // paths
     sailNcclComm_t comm = nullptr;
 };
 
@@ -77,9 +84,9 @@ struct sail_ctx {
     SailSceneBlock hostScene;
     uint64_t launches = 0;
     // scene-specialised kernels (sail_jit.cpp): requested per kernel kind after an upload, compiled on a worker thread
-    SailJitJob* jitJob[2][4];
-    bool jitRequested[2][4], jitFailed[2][4];
-    char jitNote[2][4][320];
+    SailJitJob* jitJob[3][4];
+    bool jitRequested[3][4], jitFailed[3][4];
+    char jitNote[3][4][320];
     char kernelInfo[400];
     char err[512];
     sail_ctx() {
@@ -449,6 +456,11 @@ void fillPresentParams(sail_ctx* ctx, PresentParams& P, const float* color) {
 // (512 paths per CTA when compiled at run time) pays where the scene has many shape codes (quadrics); among the
 // ahead-of-time variants also where it has many BSDFs (metal / glass).
 int kernelKind(const sail_ctx* ctx, int F, bool jit) {
+    if (ctx->cfg.kernel == SAIL_KERNEL_QUEUE) {
+        // whole images only (its batches are runs of consecutive pixels), scene-specialised only; else the shared-memory wavefront
+        const bool whole = ctx->y0 == 0 && ctx->y1 == ctx->H && ctx->bandStride <= 1 && !(ctx->grouped() && ctx->shardMode == SAIL_SHARD_TILE);
+        return (jit && whole && ctx->cfg.max_bounces <= SAIL_Q_MAX_BOUNCES && ctx->cfg.max_bounces >= 1) ? 2 : 1;
+    }
     if (ctx->cfg.kernel == SAIL_KERNEL_WAVEFRONT) return 1;
     if (ctx->cfg.kernel == SAIL_KERNEL_MEGA) return 0;
     if (jit) return (F & SAIL_F_QUADRICS) ? 1 : 0;
@@ -490,6 +502,7 @@ bool specialisedReady(sail_ctx* ctx, int kind, int small, int F, bool wait) {
         if (rc == 0) {
             m.jitFn[kind][small] = k.fn;
             m.jitBlock[kind][small] = k.block;
+            if (kind == 2) for (int st = 0; st < 5; st++) m.jitStage[small][st] = k.stage[st];
             snprintf(note, noteLen, "%s", k.info);
         } else if (rc < 0) {
             ctx->jitFailed[kind][small] = true;
@@ -513,6 +526,56 @@ bool rngArgsSmall(const sail_ctx* ctx, const sail_frame* frames, int count) {
     const double ax = (double)ctx->W + seed, ay = (double)ctx->H + seed, az = 0.5 + seed;
     const double d1 = ax * 12.9898 + ay * 78.233 + az * 151.7182, d2 = ax * 63.7264 + ay * 10.873 + az * 623.6736;
     return (d1 > d2 ? d1 : d2) * 1.001 < 4194304.0;
+}
+
+// One sail_render_n() share of a member through the queue wavefront: batches of consecutive pixels x all frames of the call.
+int launchQueue(sail_ctx* ctx, SailMember& m, int small, const SailFrameDev* frames, int nframes, int accumMode) {
+    const size_t npixTotal = npix(ctx);
+    const size_t maxPaths = (size_t)1 << 22;
+    if (!m.qState) {
+        size_t cap = npixTotal * SAIL_MAX_BATCH;
+        if (cap > maxPaths) cap = maxPaths;
+        if (cap < 1024) cap = 1024;
+        CU(cudaMalloc(&m.qState, cap * 4 * sizeof(float4)));
+        CU(cudaMalloc(&m.qPerm, cap * sizeof(int)));
+        CU(cudaMalloc(&m.qCounters, (SAIL_Q_MAX_BOUNCES + 1) * 2 * SAIL_Q_CLASSES * sizeof(int)));
+        m.qCapacity = cap;
+    }
+    size_t chunk = m.qCapacity / (size_t)nframes;
+    if (chunk >= 32) chunk &= ~(size_t)31;
+    if (chunk < 1) return setErr(ctx, SAIL_ERR_NOMEM, "queue wavefront: batch too small");
+    SailQLaunch Q;
+    Q.W = ctx->W; Q.H = ctx->H;
+    Q.nframes = nframes; Q.maxBounces = ctx->cfg.max_bounces; Q.rrStart = ctx->cfg.rr_start_bounce; Q.accumMode = accumMode;
+    Q.pad0 = 0;
+    Q.rcpW = dm_rcp((float)ctx->W); Q.rcpH = dm_rcp((float)ctx->H);
+    Q.accum = m.accum; Q.scene = m.dScene; Q.state = m.qState; Q.perm = m.qPerm; Q.counters = m.qCounters;
+    memcpy(Q.frames, frames, (size_t)nframes * sizeof(SailFrameDev));
+    const unsigned smem = (unsigned)sailSceneSmemBytes(ctx->hostScene.n, ctx->hostScene.ln);
+    char why[200];
+    for (size_t pix0 = 0; pix0 < npixTotal; pix0 += chunk) {
+        Q.pix0 = (int)pix0;
+        Q.npix = (int)(npixTotal - pix0 < chunk ? npixTotal - pix0 : chunk);
+        const unsigned pathBlocks = (unsigned)(((size_t)Q.npix * nframes + SAIL_Q_THREADS - 1) / SAIL_Q_THREADS);
+        const unsigned pixBlocks = (unsigned)((Q.npix + SAIL_Q_THREADS - 1) / SAIL_Q_THREADS);
+#define QSTAGE(st, blocks, sm)                                                                                                       \
+    do {                                                                                                                             \
+        if (sail_jit_launch(m.jitStage[small][st], &Q, blocks, 1, SAIL_Q_THREADS, sm, m.stream, why, sizeof(why)) != 0)              \
+            return setErr(ctx, SAIL_ERR_CUDA, "%s", why);                                                                            \
+        ctx->launches++;                                                                                                             \
+    } while (0)
+        Q.bounce = 0;
+        QSTAGE(0, pathBlocks, 0);
+        for (int d = 1; d <= Q.maxBounces; d++) {
+            Q.bounce = d;
+            QSTAGE(1, pathBlocks, smem);
+            if (d > 1) QSTAGE(2, pathBlocks, 0);
+            QSTAGE(3, pathBlocks, smem);
+        }
+        QSTAGE(4, pixBlocks, 0);
+#undef QSTAGE
+    }
+    return SAIL_OK;
 }
 
 }  // namespace
@@ -635,6 +698,7 @@ void sail_destroy(sail_ctx* ctx) {
         cudaSetDevice(m.device);
         if (m.comm && sail_nccl()->ok) sail_nccl()->commDestroy(m.comm);
         cudaFree(m.dScene); cudaFree(m.accum); cudaFree(m.normal); cudaFree(m.position); cudaFree(m.depth); cudaFree(m.hitId);
+        cudaFree(m.qState); cudaFree(m.qPerm); cudaFree(m.qCounters);
         if (m.evStart) cudaEventDestroy(m.evStart);
         if (m.evStop) cudaEventDestroy(m.evStop);
         if (m.evDone) cudaEventDestroy(m.evDone);
@@ -711,7 +775,7 @@ int sail_configure(sail_ctx* ctx, const sail_config* cfg) {
     if (cfg->max_bounces < 0 || cfg->max_bounces > 1024) return setErr(ctx, SAIL_ERR_INVALID, "max_bounces %d out of range", cfg->max_bounces);
     if (cfg->filter_id < 0 || cfg->filter_id > SAIL_FILTER_TONEMAPPING) return setErr(ctx, SAIL_ERR_INVALID, "unknown filter id %d", cfg->filter_id);
     if (cfg->accum_mode != SAIL_ACCUM_MEAN && cfg->accum_mode != SAIL_ACCUM_SUM) return setErr(ctx, SAIL_ERR_INVALID, "unknown accum_mode %d", cfg->accum_mode);
-    if (cfg->kernel < SAIL_KERNEL_MEGA || cfg->kernel > SAIL_KERNEL_AUTO) return setErr(ctx, SAIL_ERR_INVALID, "unknown kernel %d", cfg->kernel);
+    if (cfg->kernel < SAIL_KERNEL_MEGA || cfg->kernel > SAIL_KERNEL_QUEUE) return setErr(ctx, SAIL_ERR_INVALID, "unknown kernel %d", cfg->kernel);
     if (cfg->rr_start_bounce < 0 || cfg->rr_start_bounce > 1024) return setErr(ctx, SAIL_ERR_INVALID, "rr_start_bounce %d out of range", cfg->rr_start_bounce);
     if (cfg->specialise < SAIL_SPECIALISE_AUTO || cfg->specialise > SAIL_SPECIALISE_REQUIRE) return setErr(ctx, SAIL_ERR_INVALID, "unknown specialise mode %d", cfg->specialise);
     if (cfg->max_bounces != ctx->cfg.max_bounces) {  // the pending AOVs are those of the old setting (max_bounces < 1: no hit at all)
@@ -769,7 +833,7 @@ int sail_scene_features(const float* objects, int32_t n, const float* texparams,
 
 int sail_jit_compile_check(const float* objects, int32_t n, const float* texparams, int32_t tn, const float* lights, int32_t ln,
                            int32_t kernel, char* info, int32_t infolen) {
-    if (kernel != SAIL_KERNEL_MEGA && kernel != SAIL_KERNEL_WAVEFRONT) return SAIL_ERR_INVALID;
+    if (kernel != SAIL_KERNEL_MEGA && kernel != SAIL_KERNEL_WAVEFRONT && kernel != SAIL_KERNEL_QUEUE) return SAIL_ERR_INVALID;
     SailSceneBlock* blk = new (std::nothrow) SailSceneBlock;
     if (!blk) return SAIL_ERR_NOMEM;
     int rc = sail_pack_scene(objects, n, texparams, tn, lights, ln, blk, info, infolen);
@@ -778,7 +842,7 @@ int sail_jit_compile_check(const float* objects, int32_t n, const float* texpara
         char why[400];
         why[0] = 0;
         const int F = blk->features & SAIL_F_ALL;
-        SailJitJob* job = sail_jit_request(kernel == SAIL_KERNEL_WAVEFRONT ? 1 : 0, F, SAIL_MIN_CTAS(F), 1, blk, why, sizeof(why));
+        SailJitJob* job = sail_jit_request(kernel == SAIL_KERNEL_QUEUE ? 2 : (kernel == SAIL_KERNEL_WAVEFRONT ? 1 : 0), F, SAIL_MIN_CTAS(F), 1, blk, why, sizeof(why));
         // SAIL_B200_JIT_CHECK_NOWAIT=1 (tests): only start the compilation, to exercise a host that exits while NVRTC is working
         const char* nowait = getenv("SAIL_B200_JIT_CHECK_NOWAIT");
         if (job && nowait && nowait[0] == '1') {
@@ -847,7 +911,7 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
         if (jit) snprintf(ctx->kernelInfo, sizeof(ctx->kernelInfo), "%s", ctx->jitNote[kind][small]);
         else {
             const char* note = ctx->jitNote[kind][small];
-            kind = kernelKind(ctx, F, false);  // the ahead-of-time variants have their own measured policy
+            kind = kernelKind(ctx, F, false);  // the ahead-of-time variants have their own measured policy (no queue build among them)
             snprintf(ctx->kernelInfo, sizeof(ctx->kernelInfo), "aot %s<F=%d> (%s)", kind ? "wavefront" : "mega", F, note);
         }
     } else {
@@ -885,7 +949,10 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
         CU(cudaEventRecord(m.evStart, m.stream));
         if (L.nframes > 0 && tileRows > 0) {
             dim3 grid((ctx->W + SAIL_TILE_W - 1) / SAIL_TILE_W, tileRows);
-            if (jit) {
+            if (jit && kind == 2) {
+                int qrc = launchQueue(ctx, m, small, L.frames, L.nframes, L.accumMode);
+                if (qrc) return qrc;
+            } else if (jit) {
                 char why[200];
                 unsigned gx = grid.x;
                 if (kind == 1) gx = ((unsigned)ctx->W + m.jitBlock[1][small] / 8u - 1u) / (m.jitBlock[1][small] / 8u);  // tile = (threads / 8) x 8
@@ -893,7 +960,7 @@ int sail_render_n(sail_ctx* ctx, const sail_frame* frames, int32_t count) {
                     return setErr(ctx, SAIL_ERR_CUDA, "%s", why);
             } else if (kind == 1) CU(launchWave(F, L, grid, m.stream));
             else CU(launchMega(F, L, grid, m.stream));
-            ctx->launches++;
+            if (!(jit && kind == 2)) ctx->launches++;
         }
         CU(cudaEventRecord(m.evStop, m.stream));
         m.timed = true;

@@ -138,6 +138,7 @@ struct SailJitJob {
     std::vector<char> cubin;
     double secs = 0.0;
     std::map<int, void*> fn;  // device -> CUfunction (guarded by g_mutex)
+    std::map<int, void* [5]> stage;  // kind 2: device -> the five stage kernels
 };
 
 namespace {
@@ -158,7 +159,7 @@ Registry& registry() {
 int makePlan(int kind, int F, int minCtas, int rngSmall, const SailSceneBlock* scene, Plan* plan, char* err, int errlen) {
     const int n = scene->n;
     if (n < 1) { setErr(err, errlen, "empty scene"); return 2; }
-    if (kind != 0 && kind != 1) { setErr(err, errlen, "unknown kernel kind"); return 2; }
+    if (kind < 0 || kind > 2) { setErr(err, errlen, "unknown kernel kind"); return 2; }
     // runs of equal shape category in slot order
     std::string cats, runCat, runStart, runLen;
     int nruns = 0;
@@ -233,7 +234,7 @@ int makePlan(int kind, int F, int minCtas, int rngSmall, const SailSceneBlock* s
     }
     char head[96];
     if (kind == 1 && block != 128) snprintf(head, sizeof(head), "jit wavefront<F=%d,%u paths> n=%d shapes=", F, block, n);
-    else snprintf(head, sizeof(head), "jit %s<F=%d> n=%d shapes=", kind ? "wavefront" : "mega", F, n);
+    else snprintf(head, sizeof(head), "jit %s<F=%d> n=%d shapes=", kind == 2 ? "queue" : (kind ? "wavefront" : "mega"), F, n);
     // One shared sqrt instead of ~50 inlined copies: pays for quadric kernels that overflow the 32 KB instruction cache (megakernel,
     // 128-path wavefront: config 3 +5..16 %), costs 3.7 % once the 512-path wavefront has taken that pressure away (2318 vs 2404
     // Mpaths/s); metal/glass-only kernels are faster inlined.  SAIL_B200_INLINE_SQRT=0/1 overrides for A/B runs.
@@ -245,19 +246,28 @@ int makePlan(int kind, int F, int minCtas, int rngSmall, const SailSceneBlock* s
     if (!(F & 1 /* SAIL_F_QUADRICS */) && n <= 8) tuning += "#define SAIL_INLINE_SCAN 1\n";
     if (rngSmall & 1) tuning += "#define SAIL_RNG_SMALL_ARGS 1\n";
     tuning += (rngSmall & 2) ? "#define SAIL_JIT_RR 1\n" : "#define SAIL_JIT_RR 0\n";
-    char src[4096];
-    snprintf(src, sizeof(src),
+    char src[6144];
+    int len = snprintf(src, sizeof(src),
              "%s#define SAIL_JIT_NRUNS %d\n#define SAIL_JIT_RUN_CATS %s\n#define SAIL_JIT_RUN_STARTS %s\n#define SAIL_JIT_RUN_LENS %s\n"
              "#define SAIL_JIT_SHAPES 0x%xu\n#define SAIL_JIT_MATS 0x%xu\n#define SAIL_JIT_TEXS 0x%xu\n#define SAIL_JIT_LIGHTS 0x%xu\n"
              "#define SAIL_JIT_GLASS %u\n#define SAIL_JIT_MATTE %u\n#define SAIL_JIT_TR %u\n#define SAIL_JIT_LIGHT_SHAPES 0x%xu\n#define SAIL_WF_THREADS %u\n%s"
-             "#include \"sail_mega.cuh\"\n#include \"sail_wavefront.cuh\"\n"
-             "extern \"C\" __global__ void __launch_bounds__(%u, %d) sail_jit_kernel(const __grid_constant__ SailLaunch L) "
-             "{ %s<%d>(L); }\n",
+             "#include \"sail_mega.cuh\"\n#include \"sail_wavefront.cuh\"\n#include \"sail_queue.cuh\"\n",
              extraDefs.c_str(), nruns, runCat.c_str(), runStart.c_str(), runLen.c_str(), shapes, mats, texs, lights, glass, matte, tr, lightShapes,
              kind == 1 ? block : 128u,
              // kernels that are not instruction-cache bound also inline the sines of the RNG, the sampler's sincos and the sphere's
              // acos / sin (measured: config 2 +2.2 %, config 5 +2.9 %, config 3 +0.5 %)
-             tuning.c_str(), block, minCtas, kind ? "sailWaveBody" : "sailMegaBody", F);
+             tuning.c_str());
+    if (kind == 2) {  // one entry point per stage of sail_queue.cuh; each stage gets its own register budget
+        static const char* const stages[5] = {"Raygen", "Scan", "Scatter", "Shade", "Accumulate"};
+        for (int st = 0; st < 5; st++)
+            len += snprintf(src + len, sizeof(src) - (size_t)len,
+                            "extern \"C\" __global__ void __launch_bounds__(%u, %d) sail_jit_q%d(const __grid_constant__ SailQLaunch L) { sailQ%s<%d>(L); }\n",
+                            block, st == 3 ? minCtas : (st == 1 ? minCtas : 8), st, stages[st], F);
+    } else {
+        snprintf(src + len, sizeof(src) - (size_t)len,
+                 "extern \"C\" __global__ void __launch_bounds__(%u, %d) sail_jit_kernel(const __grid_constant__ SailLaunch L) { %s<%d>(L); }\n",
+                 block, minCtas, kind ? "sailWaveBody" : "sailMegaBody", F);
+    }
     plan->src = src;
     // The key is the generated source itself: whatever is baked into the kernel decides which cached kernel may be reused.
     plan->key = plan->src;
@@ -300,7 +310,7 @@ void compileJob(SailJitJob* job) {
     const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     if (rc == 0)
         if (const char* dump = getenv("SAIL_B200_JIT_DUMP")) {  // keep the cubin for cuobjdump / nvdisasm / tools/sass_lines.py
-            std::string name = std::string(dump) + "/sail_jit_" + (job->plan.kind ? "wave" : "mega") + "_F" + std::to_string(job->plan.F) + "_n" + std::to_string(job->plan.n) + ".cubin";
+            std::string name = std::string(dump) + "/sail_jit_" + (job->plan.kind == 2 ? "queue" : (job->plan.kind ? "wave" : "mega")) + "_F" + std::to_string(job->plan.F) + "_n" + std::to_string(job->plan.n) + ".cubin";
             if (FILE* f = fopen(name.c_str(), "wb")) { fwrite(cubin.data(), 1, cubin.size(), f); fclose(f); }
         }
     {
@@ -367,7 +377,14 @@ int sail_jit_poll(SailJitJob* job, int device, int wait, SailJitKernel* out, cha
     if (it == job->fn.end()) {
         void *mod = nullptr, *fn = nullptr;
         int cr = g_api.moduleLoadData(&mod, job->cubin.data());
-        if (cr == 0) cr = g_api.moduleGetFunction(&fn, mod, "sail_jit_kernel");
+        if (cr == 0 && p.kind == 2) {
+            for (int st = 0; st < 5 && cr == 0; st++) {
+                char name[32];
+                snprintf(name, sizeof(name), "sail_jit_q%d", st);
+                cr = g_api.moduleGetFunction(&job->stage[device][st], mod, name);
+            }
+            fn = job->stage[device][0];
+        } else if (cr == 0) cr = g_api.moduleGetFunction(&fn, mod, "sail_jit_kernel");
         // A 512-path wavefront holds 45 KB of static shared memory (exchange slots); together with the scene block of a large
         // scene (up to 17 KB, dynamic) that passes the 48 KB a kernel gets without opting in.
         if (cr == 0 && p.block > 128) cr = g_api.funcSetAttribute(fn, 8 /* CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES */, (int)sizeof(SailSceneBlock));
@@ -380,6 +397,7 @@ int sail_jit_poll(SailJitJob* job, int device, int wait, SailJitKernel* out, cha
         it = job->fn.emplace(device, fn).first;
     }
     out->fn = it->second;
+    for (int st = 0; st < 5; st++) out->stage[st] = p.kind == 2 ? job->stage[device][st] : nullptr;
     snprintf(out->info, sizeof(out->info), "%s%s%s (nvrtc %d.%d, %.2f s)", p.head.c_str(), p.cats.c_str(), p.masks.c_str(), g_api.nvrtcMajor, g_api.nvrtcMinor, job->secs);
     return 0;
 }

@@ -9,6 +9,7 @@ struct SailJitKernel {
     void* fn;        // CUfunction (null after a compile-only request)
     char info[200];  // "jit mega<F=0> n=3 shapes=1,9,2 (nvrtc 12.9, 0.80 s)" or "... (cached)"
     unsigned block;  // threads per CTA the kernel was compiled for
+    void* stage[5];  // kind 2 (sail_queue.cuh): raygen, scan, scatter, shade, accumulate; fn = stage[0]
 };
 #define SAIL_JIT_WF_THREADS_DEFAULT 128  // paths per wavefront CTA of the run-time compiled kernel (SAIL_B200_WF_THREADS overrides)
 #define SAIL_JIT_CTA_THREADS 128u  // = SAIL_CTA_THREADS of sail_mega.cuh
@@ -16,7 +17,7 @@ struct SailJitKernel {
 // A compilation in flight or finished; lives for the process (cubins are cached per scene structure and shared by all devices).
 struct SailJitJob;
 
-// kind: 0 megakernel, 1 wavefront.  Starts (or finds) the NVRTC compilation of the kernel specialised for `scene`'s structure on a
+// kind: 0 megakernel, 1 shared-memory wavefront, 2 queue wavefront (five stage kernels in one module).  Starts (or finds) the NVRTC compilation of the kernel specialised for `scene`'s structure on a
 // worker thread and returns its job, or null with a message in `err` (NVRTC missing, scene not specialisable ...): the caller then
 // keeps using the ahead-of-time variant.  Never blocks on the compiler.
 // rngSmall bit 1: Russian roulette compiled in (sail_config.rr_start_bounce > 0).  rngSmall bit 0: the caller guarantees |argument| < 2^22 for every sine of the hash RNG (sail_shade.cuh sinPair), so the

@@ -53,7 +53,8 @@ def _compare(capi, oracle, scene, o, t, l, W, H, frames_k, bounces, kernel, spec
     return info
 
 
-@pytest.mark.parametrize("kernel,specialise", [(2, 2), (2, 1), (0, 2), (1, 2)], ids=["auto-jit", "auto-aot", "mega-jit", "wavefront-jit"])
+@pytest.mark.parametrize("kernel,specialise", [(2, 2), (2, 1), (0, 2), (1, 2), (3, 2)],
+                         ids=["auto-jit", "auto-aot", "mega-jit", "wavefront-jit", "queue-jit"])
 @pytest.mark.parametrize("cfg", [1, 2, 3, 4, 5])
 def test_full_size_frame_bit_exact(capi, oracle, cfg, kernel, specialise):
     """Frame k = 2 (non-zero jitter) of each BASELINE config at its stated size -- the kernel SAIL_KERNEL_AUTO picks as the
@@ -65,7 +66,7 @@ def test_full_size_frame_bit_exact(capi, oracle, cfg, kernel, specialise):
 
 
 @pytest.mark.parametrize("specialise", [2, 1], ids=["jit", "aot"])
-@pytest.mark.parametrize("kernel", [0, 1], ids=["mega", "wavefront"])
+@pytest.mark.parametrize("kernel", [0, 1, 3], ids=["mega", "wavefront", "queue"])
 @pytest.mark.parametrize("name", sorted(matrix_scenes.MATRIX))
 def test_plugin_matrix_bit_exact(capi, oracle, name, kernel, specialise):
     W, H = 96, 64
@@ -214,7 +215,7 @@ def test_specialisation_is_compiled_off_the_render_path(capi, oracle, monkeypatc
 
 
 @pytest.mark.parametrize("specialise", [2, 1], ids=["jit", "aot"])
-@pytest.mark.parametrize("kernel", [0, 1], ids=["mega", "wavefront"])
+@pytest.mark.parametrize("kernel", [0, 1, 3], ids=["mega", "wavefront", "queue"])
 @pytest.mark.parametrize("cfg,rr", [(1, 2), (2, 3), (3, 2), (5, 4)])
 def test_russian_roulette_bit_exact(capi, oracle, cfg, rr, kernel, specialise):
     """The opt-in Russian roulette (sail_config.rr_start_bounce; no counterpart in the reference, off by default): the kernels
@@ -297,7 +298,7 @@ def test_random_scenes_bit_exact(capi, oracle, seed):
 
 
 @pytest.mark.parametrize("size", [(1, 1), (37, 29), (130, 7), (8, 200)])
-@pytest.mark.parametrize("kernel", [0, 1], ids=["mega", "wavefront"])
+@pytest.mark.parametrize("kernel", [0, 1, 3], ids=["mega", "wavefront", "queue"])
 def test_odd_image_sizes_bit_exact(capi, oracle, size, kernel):
     """Sizes that are not multiples of the 16x8 (megakernel) / 64x8 (512-path wavefront) CTA tiles, down to one pixel: edge tiles,
     idle lanes taking part in the wavefront's barriers, the display pass at the borders."""

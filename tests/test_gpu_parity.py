@@ -45,12 +45,14 @@ def _render_both(capi, oracle, cfg, nframes, kernel=0, batch=False, specialise=0
 
 
 @pytest.mark.parametrize("specialise", [2, 1], ids=["jit", "aot"])
-@pytest.mark.parametrize("kernel", [0, 1], ids=["mega", "wavefront"])
+@pytest.mark.parametrize("kernel", [0, 1, 3], ids=["mega", "wavefront", "queue"])
 @pytest.mark.parametrize("cfg", [1, 2, 3, 5])
 def test_frames_bit_exact(capi, oracle, cfg, kernel, specialise):
     """Both kernels, each as the scene-specialised build (NVRTC at run time; REQUIRE fails loudly if that is not
     possible) and as the ahead-of-time variant, against the oracle."""
-    out, ref = _render_both(capi, oracle, cfg, 4, kernel=kernel, batch=(kernel == 1), specialise=specialise)
+    out, ref = _render_both(capi, oracle, cfg, 4, kernel=kernel, batch=(kernel != 0), specialise=specialise)
+    if kernel == 3 and specialise == 2:
+        assert out["kernel_info"].startswith("jit queue<"), out["kernel_info"]
     assert out["kernel_info"].startswith("jit " if specialise == 2 else "aot "), out["kernel_info"]
     assert np.array_equal(out["hit_id"], ref["hit_id"]), "primary hit ids differ"
     for name in ("depth", "normal", "position", "color"):
@@ -81,7 +83,7 @@ def _assert_same(out, ref, what):
         assert bits_equal(out[name], ref[name]), mismatch_report(out[name], ref[name], "%s %s" % (what, name))
 
 
-@pytest.mark.parametrize("kernel", [0, 1], ids=["mega", "wavefront"])
+@pytest.mark.parametrize("kernel", [0, 1, 3], ids=["mega", "wavefront", "queue"])
 @pytest.mark.parametrize("bounces", [1, 2, 3])
 @pytest.mark.parametrize("cfg", [1, 2])
 def test_short_paths_bit_exact(capi, oracle, cfg, bounces, kernel):
