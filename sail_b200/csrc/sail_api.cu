@@ -47,7 +47,9 @@ struct SailMember {
     unsigned jitBlock[3][4] = {};
     void* jitStage[4][5] = {};  // kind 2 (queue wavefront): the five stage kernels per variant
     // queue wavefront (sail_queue.cuh): path state, permutation, counters for one batch; allocated at first use
-    float4* qState = nullptr;
+    float4* qRay = nullptr;
+    float4* qCarry = nullptr;
+    int2* qHit = nullptr;
     int* qPerm = nullptr;
     int* qCounters = nullptr;
     size_t qCapacity = 0;  // paths
@@ -531,12 +533,18 @@ bool rngArgsSmall(const sail_ctx* ctx, const sail_frame* frames, int count) {
 // One sail_render_n() share of a member through the queue wavefront: batches of consecutive pixels x all frames of the call.
 int launchQueue(sail_ctx* ctx, SailMember& m, int small, const SailFrameDev* frames, int nframes, int accumMode) {
     const size_t npixTotal = npix(ctx);
-    const size_t maxPaths = (size_t)1 << 22;
-    if (!m.qState) {
+    size_t maxPaths = (size_t)1 << 22;
+    if (const char* e = getenv("SAIL_B200_QUEUE_PATHS")) {  // batch size sweep (paths per batch)
+        const long long v = atoll(e);
+        if (v >= 1024 && v <= ((long long)1 << 26)) maxPaths = (size_t)v;
+    }
+    if (!m.qRay) {
         size_t cap = npixTotal * SAIL_MAX_BATCH;
         if (cap > maxPaths) cap = maxPaths;
         if (cap < 1024) cap = 1024;
-        CU(cudaMalloc(&m.qState, cap * 4 * sizeof(float4)));
+        CU(cudaMalloc(&m.qRay, cap * 2 * sizeof(float4)));
+        CU(cudaMalloc(&m.qCarry, cap * 2 * sizeof(float4)));
+        CU(cudaMalloc(&m.qHit, cap * sizeof(int2)));
         CU(cudaMalloc(&m.qPerm, cap * sizeof(int)));
         CU(cudaMalloc(&m.qCounters, (SAIL_Q_MAX_BOUNCES + 1) * 2 * SAIL_Q_CLASSES * sizeof(int)));
         m.qCapacity = cap;
@@ -549,7 +557,7 @@ int launchQueue(sail_ctx* ctx, SailMember& m, int small, const SailFrameDev* fra
     Q.nframes = nframes; Q.maxBounces = ctx->cfg.max_bounces; Q.rrStart = ctx->cfg.rr_start_bounce; Q.accumMode = accumMode;
     Q.pad0 = 0;
     Q.rcpW = dm_rcp((float)ctx->W); Q.rcpH = dm_rcp((float)ctx->H);
-    Q.accum = m.accum; Q.scene = m.dScene; Q.state = m.qState; Q.perm = m.qPerm; Q.counters = m.qCounters;
+    Q.accum = m.accum; Q.scene = m.dScene; Q.ray = m.qRay; Q.carry = m.qCarry; Q.hit = m.qHit; Q.perm = m.qPerm; Q.counters = m.qCounters;
     memcpy(Q.frames, frames, (size_t)nframes * sizeof(SailFrameDev));
     const unsigned smem = (unsigned)sailSceneSmemBytes(ctx->hostScene.n, ctx->hostScene.ln);
     char why[200];
@@ -698,7 +706,7 @@ void sail_destroy(sail_ctx* ctx) {
         cudaSetDevice(m.device);
         if (m.comm && sail_nccl()->ok) sail_nccl()->commDestroy(m.comm);
         cudaFree(m.dScene); cudaFree(m.accum); cudaFree(m.normal); cudaFree(m.position); cudaFree(m.depth); cudaFree(m.hitId);
-        cudaFree(m.qState); cudaFree(m.qPerm); cudaFree(m.qCounters);
+        cudaFree(m.qRay); cudaFree(m.qCarry); cudaFree(m.qHit); cudaFree(m.qPerm); cudaFree(m.qCounters);
         if (m.evStart) cudaEventDestroy(m.evStart);
         if (m.evStop) cudaEventDestroy(m.evStop);
         if (m.evDone) cudaEventDestroy(m.evDone);

@@ -9,11 +9,12 @@
 // same object (one shape code, one material, one texture).
 //
 //   batch  = npix pixels x nframes frames of one sail_render_n() call; path p = k * npix + pixel (k = frame within the call)
-//   state  = 64 B per path, array of structures: ray origin / direction, throughput, radiance, hit distance, hit object
+//   state  = three arrays, one record per path: ray (32 B: origin, direction), carry (32 B: throughput, radiance), hit (8 B: distance,
+//            object or -1 = ended) -- split so that every stage reads whole 32-byte sectors of exactly what it needs
 //   stages = raygen | per bounce: scan (+ histogram of hit objects) -> scatter (counting sort -> permutation) -> shade | accumulate
 //
-// Queue traffic per path and bounce: scan reads 32 B and writes 8 B, scatter reads 4 B and writes 4 B, shade reads 4 + 64 B and
-// writes 56 B = 172 B.  A path is an independent computation (the hash RNG is keyed by pixel, frame time and bounce), so which thread
+// Queue traffic per path and bounce: scan reads 40 B and writes 8 B, scatter reads 8 B and writes 4 B, shade reads 4 + 72 B and
+// writes 64 (+ 8) B = 200 B.  A path is an independent computation (the hash RNG is keyed by pixel, frame time and bounce), so which thread
 // evaluates it changes no bit: the output equals the megakernel's and the oracle's exactly.
 #ifndef SAIL_QUEUE_CUH
 #define SAIL_QUEUE_CUH
@@ -32,7 +33,9 @@ struct SailQLaunch {
     float rcpW, rcpH;
     float* accum;                 // W*H*3
     const SailSceneBlock* scene;
-    float4* state;                // [npix * nframes][4]: {o.xyz, d.x} {d.yz, fpdf.xy} {fpdf.z, e.xyz} {t, id, -, -}
+    float4* ray;                  // [npix * nframes][2]: {o.xyz, d.x} {d.yz, -, -}
+    float4* carry;                // [npix * nframes][2]: {fpdf.xyz, e.x} {e.yz, -, -}
+    int2* hit;                    // [npix * nframes]: {float bits of t, object id or -1 = the path has ended}
     int* perm;                    // [npix * nframes] paths in shade order (regrouped by hit object)
     int* counters;                // [SAIL_Q_MAX_BOUNCES + 1][2][SAIL_Q_CLASSES]: histogram and scatter cursors per bounce
     SailFrameDev frames[SAIL_MAX_BATCH];
@@ -53,11 +56,11 @@ SD void sailQRaygen(const SailQLaunch& L) {
     const SailFrameDev& f = L.frames[k];  // k is uniform across a warp (npix is a multiple of 32)
     const float fx = (float)x + 0.5f, fy = (float)y + 0.5f;
     const V3 d = primaryDir(f, fx * L.rcpW, fy * L.rcpH);
-    float4* s = L.state + 4 * (size_t)p;
-    s[0] = make_float4(f.eye[0], f.eye[1], f.eye[2], d.x);
-    s[1] = make_float4(d.y, d.z, 1.0f, 1.0f);
-    s[2] = make_float4(1.0f, 0.0f, 0.0f, 0.0f);
-    s[3] = make_float4(SAIL_MAX_DISTANCE, __int_as_float(0), 0.0f, 0.0f);  // id >= 0: alive
+    L.ray[2 * (size_t)p] = make_float4(f.eye[0], f.eye[1], f.eye[2], d.x);
+    L.ray[2 * (size_t)p + 1] = make_float4(d.y, d.z, 0.0f, 0.0f);
+    L.carry[2 * (size_t)p] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+    L.carry[2 * (size_t)p + 1] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    L.hit[p] = make_int2(__float_as_int(SAIL_MAX_DISTANCE), 0);  // id >= 0: alive
 }
 
 // ---- stage 1: nearest-hit scan over the batch + histogram of the hit objects (shader.shape.js:28-37) --------------------------------
@@ -71,10 +74,8 @@ SD void sailQScan(const SailQLaunch& L) {
     const bool inRange = p < L.npix * L.nframes;
     int key = sc.n;  // ended
     if (inRange) {
-        float4* s = L.state + 4 * (size_t)p;
-        const float4 s3 = s[3];
-        if (__float_as_int(s3.y) >= 0) {  // still alive
-            const float4 s0 = s[0], s1 = s[1];
+        if (L.hit[p].y >= 0) {  // still alive
+            const float4 s0 = L.ray[2 * (size_t)p], s1 = L.ray[2 * (size_t)p + 1];
             Ray ray;
             ray.o = mk3(s0.x, s0.y, s0.z);
             ray.d = mk3(s0.w, s1.x, s1.y);
@@ -82,7 +83,7 @@ SD void sailQScan(const SailQLaunch& L) {
             bool alive = nr.id >= 0;  // path.glsl:22 `break`
             // last bounce on an object that neither emits nor gets NEE: adds +0 to e (see tracePath()), the path is done
             if (alive && SAIL_IS_LAST_BOUNCE(L.bounce, L.maxBounces) && !lastBounceNeedsRecord<F>(sc.shape[nr.id])) alive = false;
-            s[3] = make_float4(nr.t, __int_as_float(alive ? nr.id : -1), 0.0f, 0.0f);
+            L.hit[p] = make_int2(__float_as_int(nr.t), alive ? nr.id : -1);
             if (alive) key = nr.id;
         }
     }
@@ -113,7 +114,7 @@ SD void sailQScatter(const SailQLaunch& L) {
     const bool inRange = p < L.npix * L.nframes;
     const unsigned active = __ballot_sync(0xffffffffu, inRange);
     if (!inRange) return;
-    const int id = __float_as_int(L.state[4 * (size_t)p + 3].y);
+    const int id = L.hit[p].y;
     const int key = id >= 0 ? id : n;
     const unsigned peers = __match_any_sync(active, key);
     const int lane = threadIdx.x & 31, leader = __ffs(peers) - 1;
@@ -131,20 +132,20 @@ SD void sailQShade(const SailQLaunch& L) {
     if (j >= L.npix * L.nframes) return;
     // primary rays are coherent in pixel order already; later bounces run in the order of the counting sort
     const int p = L.bounce > 1 ? L.perm[j] : j;
-    float4* s = L.state + 4 * (size_t)p;
-    const float4 s3 = s[3];
-    const int id = __float_as_int(s3.y);
+    const int2 hit = L.hit[p];
+    const int id = hit.y;
     if (id < 0) return;  // ended paths sort to the end: whole warps leave here
-    const float4 s0 = s[0], s1 = s[1], s2 = s[2];
+    const float4 s0 = L.ray[2 * (size_t)p], s1 = L.ray[2 * (size_t)p + 1];
+    const float4 c0 = L.carry[2 * (size_t)p], c1 = L.carry[2 * (size_t)p + 1];
     Ray ray;
     ray.o = mk3(s0.x, s0.y, s0.z);
     ray.d = mk3(s0.w, s1.x, s1.y);
-    V3 fpdf = mk3(s1.z, s1.w, s2.x), e = mk3(s2.y, s2.z, s2.w);
+    V3 fpdf = mk3(c0.x, c0.y, c0.z), e = mk3(c0.w, c1.x, c1.y);
     const int k = p / L.npix, pix = L.pix0 + (p - k * L.npix);
     const int y = pix / L.W, x = pix - y * L.W;
     const float fx = (float)x + 0.5f, fy = (float)y + 0.5f;
     Hit h;
-    hitRecord<F>(sc, id, s3.x, ray, h);
+    hitRecord<F>(sc, id, __int_as_float(hit.x), ray, h);
     bool alive = true;
     if (SAIL_IS_LAST_BOUNCE(L.bounce, L.maxBounces) && lastBounceIsEmissionOnly<F>(h)) {  // see tracePath(): dead BSDF sample
         e = e + (h.emission + splat3(0.0f)) * fpdf;
@@ -162,10 +163,14 @@ SD void sailQShade(const SailQLaunch& L) {
         ray.d = wi;
     }
     if (L.bounce >= L.maxBounces) alive = false;
-    s[0] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.d.x);
-    s[1] = make_float4(ray.d.y, ray.d.z, fpdf.x, fpdf.y);
-    s[2] = make_float4(fpdf.z, e.x, e.y, e.z);
-    if (!alive) s[3] = make_float4(s3.x, __int_as_float(-1), 0.0f, 0.0f);
+    if (alive) {
+        L.ray[2 * (size_t)p] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.d.x);
+        L.ray[2 * (size_t)p + 1] = make_float4(ray.d.y, ray.d.z, 0.0f, 0.0f);
+    } else {
+        L.hit[p] = make_int2(hit.x, -1);
+    }
+    L.carry[2 * (size_t)p] = make_float4(fpdf.x, fpdf.y, fpdf.z, e.x);
+    L.carry[2 * (size_t)p + 1] = make_float4(e.y, e.z, 0.0f, 0.0f);
 }
 
 // ---- stage 4: progressive accumulation of the batch's frames, in frame order (fstrace.glsl:13-14) ---------------------------------
@@ -176,8 +181,9 @@ SD void sailQAccumulate(const SailQLaunch& L) {
     const size_t pix = (size_t)L.pix0 + i;
     V3 c = mk3(L.accum[3 * pix], L.accum[3 * pix + 1], L.accum[3 * pix + 2]);
     for (int k = 0; k < L.nframes; k++) {
-        const float4 s2 = L.state[4 * ((size_t)k * L.npix + i) + 2];
-        const V3 e = mk3(nanToZero(s2.y), nanToZero(s2.z), nanToZero(s2.w));
+        const size_t p = (size_t)k * L.npix + i;
+        const float4 c0 = L.carry[2 * p], c1 = L.carry[2 * p + 1];
+        const V3 e = mk3(nanToZero(c0.w), nanToZero(c1.x), nanToZero(c1.y));
         if (L.accumMode == 0) c = mix3(e, c, L.frames[k].textureWeight);
         else c = c + e;
     }
