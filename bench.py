@@ -291,6 +291,54 @@ def sustained_leg(local_rank, peak_tops, min_seconds=2.0):
             "roofline_frac": paths_s * ops / 1e12 / peak_tops, "ops_per_path": ops, "clocks": clocks}
 
 
+def interactive_leg(local_rank, frames=600):
+    """BASELINE configs[0] the way the reference runs it (ui/ui.js:67-70): 512x512 Cornell box, ONE progressive sample per
+    ``Renderer.render(scene)`` call, display pass and read-back of the RGBA8 canvas every call.  Wall clock around ``frames``
+    calls, synchronous (each call returns its own image) and with the two-slot swapchain (``render_pipelined``); the third
+    figure leaves the Python host work (jitter + inverse MVP per frame) outside: the same C-ABI calls on prepared frames."""
+    from sail_b200 import configs
+    from sail_b200.renderer import Renderer
+    scene, W, H, _, bounces = configs.config1()
+    r = Renderer((W, H), device=local_rank)
+    r.ctx.configure(max_bounces=bounces)
+    r.update(scene)
+    r.render(scene)
+    r.ctx.specialise_wait()
+    for _ in range(20):
+        r.render(scene)
+    r.ctx.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(frames):
+        img = r.render(scene)
+    r.ctx.synchronize()
+    sync_s = time.perf_counter() - t0
+    assert img.shape == (H, W, 4)
+    for _ in range(4):
+        r.render_pipelined(scene)
+    r.flush()
+    t0 = time.perf_counter()
+    for _ in range(frames):
+        r.render_pipelined(scene)
+    img = r.flush()
+    r.ctx.synchronize()
+    pipe_s = time.perf_counter() - t0
+    assert img.shape == (H, W, 4)
+    prepared = [r.tracer.frames(scene.mat, scene.eye, scene.sampleCount + i, 1) for i in range(frames)]
+    t0 = time.perf_counter()
+    for fr in prepared:
+        r.ctx.render_n(fr)
+        img = r.ctx.present(as_u8=True, pinned=True)
+    r.ctx.synchronize()
+    cabi_s = time.perf_counter() - t0
+    used = r.ctx.kernel_info()
+    r.close()
+    return {"workload": "BASELINE configs[0]: Cornell box 512x512, 1 spp per Renderer.render() call + display pass + RGBA8 read-back",
+            "frames": frames, "frames_per_s": frames / sync_s, "ms_per_frame": sync_s / frames * 1e3,
+            "frames_per_s_pipelined": frames / pipe_s, "frames_per_s_c_abi_prepared_frames": frames / cabi_s,
+            "mpaths_per_s": frames * W * H / sync_s / 1e6, "d2h_bytes_per_frame": W * H * 4, "kernel_used": used,
+            "note": "the reference paces this loop with requestAnimationFrame (display refresh, typically 60 Hz)"}
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
 
@@ -479,6 +527,7 @@ def run_ours(args, rank, world, local_rank):
             line["cpu_baseline"] = cpu_baseline()
         if world == 1 and not args.no_cpu and _workload == "cornell":
             line["other_workloads"] = [other_workload(w, local_rank, peak) for w in ("config2", "config3", "config5")]
+            line["interactive"] = interactive_leg(local_rank)
             line["other_workloads"].append(sustained_leg(local_rank, peak))
             # The same workload with the last-bounce reductions compiled out (every bounce evaluated in full, as the
             # reference's loop does; identical image): how much of `value` is skipped dead work.
