@@ -79,6 +79,7 @@ struct sail_ctx {
     bool copyInFlight = false, copiedOnce = false;
     float* presentF32 = nullptr;
     unsigned char* presentU8 = nullptr;
+    float4* presentPad = nullptr;  // colour map padded to 16 B per texel for the window filters (sail_pad_rgb_kernel), W*H float4
     sail_config cfg;
     bool sceneLoaded = false;
     std::vector<float> texparams, lights;  // kept for sail_upload_objects (tracer.js:25-40 re-uses them)
@@ -712,7 +713,7 @@ void sail_destroy(sail_ctx* ctx) {
         if (m.evDone) cudaEventDestroy(m.evDone);
         if (m.evCombined) cudaEventDestroy(m.evCombined);
         if (i == 0) {
-            cudaFree(ctx->combined); cudaFree(ctx->presentF32); cudaFree(ctx->presentU8);
+            cudaFree(ctx->combined); cudaFree(ctx->presentF32); cudaFree(ctx->presentU8); cudaFree(ctx->presentPad);
             if (ctx->evPresented) cudaEventDestroy(ctx->evPresented);
             if (ctx->evCopied) cudaEventDestroy(ctx->evCopied);
             if (ctx->evConsumed) cudaEventDestroy(ctx->evConsumed);
@@ -1109,7 +1110,11 @@ int sail_present_begin(sail_ctx* ctx, uint8_t* rgba8) {
     P.out_u8 = ctx->presentU8;
     // the filter overwrites the device image: it must not overtake the previous copy (long finished in practice)
     if (ctx->copiedOnce) CU(cudaStreamWaitEvent(r.stream, ctx->evCopied, 0));
-    sailLaunchPresent(P, r.stream);
+    if (sailPresentWantsPadded(P.filter_id)) {
+        if (!ctx->presentPad) CU(cudaMalloc(&ctx->presentPad, n * sizeof(float4)));
+        ctx->launches++;  // sail_pad_rgb_kernel
+    }
+    sailLaunchPresent(P, ctx->presentPad, r.stream);
     ctx->launches++;
     CU(cudaGetLastError());
     CU(cudaEventRecord(ctx->evPresented, r.stream));
@@ -1149,7 +1154,11 @@ int sail_present(sail_ctx* ctx, float* rgba_f32, uint8_t* rgba8) {
     fillPresentParams(ctx, P, img);
     P.out_f32 = rgba_f32 ? ctx->presentF32 : nullptr;
     P.out_u8 = rgba8 ? ctx->presentU8 : nullptr;
-    sailLaunchPresent(P, r.stream);
+    if (sailPresentWantsPadded(P.filter_id)) {
+        if (!ctx->presentPad) CU(cudaMalloc(&ctx->presentPad, n * sizeof(float4)));
+        ctx->launches++;  // sail_pad_rgb_kernel
+    }
+    sailLaunchPresent(P, ctx->presentPad, r.stream);
     ctx->launches++;
     CU(cudaGetLastError());
     if ((rc = markConsumed(ctx)) != 0) return rc;

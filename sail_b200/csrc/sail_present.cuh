@@ -26,6 +26,7 @@ struct PresentParams {
     float radius[2];
     float weights[16];
     const float* color;
+    const float4* color4;  // the colour map padded to 16 bytes per texel (sail_pad_rgb_kernel): what the window filters fetch
     const float* normal;
     const float* position;
     float* out_f32;        // W*H*4 or NULL
@@ -78,15 +79,17 @@ SD AxisTap axisTap(float c, int size) {
     a.i1 = wrapIndex(i0 + 1, size);
     return a;
 }
-SD V3 texel3(const float* img, int W, int x, int y) {
-    const float* p = img + 3 * ((size_t)y * W + x);
-    return mk3(__ldg(p), __ldg(p + 1), __ldg(p + 2));
+// One 16-byte load per texel instead of three 4-byte loads 12 bytes apart: the 64 taps x 4 texels of a window filter are bound by
+// L1 wavefronts (a warp's 32 texels span three cache lines per scalar load), not by arithmetic.
+SD V3 texel3(const float4* img, int W, int x, int y) {
+    const float4 c = __ldg(img + ((size_t)y * W + x));
+    return mk3(c.x, c.y, c.z);
 }
 SD V3 windowTap(const PresentParams& P, const AxisTap& X, const AxisTap& Y, int& count) {
     if (!(X.ok && Y.ok)) return splat3(0.0f);
     count++;
-    const V3 c00 = texel3(P.color, P.W, X.i0, Y.i0), c10 = texel3(P.color, P.W, X.i1, Y.i0);
-    const V3 c01 = texel3(P.color, P.W, X.i0, Y.i1), c11 = texel3(P.color, P.W, X.i1, Y.i1);
+    const V3 c00 = texel3(P.color4, P.W, X.i0, Y.i0), c10 = texel3(P.color4, P.W, X.i1, Y.i0);
+    const V3 c01 = texel3(P.color4, P.W, X.i0, Y.i1), c11 = texel3(P.color4, P.W, X.i1, Y.i1);
     // textureLinear(): a = c00*(1-tx) + c10*tx, b = c01*(1-tx) + c11*tx, a*(1-ty) + b*ty, per channel, plain scalar operations
     const V3 a = mk3(c00.x * X.omt + c10.x * X.t, c00.y * X.omt + c10.y * X.t, c00.z * X.omt + c10.z * X.t);
     const V3 b = mk3(c01.x * X.omt + c11.x * X.t, c01.y * X.omt + c11.y * X.t, c01.z * X.omt + c11.z * X.t);
@@ -231,9 +234,23 @@ __global__ void __launch_bounds__(256) sail_present_kernel(const __grid_constant
     }
 }
 
+// RGB (12 bytes per texel, the accumulator's layout) -> RGB1 (16 bytes): the window filters' fetch format
+__global__ void __launch_bounds__(256) sail_pad_rgb_kernel(const float* __restrict__ rgb, float4* __restrict__ out, size_t n) {
+    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (i < n) out[i] = make_float4(rgb[3 * i], rgb[3 * i + 1], rgb[3 * i + 2], 1.0f);
+}
+
 #ifndef __CUDACC_RTC__
-static inline void sailLaunchPresent(const PresentParams& P, cudaStream_t stream) {
+static inline bool sailPresentWantsPadded(int filter_id) { return filter_id >= 2 && filter_id <= 6; }
+// `pad`: W*H float4 of scratch, required for the window filters (sailPresentWantsPadded), unused otherwise
+static inline void sailLaunchPresent(PresentParams P, float4* pad, cudaStream_t stream) {
     dim3 grid((P.W + 31) / 32, (P.H + 7) / 8);
+    P.color4 = nullptr;
+    if (sailPresentWantsPadded(P.filter_id)) {
+        const size_t n = (size_t)P.W * P.H;
+        sail_pad_rgb_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(P.color, pad, n);
+        P.color4 = pad;
+    }
     if (P.filter_id == 9) sail_present_kernel<2><<<grid, 256, 0, stream>>>(P);
     else if (P.filter_id >= 2 && P.filter_id <= 6) sail_present_kernel<1><<<grid, 256, 0, stream>>>(P);
     else sail_present_kernel<0><<<grid, 256, 0, stream>>>(P);
