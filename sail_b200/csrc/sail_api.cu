@@ -79,7 +79,8 @@ struct sail_ctx {
     bool copyInFlight = false, copiedOnce = false;
     float* presentF32 = nullptr;
     unsigned char* presentU8 = nullptr;
-    float4* presentPad = nullptr;  // colour map padded to 16 B per texel for the window filters (sail_pad_rgb_kernel), W*H float4
+    float4* presentPad = nullptr;   // colour map padded to 16 B per texel for the window filters and the wavelet (sail_pad_rgb_kernel), W*H float4
+    float4* presentPad2 = nullptr;  // position map likewise (wavelet)
     sail_config cfg;
     bool sceneLoaded = false;
     std::vector<float> texparams, lights;  // kept for sail_upload_objects (tracer.js:25-40 re-uses them)
@@ -713,7 +714,7 @@ void sail_destroy(sail_ctx* ctx) {
         if (m.evDone) cudaEventDestroy(m.evDone);
         if (m.evCombined) cudaEventDestroy(m.evCombined);
         if (i == 0) {
-            cudaFree(ctx->combined); cudaFree(ctx->presentF32); cudaFree(ctx->presentU8); cudaFree(ctx->presentPad);
+            cudaFree(ctx->combined); cudaFree(ctx->presentF32); cudaFree(ctx->presentU8); cudaFree(ctx->presentPad); cudaFree(ctx->presentPad2);
             if (ctx->evPresented) cudaEventDestroy(ctx->evPresented);
             if (ctx->evCopied) cudaEventDestroy(ctx->evCopied);
             if (ctx->evConsumed) cudaEventDestroy(ctx->evConsumed);
@@ -1114,7 +1115,11 @@ int sail_present_begin(sail_ctx* ctx, uint8_t* rgba8) {
         if (!ctx->presentPad) CU(cudaMalloc(&ctx->presentPad, n * sizeof(float4)));
         ctx->launches++;  // sail_pad_rgb_kernel
     }
-    sailLaunchPresent(P, ctx->presentPad, r.stream);
+    if (P.filter_id == 9) {  // wavelet: the position map as well
+        if (!ctx->presentPad2) CU(cudaMalloc(&ctx->presentPad2, n * sizeof(float4)));
+        ctx->launches++;
+    }
+    CU(sailLaunchPresent(P, ctx->presentPad, ctx->presentPad2, r.stream));
     ctx->launches++;
     CU(cudaGetLastError());
     CU(cudaEventRecord(ctx->evPresented, r.stream));
@@ -1158,7 +1163,11 @@ int sail_present(sail_ctx* ctx, float* rgba_f32, uint8_t* rgba8) {
         if (!ctx->presentPad) CU(cudaMalloc(&ctx->presentPad, n * sizeof(float4)));
         ctx->launches++;  // sail_pad_rgb_kernel
     }
-    sailLaunchPresent(P, ctx->presentPad, r.stream);
+    if (P.filter_id == 9) {  // wavelet: the position map as well
+        if (!ctx->presentPad2) CU(cudaMalloc(&ctx->presentPad2, n * sizeof(float4)));
+        ctx->launches++;
+    }
+    CU(sailLaunchPresent(P, ctx->presentPad, ctx->presentPad2, r.stream));
     ctx->launches++;
     CU(cudaGetLastError());
     if ((rc = markConsumed(ctx)) != 0) return rc;

@@ -26,7 +26,8 @@ struct PresentParams {
     float radius[2];
     float weights[16];
     const float* color;
-    const float4* color4;  // the colour map padded to 16 bytes per texel (sail_pad_rgb_kernel): what the window filters fetch
+    const float4* color4;     // the colour map padded to 16 bytes per texel (sail_pad_rgb_kernel): what the window filters and the wavelet fetch
+    const float4* position4;  // the position map likewise (wavelet only)
     const float* normal;
     const float* position;
     float* out_f32;        // W*H*4 or NULL
@@ -129,48 +130,102 @@ SD V4 filterWindow(const PresentParams& P, float tx, float ty) {
     V3 c = vdivs(color, weightSum);
     return mk4(c.x, c.y, c.z, 1.0f);
 }
-// wavelet.glsl:1-54
-SD V4 filterWavelet(const PresentParams& P, float tx, float ty) {
+// textureLinear() on prepared axis values (AxisTap: texel pair, wrap-around and 8-bit blend weight of one coordinate): the same
+// V4 expressions on the same texels; the colour map comes from the padded copy, the position map from its 12-byte layout.
+SD V4 bilinearOf(V4 c00, V4 c10, V4 c01, V4 c11, const AxisTap& X, const AxisTap& Y) {
+    V4 a = c00 * X.omt + c10 * X.t;
+    V4 b = c01 * X.omt + c11 * X.t;
+    return a * Y.omt + b * Y.t;
+}
+SD V4 texel4(const float4* img, int W, int x, int y) {
+    const float4 q = __ldg(img + ((size_t)y * W + x));
+    return mk4(q.x, q.y, q.z, 1.0f);
+}
+SD V4 texel4(const float* img, int W, int x, int y) {
+    const float* p = img + 3 * ((size_t)y * W + x);
+    return mk4(__ldg(p), __ldg(p + 1), __ldg(p + 2), 1.0f);
+}
+template <class Map>
+SD V4 bilinearAt(const Map* img, int W, const AxisTap& X, const AxisTap& Y) {
+    return bilinearOf(texel4(img, W, X.i0, Y.i0), texel4(img, W, X.i1, Y.i0), texel4(img, W, X.i0, Y.i1), texel4(img, W, X.i1, Y.i1), X, Y);
+}
+// wavelet.glsl:1-54.  The 5 x 5 tap positions do not depend on the level: their coordinates are set up once per axis value (10
+// per pixel; the literal loop sets up 45 taps x 2 maps x 2 axes, each with two integer modulos), both maps are fetched from
+// 16-byte-per-texel copies, and what levels 1 and 2 evaluate again for the taps they share with level 0 -- the fetched colour,
+// the colour and position weights, the squared colour distance -- is kept from level 0 in shared memory (6 floats for each of the
+// 13 taps with an even distance to the centre tap; level 2's 7 taps are among them).  Taps, weights, every expression and the
+// order of the sums are those of the shader: 25 + 13 + 7 accumulations, level by level.
+#define SAIL_WAVELET_CACHED_TAPS 13
+#define SAIL_WAVELET_SMEM_BYTES (SAIL_WAVELET_CACHED_TAPS * 6 * 256 * sizeof(float))
+#define SAIL_WAVELET_H(q) ((q) % 5 == 0 ? 0.375f : (((q) % 5 == 1 || (q) % 5 == 4) ? 0.25f : 0.0625f))  // h[q % 5], wavelet.glsl:23
+SD V4 filterWavelet(const PresentParams& P, float tx, float ty, float* cache) {
     V4 color = mk4(0.0f, 0.0f, 0.0f, 0.0f);
     float weightSum = 0.0f;
     V4 cval = textureLinear(P.color, P.W, P.H, tx, ty);
     V4 pval = textureLinear(P.position, P.W, P.H, tx, ty);
-    const float h[5] = {0.375f, 0.25f, 0.0625f, 0.0625f, 0.25f};
     const float Rx = P.radius[0], Ry = P.radius[1];
     const float Wf = (float)P.W, Hf = (float)P.H;
-    for (int n = 0; n < 3; n++) {
-        float stepwidth = (float)(1 << n) - 1.0f;
-        int step = toInt(stepwidth) + 1;
-        int count = 0;
-        for (int i = 0; i < 5; i++) {
-            for (int j = 0; j < 5; j++, count++) {
-                int delt = abs(count - 12);
-                float _h = 0.0f;
-                if (delt % step == 0) _h = h[(delt / step) % 5];
-                if (_h == 0.0f) continue;
-                float u = tx - fdiv(Rx, Wf) + fdiv(((float)j + 0.5f) * Rx, 2.5f * Wf);
-                float v = ty - fdiv(Ry, Hf) + fdiv(((float)i + 0.5f) * Ry, 2.5f * Hf);
-                // W(), wavelet.glsl:5-20: the "normal" weight reuses the colour difference as written
-                V4 ctmp = textureLinear(P.color, P.W, P.H, u, v);
-                V4 t = cval - ctmp;
-                float dist2 = dot4(t, t);
-                float c_w = fmin2(dm_exp(fdiv(-dist2, 4.0f)), 1.0f);
-                dist2 = fmax2(fdiv(dot4(t, t), stepwidth * stepwidth), 0.0f);
-                float n_w = fmin2(dm_exp(fdiv(-dist2, 128.0f)), 1.0f);
-                V4 ptmp = textureLinear(P.position, P.W, P.H, u, v);
-                t = pval - ptmp;
-                dist2 = dot4(t, t);
-                float p_w = fmin2(dm_exp(fdiv(-dist2, 1.0f)), 1.0f);
-                float weight = c_w * n_w * p_w * _h;
-                ctmp = ctmp * weight;
-                weightSum += weight;
-                color = color + ctmp;
+    AxisTap X[5], Y[5];
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+        X[k] = axisTap(tx - fdiv(Rx, Wf) + fdiv(((float)k + 0.5f) * Rx, 2.5f * Wf), P.W);
+        Y[k] = axisTap(ty - fdiv(Ry, Hf) + fdiv(((float)k + 0.5f) * Ry, 2.5f * Hf), P.H);
+    }
+    // ---- level 0: stepwidth 0, step 1, every tap ----
+    {
+        const float stepwidth = 0.0f;
+#pragma unroll
+        for (int count = 0; count < 25; count++) {
+            const int i = count / 5, j = count % 5;
+            const int delt = count > 12 ? count - 12 : 12 - count;
+            const float _h = SAIL_WAVELET_H(delt);
+            // W(), wavelet.glsl:5-20: the "normal" weight reuses the colour difference as written
+            V4 ctmp = bilinearAt(P.color4, P.W, X[j], Y[i]);
+            V4 t = cval - ctmp;
+            float dist2 = dot4(t, t);
+            const float d2c = dist2;
+            float c_w = fmin2(dm_exp(fdiv(-dist2, 4.0f)), 1.0f);
+            dist2 = fmax2(fdiv(d2c, stepwidth * stepwidth), 0.0f);
+            float n_w = fmin2(dm_exp(fdiv(-dist2, 128.0f)), 1.0f);
+            V4 ptmp = bilinearAt(P.position4, P.W, X[j], Y[i]);
+            t = pval - ptmp;
+            dist2 = dot4(t, t);
+            float p_w = fmin2(dm_exp(fdiv(-dist2, 1.0f)), 1.0f);
+            if ((count & 1) == 0) {  // delt even: levels 1 (and 2, delt % 4 == 0) take this tap again
+                float* c = cache + (count / 2) * 6 * 256;
+                c[0] = ctmp.x; c[256] = ctmp.y; c[512] = ctmp.z; c[768] = c_w; c[1024] = p_w; c[1280] = d2c;
             }
+            float weight = c_w * n_w * p_w * _h;
+            ctmp = ctmp * weight;
+            weightSum += weight;
+            color = color + ctmp;
+        }
+    }
+    // ---- levels 1 and 2: stepwidth 1 / 3, step 2 / 4 ----
+#pragma unroll 1
+    for (int n = 1; n < 3; n++) {
+        const float stepwidth = (float)(1 << n) - 1.0f;
+#pragma unroll
+        for (int count = 0; count < 25; count += 2) {
+            const int delt = count > 12 ? count - 12 : 12 - count;
+            if (delt & ((1 << n) - 1)) continue;  // uniform: delt % step != 0 -> _h = 0, the shader adds nothing
+            const float _h = n == 1 ? SAIL_WAVELET_H(delt / 2) : SAIL_WAVELET_H(delt / 4);
+            const float* c = cache + (count / 2) * 6 * 256;
+            // the bilinear fetch of a colour map whose texels carry w = 1 has w = omt + t = 1 exactly (t is a multiple of 1/256)
+            V4 ctmp = mk4(c[0], c[256], c[512], 1.0f);
+            const float c_w = c[768], p_w = c[1024], d2c = c[1280];
+            float dist2 = fmax2(fdiv(d2c, stepwidth * stepwidth), 0.0f);
+            float n_w = fmin2(dm_exp(fdiv(-dist2, 128.0f)), 1.0f);
+            float weight = c_w * n_w * p_w * _h;
+            ctmp = ctmp * weight;
+            weightSum += weight;
+            color = color + ctmp;
         }
     }
     float r = dm_rcp(weightSum);
     return mk4(color.x * r, color.y * r, color.z * r, color.w * r);
 }
+#undef SAIL_WAVELET_H
 // tonemapping.glsl:1-4
 SD float tonemap1(float c) {
     float x = fmax2(0.0f, c - 0.004f);
@@ -179,6 +234,7 @@ SD float tonemap1(float c) {
 
 // KIND: 0 = the point filters (color / gamma / tonemapping / normal / position), 1 = window filters, 2 = wavelet -- three
 // instantiations, so the 64-tap window filter's registers (112) do not set the occupancy of the one-fetch filters.
+extern __shared__ float4 sail_present_smem[];  // KIND 2: SAIL_WAVELET_SMEM_BYTES (the wavelet's tap cache)
 template <int KIND>
 __global__ void __launch_bounds__(256) sail_present_kernel(const __grid_constant__ PresentParams P) {
     int x = blockIdx.x * 32 + (threadIdx.x & 31);
@@ -214,7 +270,7 @@ __global__ void __launch_bounds__(256) sail_present_kernel(const __grid_constant
             v = mk4(c.x, c.y, c.z, 1.0f);
             break;
         }
-        case 9: if (KIND == 2) v = filterWavelet(P, tx, ty); break;
+        case 9: if (KIND == 2) v = filterWavelet(P, tx, ty, reinterpret_cast<float*>(sail_present_smem) + threadIdx.x); break;
         case 2: case 3: case 4: case 5: case 6: if (KIND == 1) v = filterWindow(P, tx, ty); break;
         default: v = mk4(0.0f, 0.0f, 0.0f, 0.0f);
     }
@@ -241,19 +297,28 @@ __global__ void __launch_bounds__(256) sail_pad_rgb_kernel(const float* __restri
 }
 
 #ifndef __CUDACC_RTC__
-static inline bool sailPresentWantsPadded(int filter_id) { return filter_id >= 2 && filter_id <= 6; }
-// `pad`: W*H float4 of scratch, required for the window filters (sailPresentWantsPadded), unused otherwise
-static inline void sailLaunchPresent(PresentParams P, float4* pad, cudaStream_t stream) {
+static inline bool sailPresentWantsPadded(int filter_id) { return (filter_id >= 2 && filter_id <= 6) || filter_id == 9; }
+// `pad`: W*H float4 of scratch, required for the window filters and the wavelet (sailPresentWantsPadded), unused otherwise;
+// `pad2`: the same again for the wavelet (its position map)
+static inline cudaError_t sailLaunchPresent(PresentParams P, float4* pad, float4* pad2, cudaStream_t stream) {
     dim3 grid((P.W + 31) / 32, (P.H + 7) / 8);
     P.color4 = nullptr;
+    P.position4 = nullptr;
+    const size_t n = (size_t)P.W * P.H;
     if (sailPresentWantsPadded(P.filter_id)) {
-        const size_t n = (size_t)P.W * P.H;
         sail_pad_rgb_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(P.color, pad, n);
         P.color4 = pad;
     }
-    if (P.filter_id == 9) sail_present_kernel<2><<<grid, 256, 0, stream>>>(P);
-    else if (P.filter_id >= 2 && P.filter_id <= 6) sail_present_kernel<1><<<grid, 256, 0, stream>>>(P);
+    if (P.filter_id == 9) {
+        // > 48 KB of dynamic shared memory is opt-in per device; the call is a table update, made on every launch
+        cudaError_t e = cudaFuncSetAttribute(sail_present_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SAIL_WAVELET_SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        sail_pad_rgb_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(P.position, pad2, n);
+        P.position4 = pad2;
+        sail_present_kernel<2><<<grid, 256, SAIL_WAVELET_SMEM_BYTES, stream>>>(P);
+    } else if (P.filter_id >= 2 && P.filter_id <= 6) sail_present_kernel<1><<<grid, 256, 0, stream>>>(P);
     else sail_present_kernel<0><<<grid, 256, 0, stream>>>(P);
+    return cudaSuccess;
 }
 #endif
 
