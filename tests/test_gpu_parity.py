@@ -247,7 +247,11 @@ def test_device_math_matches_host(capi, oracle):
 FILTERS = [("color", {}), ("gamma", {"c": "2.2"}), ("tonemapping", {}), ("normal", {}), ("position", {}),
            ("box", {"r": "vec2(2.0,2.0)"}), ("gaussian", {"r": "vec2(2.0,2.0)", "alpha": "2.0"}),
            ("sinc", {"r": "vec2(2.0,2.0)", "tau": "3.0"}), ("mitchell", {"r": "vec2(2.0,2.0)", "b": "0.3", "c": "0.3"}),
-           ("triangle", {"r": "vec2(1.5,2.5)"}), ("wavelet", {"r": "vec2(2.0,2.0)"})]
+           ("triangle", {"r": "vec2(1.5,2.5)"}), ("wavelet", {"r": "vec2(2.0,2.0)"}),
+           # taps far outside the image (REPEAT wrap-around several times over; the window filters' bounds test), degenerate and
+           # negative radii: the per-axis set-up and the tap cache must follow the shader there too
+           ("box", {"r": "vec2(150.5,90.5)"}), ("gaussian", {"r": "vec2(0.0,0.0)", "alpha": "2.0"}), ("sinc", {"r": "vec2(-3.5,7.5)", "tau": "3.0"}),
+           ("wavelet", {"r": "vec2(120.5,75.5)"}), ("wavelet", {"r": "vec2(0.0,0.0)"}), ("wavelet", {"r": "vec2(-2.5,0.5)"})]
 
 
 @pytest.mark.parametrize("name,params", FILTERS)
