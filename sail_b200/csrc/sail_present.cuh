@@ -235,8 +235,13 @@ SD float tonemap1(float c) {
 // KIND: 0 = the point filters (color / gamma / tonemapping / normal / position), 1 = window filters, 2 = wavelet -- three
 // instantiations, so the 64-tap window filter's registers (112) do not set the occupancy of the one-fetch filters.
 extern __shared__ float4 sail_present_smem[];  // KIND 2: SAIL_WAVELET_SMEM_BYTES (the wavelet's tap cache)
+// CTAs per SM the register allocation aims at.  Measured at 1080p (tools/ubench/present_win.cu): window filters 0.53 / 0.38 / 0.38 /
+// 0.42 ms at 1 / 2 / 3 / 4 (spills from 3 on), wavelet 0.73 / 0.73 / 0.76 / 0.84 ms (its 80 KB tap cache allows two anyway).
+#ifndef SAIL_PRESENT_MIN_CTAS
+#define SAIL_PRESENT_MIN_CTAS(KIND) ((KIND) == 0 ? 1 : 2)
+#endif
 template <int KIND>
-__global__ void __launch_bounds__(256) sail_present_kernel(const __grid_constant__ PresentParams P) {
+__global__ void __launch_bounds__(256, SAIL_PRESENT_MIN_CTAS(KIND)) sail_present_kernel(const __grid_constant__ PresentParams P) {
     int x = blockIdx.x * 32 + (threadIdx.x & 31);
     int y = blockIdx.y * 8 + (threadIdx.x >> 5);
     if (x >= P.W || y >= P.H) return;
