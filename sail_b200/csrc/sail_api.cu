@@ -544,11 +544,18 @@ int launchQueue(sail_ctx* ctx, SailMember& m, int small, const SailFrameDev* fra
         size_t cap = npixTotal * SAIL_MAX_BATCH;
         if (cap > maxPaths) cap = maxPaths;
         if (cap < 1024) cap = 1024;
-        CU(cudaMalloc(&m.qRay, cap * 2 * sizeof(float4)));
-        CU(cudaMalloc(&m.qCarry, cap * 2 * sizeof(float4)));
-        CU(cudaMalloc(&m.qHit, cap * sizeof(int2)));
-        CU(cudaMalloc(&m.qPerm, cap * sizeof(int)));
-        CU(cudaMalloc(&m.qCounters, (SAIL_Q_MAX_BOUNCES + 1) * 2 * SAIL_Q_CLASSES * sizeof(int)));
+        // all or nothing: a half-allocated set must not look complete to the next call (m.qRay is the "allocated" flag)
+        cudaError_t qe = cudaMalloc(&m.qCarry, cap * 2 * sizeof(float4));
+        if (qe == cudaSuccess) qe = cudaMalloc(&m.qHit, cap * sizeof(int2));
+        if (qe == cudaSuccess) qe = cudaMalloc(&m.qPerm, cap * sizeof(int));
+        if (qe == cudaSuccess) qe = cudaMalloc(&m.qCounters, (SAIL_Q_MAX_BOUNCES + 1) * 2 * SAIL_Q_CLASSES * sizeof(int));
+        if (qe == cudaSuccess) qe = cudaMalloc(&m.qRay, cap * 2 * sizeof(float4));
+        if (qe != cudaSuccess) {
+            cudaFree(m.qCarry); cudaFree(m.qHit); cudaFree(m.qPerm); cudaFree(m.qCounters);
+            m.qCarry = nullptr; m.qHit = nullptr; m.qPerm = nullptr; m.qCounters = nullptr; m.qRay = nullptr;
+            cudaGetLastError();
+            return setErr(ctx, SAIL_ERR_NOMEM, "queue wavefront: %s allocating the queues for %zu paths", cudaGetErrorString(qe), cap);
+        }
         m.qCapacity = cap;
     }
     size_t chunk = m.qCapacity / (size_t)nframes;
