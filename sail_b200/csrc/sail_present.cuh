@@ -66,22 +66,18 @@ SD V4 textureLinear(const float* img, int W, int H, float u, float v) {
 // weight of a coordinate are computed once per axis value instead of once per tap (16 instead of 128 coordinate set-ups, 32
 // instead of 512 integer modulos per pixel).  Every tap still evaluates exactly the expressions of textureLinear().
 struct AxisTap {
-    int i0, i1;   // wrapped texel indices
-    float t, omt; // blend weight and 1 - t
-    bool ok;      // coordinate inside [0, 1] (windowSampler's test)
+    int i0, i1;  // wrapped texel indices (rowTap: offsets of the two rows' first texels)
+    float t;     // blend weight in 1/256 steps; 1 - t is formed at the use (three registers per axis value, not five)
 };
+SD bool axisInside(float c) { return !(c < 0.0f || c > 1.0f); }  // windowSampler's test, window.glsl:2-3
 SD AxisTap axisTap(float c, int size) {
     AxisTap a;
-    a.ok = !(c < 0.0f || c > 1.0f);
     int i0;
     linearCoord(c, size, i0, a.t);
-    a.omt = 1.0f - a.t;
     a.i0 = wrapIndex(i0, size);
     a.i1 = wrapIndex(i0 + 1, size);
     return a;
 }
-// One 16-byte load per texel instead of three 4-byte loads 12 bytes apart: the 64 taps x 4 texels of a window filter are bound by
-// L1 wavefronts (a warp's 32 texels span three cache lines per scalar load), not by arithmetic.
 // Texel index = row * W + column as 32-bit arithmetic on a row offset prepared once per y value (rowTap): one add and one
 // widening multiply-add per load instead of a 64-bit multiply per texel (a quarter of the kernel's instructions were address
 // arithmetic).  W * H < 2^31 texels.
@@ -94,17 +90,17 @@ SD AxisTap rowTap(AxisTap y, int W) {  // i0 / i1 become offsets of the rows' fi
     y.i1 *= W;
     return y;
 }
-SD V3 windowTap(const PresentParams& P, const AxisTap& X, const AxisTap& Yr, int& count) {
-    if (!(X.ok && Yr.ok)) return splat3(0.0f);
+SD V3 windowTap(const PresentParams& P, const AxisTap& X, const AxisTap& Yr, bool ok, int& count) {
+    if (!ok) return splat3(0.0f);
     count++;
     const V3 c00 = texel3(P.color4, (unsigned)(Yr.i0 + X.i0)), c10 = texel3(P.color4, (unsigned)(Yr.i0 + X.i1));
     const V3 c01 = texel3(P.color4, (unsigned)(Yr.i1 + X.i0)), c11 = texel3(P.color4, (unsigned)(Yr.i1 + X.i1));
     // textureLinear(): a = c00*(1-tx) + c10*tx, b = c01*(1-tx) + c11*tx, a*(1-ty) + b*ty, per channel, plain scalar operations
-    // (the red / green pair through the packed FP32 pipe was measured: 10 % fewer instructions, same 0.345 ms -- the kernel
-    // waits for its 256 texel loads per pixel, not for issue slots)
-    const V3 a = mk3(c00.x * X.omt + c10.x * X.t, c00.y * X.omt + c10.y * X.t, c00.z * X.omt + c10.z * X.t);
-    const V3 b = mk3(c01.x * X.omt + c11.x * X.t, c01.y * X.omt + c11.y * X.t, c01.z * X.omt + c11.z * X.t);
-    return mk3(a.x * Yr.omt + b.x * Yr.t, a.y * Yr.omt + b.y * Yr.t, a.z * Yr.omt + b.z * Yr.t);
+    // (the red / green pair through the packed FP32 pipe was measured: 10 % fewer instructions, same 0.345 ms)
+    const float xo = 1.0f - X.t, yo = 1.0f - Yr.t;
+    const V3 a = mk3(c00.x * xo + c10.x * X.t, c00.y * xo + c10.y * X.t, c00.z * xo + c10.z * X.t);
+    const V3 b = mk3(c01.x * xo + c11.x * X.t, c01.y * xo + c11.y * X.t, c01.z * xo + c11.z * X.t);
+    return mk3(a.x * yo + b.x * Yr.t, a.y * yo + b.y * Yr.t, a.z * yo + b.z * Yr.t);
 }
 // window.glsl:26-44 (table lookup i*j+j as written)
 SD V4 filterWindow(const PresentParams& P, float tx, float ty) {
@@ -112,15 +108,19 @@ SD V4 filterWindow(const PresentParams& P, float tx, float ty) {
     float weightSum = 0.0f;
     const float rW = dm_rcp((float)P.W), rH = dm_rcp((float)P.H);
     AxisTap Xp[4], Xm[4], Yp[4], Ym[4];
+    unsigned inside = 0;  // bit k: Xp[k], 4 + k: Xm[k], 8 + k: Yp[k], 12 + k: Ym[k] inside [0, 1]
 #pragma unroll
     for (int k = 0; k < 4; k++) {
         // window.glsl:10-24: x = vec2(i/W, 0), y = vec2(0, j/H); the shader's `+ 0.0` / `- 0.0` terms leave the sums unchanged
         const float xx = fdiv(((float)k + 0.5f) * P.radius[0], 4.0f) * rW;
         const float yy = fdiv(((float)k + 0.5f) * P.radius[1], 4.0f) * rH;
-        Xp[k] = axisTap(tx + xx + 0.0f, P.W);
-        Xm[k] = axisTap(tx - xx + 0.0f, P.W);
-        Yp[k] = rowTap(axisTap(ty + 0.0f + yy, P.H), P.W);
-        Ym[k] = rowTap(axisTap(ty + 0.0f - yy, P.H), P.W);
+        const float xp = tx + xx + 0.0f, xm = tx - xx + 0.0f, yp = ty + 0.0f + yy, ym = ty + 0.0f - yy;
+        Xp[k] = axisTap(xp, P.W);
+        Xm[k] = axisTap(xm, P.W);
+        Yp[k] = rowTap(axisTap(yp, P.H), P.W);
+        Ym[k] = rowTap(axisTap(ym, P.H), P.W);
+        inside |= (axisInside(xp) ? 1u : 0u) << k | (axisInside(xm) ? 1u : 0u) << (4 + k) | (axisInside(yp) ? 1u : 0u) << (8 + k) |
+                  (axisInside(ym) ? 1u : 0u) << (12 + k);
     }
 #pragma unroll
     for (int i = 0; i < 4; i++) {
@@ -128,10 +128,11 @@ SD V4 filterWindow(const PresentParams& P, float tx, float ty) {
         for (int j = 0; j < 4; j++) {
             int count = 0;
             V3 tmp = splat3(0.0f);
-            tmp = tmp + windowTap(P, Xp[j], Yp[i], count);
-            tmp = tmp + windowTap(P, Xp[j], Ym[i], count);
-            tmp = tmp + windowTap(P, Xm[j], Yp[i], count);
-            tmp = tmp + windowTap(P, Xm[j], Ym[i], count);
+            const bool xpIn = (inside >> j) & 1u, xmIn = (inside >> (4 + j)) & 1u, ypIn = (inside >> (8 + i)) & 1u, ymIn = (inside >> (12 + i)) & 1u;
+            tmp = tmp + windowTap(P, Xp[j], Yp[i], xpIn && ypIn, count);
+            tmp = tmp + windowTap(P, Xp[j], Ym[i], xpIn && ymIn, count);
+            tmp = tmp + windowTap(P, Xm[j], Yp[i], xmIn && ypIn, count);
+            tmp = tmp + windowTap(P, Xm[j], Ym[i], xmIn && ymIn, count);
             float weight = P.weights[i * j + j];
             weightSum += weight * (float)count;
             color = color + tmp * weight;
@@ -143,9 +144,10 @@ SD V4 filterWindow(const PresentParams& P, float tx, float ty) {
 // textureLinear() on prepared axis values (AxisTap: texel pair, wrap-around and 8-bit blend weight of one coordinate): the same
 // V4 expressions on the same texels; the colour map comes from the padded copy, the position map from its 12-byte layout.
 SD V4 bilinearOf(V4 c00, V4 c10, V4 c01, V4 c11, const AxisTap& X, const AxisTap& Y) {
-    V4 a = c00 * X.omt + c10 * X.t;
-    V4 b = c01 * X.omt + c11 * X.t;
-    return a * Y.omt + b * Y.t;
+    const float xo = 1.0f - X.t, yo = 1.0f - Y.t;
+    V4 a = c00 * xo + c10 * X.t;
+    V4 b = c01 * xo + c11 * X.t;
+    return a * yo + b * Y.t;
 }
 SD V4 texel4(const float4* img, unsigned idx) {
     const float4 q = __ldg(img + idx);
@@ -241,10 +243,11 @@ SD float tonemap1(float c) {
 // KIND: 0 = the point filters (color / gamma / tonemapping / normal / position), 1 = window filters, 2 = wavelet -- three
 // instantiations, so the 64-tap window filter's registers (112) do not set the occupancy of the one-fetch filters.
 extern __shared__ float4 sail_present_smem[];  // KIND 2: SAIL_WAVELET_SMEM_BYTES (the wavelet's tap cache)
-// CTAs per SM the register allocation aims at.  Measured at 1080p (tools/ubench/present_win.cu): window filters 0.53 / 0.38 / 0.38 /
-// 0.42 ms at 1 / 2 / 3 / 4 (spills from 3 on), wavelet 0.73 / 0.73 / 0.76 / 0.84 ms (its 80 KB tap cache allows two anyway).
+// CTAs per SM the register allocation aims at.  Measured at 1080p (tools/ubench/present_win.cu, three registers per prepared axis
+// value): window filters 0.355 / 0.326 / 0.336 ms at 2 / 3 / 4 (85 registers at 3, spills at 4), wavelet 0.700 / 0.711 / 0.765 ms
+// (its 80 KB tap cache allows two).
 #ifndef SAIL_PRESENT_MIN_CTAS
-#define SAIL_PRESENT_MIN_CTAS(KIND) ((KIND) == 0 ? 1 : 2)
+#define SAIL_PRESENT_MIN_CTAS(KIND) ((KIND) == 0 ? 1 : ((KIND) == 1 ? 3 : 2))
 #endif
 template <int KIND>
 __global__ void __launch_bounds__(256, SAIL_PRESENT_MIN_CTAS(KIND)) sail_present_kernel(const __grid_constant__ PresentParams P) {
